@@ -1,0 +1,117 @@
+/*
+ * ref_shim.c -- thin C wrapper that links the UNMODIFIED reference sources
+ * (/root/reference/suffix_array/engine.c, libsais.c) into oracle/_ref/libsa_ref.so so that
+ * tests and bench.py can call them through ctypes.  TEST INFRASTRUCTURE ONLY: nothing under
+ * suffixarray_b200/ loads this.  No reference source is copied; oracle/Makefile compiles the
+ * files where they lie.  All functions here only marshal arguments and silence the
+ * reference's printf()s; the arithmetic is the reference's own.
+ */
+#define _GNU_SOURCE
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdint.h>
+#include <unistd.h>
+#include <fcntl.h>
+#include <omp.h>
+#include "engine.h"
+#include "libsais.h"
+
+static int g_saved_fd = -1;
+static void hush(void)
+{
+    fflush(stdout);
+    g_saved_fd = dup(1);
+    int dn = open("/dev/null", O_WRONLY);
+    if (dn >= 0) { dup2(dn, 1); close(dn); }
+}
+static void unhush(void)
+{
+    fflush(stdout);
+    if (g_saved_fd >= 0) { dup2(g_saved_fd, 1); close(g_saved_fd); g_saved_fd = -1; }
+}
+
+/* construct_truncated_suffix_array (engine.c:837) on caller-owned buffers.
+ * text_padded must have >= 128 readable zero bytes after n. */
+void ref_build(const char* text_padded, uint32_t n, uint32_t max_suffix_length, uint32_t* sa_out)
+{
+    SuffixArray_struct s;
+    memset(&s, 0, sizeof s);
+    s.suffix_array = sa_out;
+    s.max_suffix_length = max_suffix_length;
+    s.n = n;
+    s.global_byte_end_idx = n;
+    hush();
+    construct_truncated_suffix_array(text_padded, &s);
+    unhush();
+}
+
+/* get_substring_positions (engine.c:869).  Returns 1 and leaves outputs untouched when the
+ * call could take the reference's `last = mid - 1` wrap at mid == 0 (out-of-bounds read):
+ * that needs strncmp(text + SA[0], q, c) >= 0, so such queries are simply not submitted. */
+int ref_query(const char* text_padded, const uint32_t* sa, uint32_t n, uint32_t max_suffix_length,
+              const char* q_cstr, uint32_t* start, uint32_t* end)
+{
+    SuffixArray_struct s;
+    memset(&s, 0, sizeof s);
+    s.suffix_array = (uint32_t*)sa;
+    s.max_suffix_length = max_suffix_length;
+    s.n = n;
+    if (n == 0) return 1;
+    size_t m = strlen(q_cstr);
+    size_t c = m < max_suffix_length ? m : max_suffix_length;
+    if (strncmp(text_padded + sa[0], q_cstr, c) >= 0) return 1;
+    pair_u32 r = get_substring_positions(text_padded, &s, q_cstr);
+    *start = r.first; *end = r.second;
+    return 0;
+}
+
+/* Batch of NUL-terminated queries at qbytes + qoff[i]; skipped[i] = 1 where ref_query refused.
+ * nthreads <= 0: all cores (an omp parallel-for over the batch, SURVEY 8(d) baseline A). */
+void ref_query_batch(const char* text_padded, const uint32_t* sa, uint32_t n, uint32_t max_suffix_length,
+                     const char* qbytes, const uint64_t* qoff, uint64_t nq,
+                     uint32_t* start, uint32_t* end, uint8_t* skipped, int nthreads)
+{
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+    for (long i = 0; i < (long)nq; ++i) {
+        skipped[i] = (uint8_t)ref_query(text_padded, sa, n, max_suffix_length, qbytes + qoff[i],
+                                        &start[i], &end[i]);
+    }
+}
+
+/* CSV path end to end: construct_truncated_suffix_array_from_csv_partitioned_mmap_full
+ * (engine.c:1454).  Single-partition files only (< 2 GiB).  Returns n, or 0 when the
+ * column was not found; copies the SA (file offsets) and the per-rank quoted bits
+ * (one byte per rank) into caller buffers of capacity cap. */
+uint32_t ref_csv_build(const char* path, const char* column, uint32_t max_suffix_length,
+                       uint32_t* sa_out, uint8_t* quoted_out, uint64_t cap)
+{
+    SuffixArrayIndex* idx = NULL;
+    char* cols[1];
+    cols[0] = (char*)column;
+    hush();
+    construct_truncated_suffix_array_from_csv_partitioned_mmap_full(&idx, path, max_suffix_length, cols, 1);
+    unhush();
+    SuffixArray_struct* s = &idx->suffix_arrays[0];
+    uint32_t n = s->n;
+    if (n <= cap) {
+        memcpy(sa_out, s->suffix_array, (size_t)n * sizeof(uint32_t));
+        for (uint32_t i = 0; i < n; ++i) quoted_out[i] = get_buffer_bit(s->is_quoted_bitflag, i);
+    }
+    free(s->suffix_array);
+    return n;
+}
+
+/* libsais (vendored 2.8.4), the "baseline B" timing arm -- a FULL suffix array, never a
+ * parity oracle.  threads <= 1: libsais(); else libsais_omp(). */
+int ref_libsais(const uint8_t* text, int32_t* sa, int32_t n, int threads)
+{
+#ifdef LIBSAIS_OPENMP
+    if (threads != 1) return libsais_omp(text, sa, n, 0, NULL, threads < 0 ? 0 : threads);
+#endif
+    (void)threads;
+    return libsais(text, sa, n, 0, NULL);
+}
+
+int ref_max_threads(void) { return omp_get_max_threads(); }
