@@ -1,0 +1,127 @@
+/*
+ * sa_cuda.h -- C ABI of libsa_cuda.so: truncated suffix-array build + batched substring query
+ * on one B200 (sm_100a).  Plain pointers and sizes only; no torch / C++ types.
+ *
+ * Each entry point names the reference interface it replaces (paths under
+ * /root/reference/suffix_array/).  The reference binds these through
+ * `cdef extern from "engine.h"` in suffix_array.pyx:37-101; INTEGRATION.md shows the
+ * replacement `cdef extern from "sa_cuda.h"` block.
+ *
+ * Conventions: every function returns SA_OK (0) or a negative sa_status; the message of the
+ * last failure on the calling thread is sa_last_error().  The library never prints and never
+ * calls exit() (the reference does both, e.g. engine.c:125,477,865).  There is no CPU
+ * fallback: without a CUDA device every call fails with SA_ERR_CUDA.
+ * Pointers named d_* are DEVICE pointers; all others are HOST pointers.
+ */
+#ifndef SA_CUDA_H
+#define SA_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SA_CUDA_ABI_VERSION 1
+
+typedef enum sa_status {
+    SA_OK = 0,
+    SA_ERR_INVALID = -1,   /* bad argument / call order */
+    SA_ERR_OOM = -2,       /* host or device allocation failed */
+    SA_ERR_CUDA = -3,      /* CUDA runtime / kernel failure */
+    SA_ERR_IO = -4,        /* file could not be opened / mapped, column not found */
+    SA_ERR_LIMIT = -5,     /* n >= 2^32 - 1024 or max_suffix_length > 4096 */
+    SA_ERR_INTERNAL = -6   /* an internal invariant failed (device-side guard tripped) */
+} sa_status;
+
+/* build flags */
+#define SA_FLAG_LOWERCASE 1u   /* ASCII A-Z -> a-z on the device copy of the text: replaces
+                                  lowercase_string, suffix_array.pyx:103-107 */
+#define SA_FLAG_TIMING    2u   /* record per-phase CUDA-event times into sa_stats */
+
+/* Opaque index: owns the device text, the SA, the doc-offset table and all scratch.
+ * Replaces SuffixArray_struct (engine.h:123-130) / SuffixArrayIndex (engine.h:163-172). */
+typedef struct sa_index sa_index;
+
+typedef struct sa_stats {
+    uint64_t n;                 /* text bytes == SA entries */
+    uint32_t max_suffix_length; /* L as given */
+    uint32_t lprime;            /* min(L, n), engine.c:841 */
+    uint32_t rounds;            /* refinement rounds after round 0 */
+    uint32_t radix_passes;      /* onesweep scatter launches of the last build */
+    uint64_t kernel_launches;   /* kernels launched by the last build / query call */
+    uint64_t refined_elems;     /* sum over rounds of elements re-sorted */
+    uint64_t finish_runs;       /* <=32 buckets re-sorted by the 17-byte window key */
+    uint64_t num_docs;          /* '\n' count + 1 */
+    float ms_total;             /* device time of the last build (SA_FLAG_TIMING) */
+    float ms_h2d, ms_pack, ms_hist, ms_sort0, ms_refine, ms_finish, ms_docs, ms_remap;
+    float ms_onesweep_sum;      /* sum of all onesweep scatter launches */
+    float ms_query, ms_hits;    /* last query batch (device time) */
+    uint64_t onesweep_elems;    /* total elements moved by those launches */
+} sa_stats;
+
+const char* sa_last_error(void);
+int sa_abi_version(void);
+
+/* Lifecycle.  Replaces init_suffix_array / init_suffix_array_byte_idxs (engine.c:309-344) and
+ * free_suffix_array (engine.c:346).  device: CUDA ordinal. */
+int sa_create(sa_index** out, uint32_t max_suffix_length, int device);
+void sa_destroy(sa_index* idx);
+
+/* Build from a host text of n bytes ('\n'-joined documents, suffix_array.pyx:143).
+ * Replaces construct_truncated_suffix_array(const char*, SuffixArray_struct*), engine.h:217 /
+ * engine.c:837-866, producing the identical uint32 order.  H2D copy included. */
+int sa_build_text(sa_index* idx, const uint8_t* text, uint64_t n, uint32_t flags);
+
+/* Same, text already resident in HBM (copied device-to-device into the index). */
+int sa_build_text_device(sa_index* idx, const uint8_t* d_text, uint64_t n, uint32_t flags);
+
+/* CSV path.  Replaces construct_truncated_suffix_array_from_csv_partitioned_mmap_full
+ * (engine.h:209-215, engine.c:1454-1482 -> :461-654): mmap the file, scan `column` into
+ * pinned text / file-offset / quoted buffers (engine.c:522-605), build, then gather
+ * SA[i] = map[SA[i]] and the per-rank quoted bits on the device (engine.c:632-651).
+ * Single partition (file < 2 GiB), as the reference handles one partition per 2 GiB. */
+int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags);
+
+/* Accessors.  sa_copy_sa_u32 returns what SuffixArray_struct.suffix_array holds after the
+ * build (text positions; FILE OFFSETS after sa_build_csv, engine.c:647-651). */
+uint64_t sa_size(const sa_index* idx);
+int sa_copy_sa_u32(sa_index* idx, uint32_t* out, uint64_t cap);
+int sa_copy_sa_i64(sa_index* idx, int64_t* out, uint64_t cap);
+int sa_copy_text_positions_u32(sa_index* idx, uint32_t* out, uint64_t cap); /* pre-remap SA (CSV) */
+int sa_copy_quoted_bits(sa_index* idx, uint8_t* out_bits, uint64_t cap_bytes); /* LSB-first, engine.c:264-286 */
+int sa_copy_text(sa_index* idx, uint8_t* out, uint64_t cap);   /* the (lower-cased) text that was indexed */
+const uint32_t* sa_device_sa(const sa_index* idx);              /* device pointer, n entries */
+int sa_get_stats(const sa_index* idx, sa_stats* out);
+
+/* Batched query.  Query i is qbytes[qoff[i] .. qoff[i+1]) (cut at its first NUL, as strlen
+ * does, engine.c:874).  Replaces get_substring_positions (engine.h:229-233, engine.c:869-918):
+ * start[i], end[i] are the inclusive rank range with the reference's UINT32_MAX sentinels.
+ * hit_off[nq+1] is the exclusive prefix sum of min(k, end-start+1) (engine.c:1181-1185);
+ * hit_off[nq] = total hits.  Any output pointer may be NULL.  Results stay on the device for
+ * sa_query_hits. */
+int sa_query_ranges(sa_index* idx, const uint8_t* qbytes, const uint64_t* qoff, uint64_t nq,
+                    uint32_t k, uint32_t* start, uint32_t* end, uint64_t* hit_off);
+
+/* Hits of the last sa_query_ranges call, in rank order, duplicates kept (engine.c:1187):
+ * hit_pos = SA[rank] (text position), hit_doc = record index = number of '\n' before it
+ * (the record engine.c:1189-1191 scans back to).  Replaces the hit loop of
+ * get_matching_records / get_matching_records_file (engine.c:1185-1211, :1356-1388). */
+int sa_query_hits(sa_index* idx, uint32_t* hit_pos, uint32_t* hit_doc, uint64_t cap);
+
+/* Device-resident variants for callers that keep batches in HBM (bench `value` path). */
+int sa_query_ranges_device(sa_index* idx, const uint8_t* d_qbytes, const uint64_t* d_qoff, uint64_t nq,
+                           uint64_t qbytes_len, uint32_t k, uint32_t* d_start, uint32_t* d_end);
+
+/* Document table: doc_start[num_docs] = text offset of each record's first byte. */
+uint64_t sa_num_docs(const sa_index* idx);
+int sa_copy_doc_starts(sa_index* idx, uint32_t* out, uint64_t cap);
+
+/* Debug / parity hooks (used by tests to localise a mismatch; not part of the drop-in). */
+int sa_debug_copy_lcp(sa_index* idx, uint16_t* out, uint64_t cap);
+int sa_debug_set(sa_index* idx, const char* key, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SA_CUDA_H */

@@ -1,0 +1,210 @@
+"""ctypes binding of libsa_cuda.so (the C ABI declared in include/sa_cuda.h).
+
+The library is built in-tree by ``suffixarray_b200/csrc/Makefile`` (``__graft_entry__.build()``).
+There is no CPU fallback: if the shared object is missing, or no CUDA device is present,
+every entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsa_cuda.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+SA_OK = 0
+SA_FLAG_LOWERCASE = 1
+SA_FLAG_TIMING = 2
+UINT32_MAX = 0xFFFFFFFF
+
+# every symbol include/sa_cuda.h declares (checked by tests/test_abi.py)
+EXPORTS = [
+    "sa_last_error", "sa_abi_version", "sa_create", "sa_destroy", "sa_build_text", "sa_build_text_device",
+    "sa_build_csv", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
+    "sa_copy_quoted_bits", "sa_copy_text", "sa_device_sa", "sa_get_stats", "sa_query_ranges", "sa_query_hits",
+    "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
+]
+
+
+class SaStats(C.Structure):
+    _fields_ = [
+        ("n", C.c_uint64), ("max_suffix_length", C.c_uint32), ("lprime", C.c_uint32), ("rounds", C.c_uint32),
+        ("radix_passes", C.c_uint32), ("kernel_launches", C.c_uint64), ("refined_elems", C.c_uint64),
+        ("finish_runs", C.c_uint64), ("num_docs", C.c_uint64), ("ms_total", C.c_float), ("ms_h2d", C.c_float),
+        ("ms_pack", C.c_float), ("ms_hist", C.c_float), ("ms_sort0", C.c_float), ("ms_refine", C.c_float),
+        ("ms_finish", C.c_float), ("ms_docs", C.c_float), ("ms_remap", C.c_float), ("ms_onesweep_sum", C.c_float),
+        ("ms_query", C.c_float), ("ms_hits", C.c_float), ("onesweep_elems", C.c_uint64),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class SaCudaError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"libsa_cuda error {code}: {msg}")
+        self.code = code
+
+
+def build_library(force: bool = False) -> None:
+    """Compile libsa_cuda.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    if force:
+        subprocess.run(["make", "-C", CSRC, "clean"], check=True, capture_output=True)
+    r = subprocess.run(["make", "-C", CSRC, "-j8"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building libsa_cuda.so failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+
+
+_lib = None
+_vp = C.c_void_p
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(the CUDA extension is required; there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    L.sa_last_error.restype = C.c_char_p
+    L.sa_abi_version.restype = C.c_int
+    L.sa_create.argtypes = [C.POINTER(_vp), C.c_uint32, C.c_int]
+    L.sa_destroy.argtypes = [_vp]
+    L.sa_destroy.restype = None
+    L.sa_build_text.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
+    L.sa_build_text_device.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
+    L.sa_build_csv.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint32]
+    L.sa_size.argtypes = [_vp]
+    L.sa_size.restype = C.c_uint64
+    L.sa_num_docs.argtypes = [_vp]
+    L.sa_num_docs.restype = C.c_uint64
+    for name in ("sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32", "sa_copy_quoted_bits",
+                 "sa_copy_text", "sa_copy_doc_starts", "sa_debug_copy_lcp"):
+        getattr(L, name).argtypes = [_vp, _vp, C.c_uint64]
+    L.sa_device_sa.argtypes = [_vp]
+    L.sa_device_sa.restype = _vp
+    L.sa_get_stats.argtypes = [_vp, C.POINTER(SaStats)]
+    L.sa_query_ranges.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp, _vp]
+    L.sa_query_hits.argtypes = [_vp, _vp, _vp, C.c_uint64]
+    L.sa_query_ranges_device.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint64, C.c_uint32, _vp, _vp]
+    L.sa_debug_set.argtypes = [_vp, C.c_char_p, C.c_int64]
+    _lib = L
+    return L
+
+
+def check(rc: int) -> None:
+    if rc != SA_OK:
+        raise SaCudaError(rc, lib().sa_last_error().decode("utf-8", "replace"))
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(_vp)
+
+
+class Index:
+    """Thin RAII wrapper over an ``sa_index*`` (NumPy in, NumPy out)."""
+
+    def __init__(self, max_suffix_length: int = 64, device: int = 0):
+        self._h = _vp()
+        check(lib().sa_create(C.byref(self._h), max_suffix_length, device))
+        self.max_suffix_length = max_suffix_length
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().sa_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # ---- builds
+    def build_text(self, text, lowercase: bool = False, timing: bool = False):
+        t = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray, memoryview)) \
+            else np.ascontiguousarray(text, dtype=np.uint8)
+        flags = (SA_FLAG_LOWERCASE if lowercase else 0) | (SA_FLAG_TIMING if timing else 0)
+        check(lib().sa_build_text(self._h, _ptr(t) if t.size else None, t.size, flags))
+
+    def build_text_ptr(self, host_ptr: int, n: int, flags: int = 0):
+        check(lib().sa_build_text(self._h, host_ptr, n, flags))
+
+    def build_text_device(self, dev_ptr: int, n: int, flags: int = 0):
+        check(lib().sa_build_text_device(self._h, dev_ptr, n, flags))
+
+    def build_csv(self, path: str, column: str, timing: bool = False):
+        check(lib().sa_build_csv(self._h, path.encode(), column.encode(), SA_FLAG_TIMING if timing else 0))
+
+    def debug_set(self, key: str, value: int):
+        check(lib().sa_debug_set(self._h, key.encode(), value))
+
+    # ---- accessors
+    @property
+    def n(self) -> int:
+        return int(lib().sa_size(self._h))
+
+    @property
+    def num_docs(self) -> int:
+        return int(lib().sa_num_docs(self._h))
+
+    def _copy(self, fn, dtype, count):
+        out = np.empty(max(count, 1), dtype=dtype)
+        check(fn(self._h, _ptr(out), count))
+        return out[:count]
+
+    def sa(self) -> np.ndarray:
+        return self._copy(lib().sa_copy_sa_u32, np.uint32, self.n)
+
+    def sa_i64(self) -> np.ndarray:
+        return self._copy(lib().sa_copy_sa_i64, np.int64, self.n)
+
+    def text_positions(self) -> np.ndarray:
+        return self._copy(lib().sa_copy_text_positions_u32, np.uint32, self.n)
+
+    def text(self) -> np.ndarray:
+        return self._copy(lib().sa_copy_text, np.uint8, self.n)
+
+    def lcp(self) -> np.ndarray:
+        return self._copy(lib().sa_debug_copy_lcp, np.uint16, self.n)
+
+    def doc_starts(self) -> np.ndarray:
+        return self._copy(lib().sa_copy_doc_starts, np.uint32, self.num_docs)
+
+    def quoted_bits(self) -> np.ndarray:
+        nbytes = (self.n + 7) // 8
+        out = np.zeros(max(nbytes, 1), dtype=np.uint8)
+        check(lib().sa_copy_quoted_bits(self._h, _ptr(out), nbytes))
+        return np.unpackbits(out[:nbytes], bitorder="little")[: self.n]
+
+    def stats(self) -> dict:
+        s = SaStats()
+        check(lib().sa_get_stats(self._h, C.byref(s)))
+        return s.as_dict()
+
+    # ---- queries
+    def query_ranges_packed(self, qbytes: np.ndarray, qoff: np.ndarray, k: int = 1000, want_offsets: bool = True):
+        nq = qoff.size - 1
+        start = np.empty(max(nq, 1), dtype=np.uint32)
+        end = np.empty(max(nq, 1), dtype=np.uint32)
+        hit_off = np.zeros(nq + 1, dtype=np.uint64) if want_offsets else None
+        check(lib().sa_query_ranges(self._h, _ptr(qbytes), _ptr(qoff), nq, k, _ptr(start), _ptr(end),
+                                    _ptr(hit_off) if want_offsets else None))
+        return start[:nq], end[:nq], hit_off
+
+    def query_ranges(self, queries, k: int = 1000):
+        """queries: list[bytes] -> (start u32, end u32, hit_off u64[nq+1])."""
+        lens = np.fromiter((len(q) for q in queries), dtype=np.uint64, count=len(queries))
+        qoff = np.zeros(len(queries) + 1, dtype=np.uint64)
+        np.cumsum(lens, out=qoff[1:])
+        joined = b"".join(queries)
+        qbytes = np.frombuffer(joined, dtype=np.uint8) if joined else np.zeros(1, np.uint8)
+        return self.query_ranges_packed(qbytes, qoff, k)
+
+    def query_hits(self, total: int):
+        pos = np.empty(max(total, 1), dtype=np.uint32)
+        doc = np.empty(max(total, 1), dtype=np.uint32)
+        check(lib().sa_query_hits(self._h, _ptr(pos), _ptr(doc), total))
+        return pos[:total], doc[:total]

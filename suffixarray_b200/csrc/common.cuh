@@ -1,0 +1,115 @@
+// common.cuh -- shared device helpers for libsa_cuda (sm_100a).
+//
+// Key representation used everywhere: a "masked word" is a big-endian u64 whose TOP cb bytes
+// are bytes [depth, depth+cb) of a suffix, with every byte after the first terminator
+// ('\n' or 0xFF -- the buckets the reference never refines, engine.c:771-773,795-796) set to
+// zero, and the low 8-cb bytes zero.  Unsigned integer order on masked words == the order of
+// the reference's per-byte counting sorts over those bytes (engine.c:734-758).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SA_SMALL 32            // insertion-sort cut-off, engine.c:710
+#define SA_TEXT_PAD 1024       // zero bytes kept after the device text
+
+namespace sa {
+
+__device__ __forceinline__ uint64_t bswap64(uint64_t v)
+{
+    uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+    lo = __byte_perm(lo, 0, 0x0123);
+    hi = __byte_perm(hi, 0, 0x0123);
+    return ((uint64_t)lo << 32) | hi;
+}
+
+// 8 text bytes starting at byte offset `a` (any alignment), first byte in the top byte.
+// The text allocation is 8-byte aligned and zero padded, so the two aligned loads are safe.
+__device__ __forceinline__ uint64_t load_be64(const uint8_t* __restrict__ text, uint64_t a)
+{
+    const uint64_t* w = reinterpret_cast<const uint64_t*>(text + (a & ~7ull));
+    uint64_t lo = __ldg(w);
+    unsigned sh = (unsigned)(a & 7ull) * 8u;
+    uint64_t v = lo;
+    if (sh) {
+        uint64_t hi = __ldg(w + 1);
+        v = (lo >> sh) | (hi << (64u - sh));
+    }
+    return bswap64(v);
+}
+
+// 0x80 in every byte of v that is zero, exact (no borrow artefacts).
+__device__ __forceinline__ uint64_t zero_bytes(uint64_t v)
+{
+    const uint64_t k7f = 0x7F7F7F7F7F7F7F7Full;
+    return ~(((v & k7f) + k7f) | v | k7f);
+}
+
+// 0x80 in every byte of be that is '\n' (0x0A) or 0xFF.
+__device__ __forceinline__ uint64_t terminator_bytes(uint64_t be)
+{
+    return zero_bytes(be ^ 0x0A0A0A0A0A0A0A0Aull) | zero_bytes(~be);
+}
+
+// keep the top cb bytes (1 <= cb <= 8)
+__device__ __forceinline__ uint64_t keep_top_bytes(uint64_t be, int cb)
+{
+    return cb >= 8 ? be : (be & (~0ull << (8 * (8 - cb))));
+}
+
+// masked word: top cb bytes, zero after the first terminator.
+__device__ __forceinline__ uint64_t mask_word(uint64_t be, int cb)
+{
+    be = keep_top_bytes(be, cb);
+    uint64_t t = terminator_bytes(be);
+    if (t) {
+        int j = __clzll((long long)t) >> 3;           // index of the first terminator byte
+        be &= ~0ull << (8 * (7 - j));
+    }
+    return be;
+}
+
+__device__ __forceinline__ bool word_has_terminator(uint64_t masked) { return terminator_bytes(masked) != 0; }
+
+// LCP contribution of two masked words sorted adjacent in one group: returns the new lcp value
+// (bytes), lprime when they are tied through a terminator or to the truncation.
+__device__ __forceinline__ uint32_t pair_lcp(uint64_t a, uint64_t b, uint32_t depth, int cb, uint32_t lprime)
+{
+    uint64_t x = a ^ b;
+    uint32_t v;
+    if (x == 0) {
+        v = word_has_terminator(b) ? lprime : depth + (uint32_t)cb;
+    } else {
+        uint32_t cm = (uint32_t)__clzll((long long)x) >> 3;
+        if (cm > (uint32_t)cb) cm = (uint32_t)cb;
+        v = depth + cm;
+    }
+    return v < lprime ? v : lprime;
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+__device__ __forceinline__ uint32_t lanemask_lt()
+{
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// streaming (evict-first) 8/4-byte loads and stores for the sort passes
+__device__ __forceinline__ uint64_t ld_stream_u64(const uint64_t* p)
+{
+    uint64_t v;
+    asm volatile("ld.global.cs.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.global.cs.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+}  // namespace sa
+
+// error flag bits written by device-side guards (sa_index::d_err)
+#define SA_DEVERR_LOOKBACK_TIMEOUT 1u
+#define SA_DEVERR_RUN_TOO_LONG 2u

@@ -1,0 +1,64 @@
+// kernels.h -- host-side launch wrappers of the sm_100a kernels (internal to libsa_cuda.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+// ---- radix.cu
+uint32_t sa_onesweep_tile_items();
+cudaError_t sa_launch_hist(const uint64_t* keys, uint32_t n, int shift0, int npasses, uint32_t* hist,
+                           int num_sms, cudaStream_t s);
+cudaError_t sa_launch_scan_hist(const uint32_t* hist, uint32_t n, int npasses, uint32_t* base, uint32_t* skip,
+                                cudaStream_t s);
+cudaError_t sa_launch_onesweep(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                               uint32_t* vals_out, uint32_t n, int shift, const uint32_t* digit_base,
+                               uint32_t* status, uint32_t* tile_counter, uint32_t* err, bool identity_vals,
+                               cudaStream_t s);
+
+// ---- refine.cu
+constexpr uint32_t SA_SCAN_TILE = 4096;   // ranks per block in the group analysis / compaction kernels
+cudaError_t sa_launch_iota(uint32_t* out, uint32_t n, cudaStream_t s);
+cudaError_t sa_launch_lowercase(uint8_t* text, uint64_t n, cudaStream_t s);
+cudaError_t sa_launch_pack0(const uint8_t* text, uint32_t n, int cb, uint64_t* keys, cudaStream_t s);
+cudaError_t sa_launch_lcp0(const uint64_t* sorted_keys, uint32_t n, int cb, uint32_t lprime, uint16_t* lcp,
+                           cudaStream_t s);
+// tie bit r = (lcp[r] == depth); the mask has one zero word in front (bit r lives at bit r+32)
+cudaError_t sa_launch_tie_mask(const uint16_t* lcp, uint32_t n, uint32_t depth, uint32_t* tie_words,
+                               uint32_t num_words, cudaStream_t s);
+// amask: ranks in tied groups of more than 32 members; hmask: first rank of each such group;
+// counts[2*tile], counts[2*tile+1]: per-tile popcounts (tile = SA_SCAN_TILE ranks)
+cudaError_t sa_launch_group_flags(const uint32_t* tie_words, uint32_t nwords_data, uint32_t* amask,
+                                  uint32_t* hmask, uint32_t* counts, cudaStream_t s);
+// exclusive scan of `num` (a,b) pairs in place; totals[0..1] = sums
+cudaError_t sa_launch_scan_pairs(uint32_t* counts, uint32_t num, uint32_t* totals, cudaStream_t s);
+cudaError_t sa_launch_compact_gather(const uint32_t* amask, const uint32_t* hmask, uint32_t nwords_data,
+                                     const uint32_t* tile_offsets, const uint32_t* sa, const uint8_t* text,
+                                     uint32_t depth, int cb, int gbits, uint32_t* slots, uint64_t* ckeys,
+                                     uint32_t* cvals, cudaStream_t s);
+cudaError_t sa_launch_writeback(const uint32_t* slots, const uint64_t* ckeys, const uint32_t* cvals, uint32_t m,
+                                uint32_t depth, int cb, int gbits, uint32_t lprime, uint32_t* sa, uint16_t* lcp,
+                                cudaStream_t s);
+
+// ---- finish.cu
+cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,
+                             uint32_t lprime, uint32_t* sa_out, unsigned long long* run_counter, uint32_t* err,
+                             cudaStream_t s);
+
+// ---- query.cu
+uint32_t sa_newline_tiles(uint32_t n);
+cudaError_t sa_launch_newline_count(const uint8_t* text, uint32_t n, uint32_t* counts, cudaStream_t s);
+cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, cudaStream_t s);
+cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint32_t* tile_offsets,
+                                    uint32_t* nlpos, cudaStream_t s);
+cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa, uint32_t n, uint32_t max_suffix_length,
+                            const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
+                            uint32_t* end, cudaStream_t s);
+cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k,
+                                 uint32_t* counts, cudaStream_t s);
+// exclusive scan of u32 counts into u64 offsets (off[num] = total)
+cudaError_t sa_launch_scan_u32_to_u64(const uint32_t* counts, uint32_t num, uint64_t* off, uint32_t* block_sums,
+                                      cudaStream_t s);
+cudaError_t sa_launch_hits(const uint32_t* sa, const uint32_t* start, const uint64_t* hit_off, uint32_t nq,
+                           const uint32_t* nlpos, uint32_t num_nl, uint32_t* hit_pos, uint32_t* hit_doc,
+                           cudaStream_t s);
+cudaError_t sa_launch_remap(const uint32_t* sa, uint32_t n, const uint32_t* map, const uint8_t* quoted_by_text,
+                            uint32_t* sa_out, uint32_t* quoted_bits_by_rank, cudaStream_t s);

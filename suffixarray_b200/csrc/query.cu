@@ -1,0 +1,387 @@
+// query.cu -- batched substring query, hit expansion, document table, CSV remap (sm_100a).
+//
+// query_kernel restates get_substring_positions (engine.c:869-918) for a batch: 8 lanes per
+// query, each lane compares 8 bytes of the <= L-byte window per probe; both bisections follow
+// the reference's probe sequence mid = (first + last) / 2 exactly (the SA is only "sorted
+// enough", so an equivalent lower_bound would not be bit-exact) and run interleaved so two
+// dependent load chains are in flight per query.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace sa {
+
+// ------------------------------------------------------------------------------ scans
+// single block, in-place exclusive scan of u32; *total = sum
+__global__ void __launch_bounds__(1024) scan_u32_kernel(uint32_t* __restrict__ c, uint32_t num,
+                                                        uint32_t* __restrict__ total)
+{
+    __shared__ uint32_t ws[32];
+    __shared__ uint32_t carry;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < num; base += 1024) {
+        const uint32_t i = base + t;
+        const uint32_t a = (i < num) ? c[i] : 0u;
+        uint32_t ia = a;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, ia, o);
+            if (lane >= o) ia += y;
+        }
+        if (lane == 31) ws[warp] = ia;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t v = ws[lane], s2 = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t y = __shfl_up_sync(0xffffffffu, s2, o);
+                if (lane >= o) s2 += y;
+            }
+            ws[lane] = s2 - v;
+        }
+        __syncthreads();
+        const uint32_t ea = carry + ws[warp] + ia - a;
+        if (i < num) c[i] = ea;
+        __syncthreads();
+        if (t == 1023) carry = ea + a;
+        __syncthreads();
+    }
+    if (t == 0) *total = carry;
+}
+
+// u32 counts -> u64 exclusive offsets, three small kernels
+__global__ void __launch_bounds__(1024) block_sum_kernel(const uint32_t* __restrict__ c, uint32_t num,
+                                                         unsigned long long* __restrict__ sums)
+{
+    __shared__ unsigned long long ws[32];
+    const uint32_t i = blockIdx.x * 1024 + threadIdx.x;
+    unsigned long long v = (i < num) ? c[i] : 0ull;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        v = ws[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (threadIdx.x == 0) sums[blockIdx.x] = v;
+    }
+}
+
+__global__ void scan_u64_serial_kernel(unsigned long long* __restrict__ sums, uint32_t num)
+{
+    // num = ceil(nq / 1024) block sums: a warp-strided serial scan is plenty
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long acc = 0;
+    for (uint32_t i = 0; i < num; ++i) { unsigned long long v = sums[i]; sums[i] = acc; acc += v; }
+    sums[num] = acc;
+}
+
+__global__ void __launch_bounds__(1024) offsets_kernel(const uint32_t* __restrict__ c, uint32_t num,
+                                                       const unsigned long long* __restrict__ sums,
+                                                       uint32_t nblocks, uint64_t* __restrict__ off)
+{
+    __shared__ unsigned long long ws[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t i = blockIdx.x * 1024 + t;
+    const unsigned long long a = (i < num) ? c[i] : 0ull;
+    unsigned long long ia = a;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long y = __shfl_up_sync(0xffffffffu, ia, o);
+        if (lane >= o) ia += y;
+    }
+    if (lane == 31) ws[warp] = ia;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long v = ws[lane], s2 = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long y = __shfl_up_sync(0xffffffffu, s2, o);
+            if (lane >= o) s2 += y;
+        }
+        ws[lane] = s2 - v;
+    }
+    __syncthreads();
+    if (i < num) off[i] = sums[blockIdx.x] + ws[warp] + ia - a;
+    if (i == 0) off[num] = sums[nblocks];
+}
+
+// ------------------------------------------------------------------------------ document table
+constexpr int NL_TILE = 4096;   // bytes per block, 16 per thread
+
+__device__ __forceinline__ uint32_t count_nl16(uint4 v)
+{
+    const uint64_t a = ((uint64_t)v.y << 32) | v.x, b = ((uint64_t)v.w << 32) | v.z;
+    return __popcll(zero_bytes(a ^ 0x0A0A0A0A0A0A0A0Aull)) + __popcll(zero_bytes(b ^ 0x0A0A0A0A0A0A0A0Aull));
+}
+
+__global__ void __launch_bounds__(256) newline_count_kernel(const uint4* __restrict__ text16, uint32_t n,
+                                                            uint32_t* __restrict__ counts)
+{
+    __shared__ uint32_t ws[8];
+    const uint64_t byte0 = (uint64_t)blockIdx.x * NL_TILE + threadIdx.x * 16;
+    uint32_t c = 0;
+    if (byte0 < n) c = count_nl16(text16[byte0 >> 4]);     // bytes past n are zero padding
+#pragma unroll
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int i = 0; i < 8; ++i) t += ws[i];
+        counts[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(256) newline_write_kernel(const uint4* __restrict__ text16, uint32_t n,
+                                                            const uint32_t* __restrict__ tile_offsets,
+                                                            uint32_t* __restrict__ nlpos)
+{
+    __shared__ uint32_t ws[8];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint64_t byte0 = (uint64_t)blockIdx.x * NL_TILE + t * 16;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (byte0 < n) v = text16[byte0 >> 4];
+    const uint32_t c = count_nl16(v);
+    uint32_t inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += y;
+    }
+    if (lane == 31) ws[warp] = inc;
+    __syncthreads();
+    uint32_t pre = tile_offsets[blockIdx.x];
+    for (int w = 0; w < warp; ++w) pre += ws[w];
+    uint32_t o = pre + inc - c;
+    if (c) {
+        const uint8_t* b = reinterpret_cast<const uint8_t*>(&v);
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if (b[i] == '\n') nlpos[o++] = (uint32_t)(byte0 + i);
+    }
+}
+
+// ------------------------------------------------------------------------------ query
+__device__ __forceinline__ uint64_t load_query_word(const uint8_t* __restrict__ q, uint32_t off, uint32_t c)
+{
+    // bytes [off, off+8) of the query, big-endian, zero past c
+    uint64_t w = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        uint32_t x = (off + i < c) ? q[off + i] : 0u;
+        w = (w << 8) | x;
+    }
+    return w;
+}
+
+// sign of strncmp(text + pos, q, c) computed by the 8 lanes of a group.
+__device__ __forceinline__ int group_compare(const uint8_t* __restrict__ text, uint32_t pos,
+                                             const uint8_t* __restrict__ q, uint32_t c, uint64_t qw0,
+                                             uint32_t gmask, int sub, int gshift)
+{
+    for (uint32_t cbase = 0; cbase < c; cbase += 64) {
+        const uint32_t off = cbase + 8u * sub;
+        uint64_t tw = 0, qw = 0;
+        if (off < c) {
+            const uint32_t nb = (c - off) < 8u ? (c - off) : 8u;
+            tw = keep_top_bytes(load_be64(text, (uint64_t)pos + off), (int)nb);
+            qw = cbase ? load_query_word(q, off, c) : qw0;
+        }
+        const uint32_t bal = (__ballot_sync(gmask, tw != qw) >> gshift) & 0xFFu;
+        if (bal) {
+            const int src = gshift + __ffs((int)bal) - 1;
+            const uint64_t t2 = __shfl_sync(gmask, tw, src), q2 = __shfl_sync(gmask, qw, src);
+            return t2 < q2 ? -1 : 1;
+        }
+    }
+    return 0;
+}
+
+__global__ void __launch_bounds__(256)
+query_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, uint32_t n, uint32_t L,
+             const uint8_t* __restrict__ qbytes, const uint64_t* __restrict__ qoff, uint32_t nq,
+             uint32_t* __restrict__ start_out, uint32_t* __restrict__ end_out)
+{
+    const uint32_t gq = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    if (gq >= nq) return;
+    const int lane = threadIdx.x & 31, sub = lane & 7, gshift = lane & 24;
+    const uint32_t gmask = 0xFFu << gshift;
+    const uint64_t qb = qoff[gq];
+    const uint32_t len = (uint32_t)(qoff[gq + 1] - qb);
+    const uint8_t* q = qbytes + qb;
+    // strlen (engine.c:874): cut at the first NUL
+    uint32_t m = len;
+    for (uint32_t cbase = 0; cbase < len; cbase += 64) {
+        const uint32_t off = cbase + 8u * sub;
+        uint32_t first_zero = 8;
+#pragma unroll
+        for (int i = 7; i >= 0; --i)
+            if (off + i < len && q[off + i] == 0) first_zero = i;
+        const uint32_t bal = (__ballot_sync(gmask, first_zero < 8) >> gshift) & 0xFFu;
+        if (bal) {
+            const int src = gshift + __ffs((int)bal) - 1;
+            const uint32_t fz = __shfl_sync(gmask, first_zero, src);
+            m = cbase + 8u * (uint32_t)(src - gshift) + fz;
+            break;
+        }
+    }
+    const uint32_t c = m < L ? m : L;                               // engine.c:881 (L, not L')
+    const uint64_t qw0 = load_query_word(q, 8u * sub, c);
+
+    uint32_t start = 0xFFFFFFFFu, end = 0xFFFFFFFFu;
+    int64_t f1 = 0, l1 = (int64_t)n - 1, f2 = 0, l2 = (int64_t)n - 1;
+    while (f1 <= l1 || f2 <= l2) {
+        const bool a1 = f1 <= l1, a2 = f2 <= l2;
+        const int64_t m1 = (f1 + l1) / 2, m2 = (f2 + l2) / 2;
+        const uint32_t p1 = a1 ? __ldg(sa + m1) : 0u;
+        const uint32_t p2 = a2 ? ((a1 && m2 == m1) ? p1 : __ldg(sa + m2)) : 0u;
+        if (a1) {
+            const int cmp = group_compare(text, p1, q, c, qw0, gmask, sub, gshift);
+            if (cmp < 0) f1 = m1 + 1;                               // engine.c:887-893
+            else { l1 = m1 - 1; start = (uint32_t)m1; }
+            if (a2 && m2 == m1) {
+                if (cmp > 0) l2 = m2 - 1; else { f2 = m2 + 1; end = (uint32_t)m2; }
+                continue;
+            }
+        }
+        if (a2) {
+            const int cmp = group_compare(text, p2, q, c, qw0, gmask, sub, gshift);
+            if (cmp > 0) l2 = m2 - 1;                               // engine.c:904-913
+            else { f2 = m2 + 1; end = (uint32_t)m2; }
+        }
+    }
+    if (start == 0xFFFFFFFFu) end = 0xFFFFFFFFu;                    // engine.c:896-899
+    if (sub == 0) { start_out[gq] = start; end_out[gq] = end; }
+}
+
+// engine.c:1181-1185: first == UINT32_MAX -> 0 hits, else min(k, second - first + 1) in u32
+__global__ void hit_counts_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end,
+                                  uint32_t nq, uint32_t k, uint32_t* __restrict__ counts)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    uint32_t s = start[i], c = 0;
+    if (s != 0xFFFFFFFFu) { c = end[i] - s + 1u; if (c > k) c = k; }
+    counts[i] = c;
+}
+
+// one warp per query: rank -> text position -> record index (# of '\n' before the position)
+__global__ void __launch_bounds__(256)
+hits_kernel(const uint32_t* __restrict__ sa, const uint32_t* __restrict__ start,
+            const uint64_t* __restrict__ hit_off, uint32_t nq, const uint32_t* __restrict__ nlpos,
+            uint32_t num_nl, uint32_t* __restrict__ hit_pos, uint32_t* __restrict__ hit_doc)
+{
+    const uint32_t wq = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (wq >= nq) return;
+    const uint64_t o = hit_off[wq];
+    const uint32_t take = (uint32_t)(hit_off[wq + 1] - o);
+    const uint32_t s = start[wq];
+    for (uint32_t j = threadIdx.x & 31; j < take; j += 32) {
+        const uint32_t p = sa[(uint64_t)s + j];
+        uint32_t lo = 0, hi = num_nl;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(nlpos + mid) < p) lo = mid + 1; else hi = mid;
+        }
+        if (hit_pos) hit_pos[o + j] = p;
+        if (hit_doc) hit_doc[o + j] = lo;
+    }
+}
+
+// engine.c:632-651: quoted bit of rank i = flag of text byte SA[i]; SA[i] = map[SA[i]]
+__global__ void remap_kernel(const uint32_t* __restrict__ sa, uint32_t n, const uint32_t* __restrict__ map,
+                             const uint8_t* __restrict__ quoted_by_text, uint32_t* __restrict__ sa_out,
+                             uint32_t* __restrict__ qbits)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool qd = false;
+    if (i < n) {
+        const uint32_t p = sa[i];
+        qd = quoted_by_text[p] != 0;
+        sa_out[i] = map[p];
+    }
+    const uint32_t b = __ballot_sync(0xffffffffu, qd);
+    if ((threadIdx.x & 31) == 0 && (i >> 5) < ((n + 31) >> 5)) qbits[i >> 5] = b;
+}
+
+}  // namespace sa
+
+// ------------------------------------------------------------------------------ launchers
+cudaError_t sa_launch_newline_count(const uint8_t* text, uint32_t n, uint32_t* counts, cudaStream_t s)
+{
+    const uint32_t tiles = (n + sa::NL_TILE - 1) / sa::NL_TILE;
+    if (!tiles) return cudaSuccess;
+    sa::newline_count_kernel<<<tiles, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), n, counts);
+    return cudaGetLastError();
+}
+
+uint32_t sa_newline_tiles(uint32_t n) { return (n + sa::NL_TILE - 1) / sa::NL_TILE; }
+
+cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, cudaStream_t s)
+{
+    sa::scan_u32_kernel<<<1, 1024, 0, s>>>(counts, num, total);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint32_t* tile_offsets, uint32_t* nlpos,
+                                    cudaStream_t s)
+{
+    const uint32_t tiles = (n + sa::NL_TILE - 1) / sa::NL_TILE;
+    if (!tiles) return cudaSuccess;
+    sa::newline_write_kernel<<<tiles, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), n, tile_offsets, nlpos);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa_, uint32_t n, uint32_t max_suffix_length,
+                            const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
+                            uint32_t* end, cudaStream_t s)
+{
+    if (!nq) return cudaSuccess;
+    const uint64_t threads = (uint64_t)nq * 8;
+    sa::query_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(text, sa_, n, max_suffix_length, qbytes, qoff,
+                                                                      nq, start, end);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k,
+                                 uint32_t* counts, cudaStream_t s)
+{
+    if (!nq) return cudaSuccess;
+    sa::hit_counts_kernel<<<(nq + 255) / 256, 256, 0, s>>>(start, end, nq, k, counts);
+    return cudaGetLastError();
+}
+
+// block_sums must hold ceil(num/1024) + 1 u64 entries
+cudaError_t sa_launch_scan_u32_to_u64(const uint32_t* counts, uint32_t num, uint64_t* off, uint32_t* block_sums,
+                                      cudaStream_t s)
+{
+    unsigned long long* sums = reinterpret_cast<unsigned long long*>(block_sums);
+    const uint32_t nb = (num + 1023) / 1024;
+    if (!num) return cudaMemsetAsync(off, 0, sizeof(uint64_t), s);
+    sa::block_sum_kernel<<<nb, 1024, 0, s>>>(counts, num, sums);
+    sa::scan_u64_serial_kernel<<<1, 32, 0, s>>>(sums, nb);
+    sa::offsets_kernel<<<nb, 1024, 0, s>>>(counts, num, sums, nb, off);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_hits(const uint32_t* sa_, const uint32_t* start, const uint64_t* hit_off, uint32_t nq,
+                           const uint32_t* nlpos, uint32_t num_nl, uint32_t* hit_pos, uint32_t* hit_doc,
+                           cudaStream_t s)
+{
+    if (!nq) return cudaSuccess;
+    const uint64_t threads = (uint64_t)nq * 32;
+    sa::hits_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(sa_, start, hit_off, nq, nlpos, num_nl, hit_pos,
+                                                                     hit_doc);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_remap(const uint32_t* sa_, uint32_t n, const uint32_t* map, const uint8_t* quoted_by_text,
+                            uint32_t* sa_out, uint32_t* quoted_bits_by_rank, cudaStream_t s)
+{
+    if (!n) return cudaSuccess;
+    sa::remap_kernel<<<(n + 255) / 256, 256, 0, s>>>(sa_, n, map, quoted_by_text, sa_out, quoted_bits_by_rank);
+    return cudaGetLastError();
+}

@@ -1,0 +1,127 @@
+// sa_index.h -- the opaque handle behind sa_cuda.h and small host utilities.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/sa_cuda.h"
+#include "common.cuh"
+#include "kernels.h"
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap && p) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        if (bytes == 0) bytes = 256;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// layout of the small device scratch block (u32 words)
+enum SmallSlot : uint32_t {
+    SM_HIST = 0,            // 8*256
+    SM_BASE = 2048,         // 8*256
+    SM_SKIP = 4096,         // 8
+    SM_TOTALS = 4104,       // 2
+    SM_TILECTR = 4106,      // 1
+    SM_ERR = 4107,          // 1
+    SM_RUNCTR = 4108,       // 2 (u64, 8-byte aligned)
+    SM_NLTOTAL = 4110,      // 1
+    SM_WORDS = 4112
+};
+
+struct PhaseTimer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    float* target = nullptr;
+};
+
+struct sa_index {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    uint32_t L = 0;
+    uint64_t n = 0;
+    uint32_t lprime = 0;
+    bool built = false;
+    bool csv = false;
+    std::mutex mu;
+
+    // persistent after a build
+    DevBuf text;        // n + SA_TEXT_PAD bytes, zero padded
+    DevBuf sa_final;    // u32[n] text positions in ORDER-E
+    DevBuf nlpos;       // u32[num_nl] positions of '\n'
+    uint32_t num_nl = 0;
+    DevBuf sa_file;     // CSV: u32[n] file offsets (engine.c:647-651)
+    DevBuf qbits;       // CSV: quoted bit per rank
+    DevBuf map, quoted_text;   // CSV feeder outputs on the device
+
+    // build scratch (kept between builds so repeated builds do not re-allocate)
+    DevBuf keys[2], vals[2], aux[2], lcp, tie, amask, hmask, counts, status, small, nl_counts;
+
+    // query scratch / results of the last batch
+    DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
+    uint64_t last_nq = 0, last_total_hits = 0;
+    bool have_ranges = false;
+
+    uint32_t* h_small = nullptr;   // pinned mirror for tiny read-backs (64 words)
+
+    sa_stats stats{};
+    std::vector<PhaseTimer> timers;
+    std::vector<cudaEvent_t> event_pool;
+    size_t events_used = 0;
+    bool timing = false;
+
+    // debug knobs (sa_debug_set)
+    int64_t dbg_max_rounds = -1;    // stop refining after this many rounds (-1: no limit)
+    int64_t dbg_skip_finish = 0;    // leave the phase-1 order (no <=32 bucket step)
+    int64_t dbg_force_gbits = 0;    // use at least this many group-id bits (exercises small cb)
+};
+
+void sa_set_error(const char* fmt, ...);
+int sa_cuda_fail(cudaError_t e, const char* what);
+
+#define SA_CU(call)                                             \
+    do {                                                        \
+        cudaError_t e__ = (call);                               \
+        if (e__ != cudaSuccess) return sa_cuda_fail(e__, #call); \
+    } while (0)
+
+// phase timing (no-ops unless SA_FLAG_TIMING): a ScopedPhase records two events on the index
+// stream; sa_time_collect() synchronises and adds the elapsed times to their targets.
+cudaEvent_t sa_take_event(sa_index* idx);
+void sa_time_collect(sa_index* idx);
+
+struct ScopedPhase {
+    sa_index* idx;
+    cudaEvent_t a = nullptr, b = nullptr;
+    float* target;
+    ScopedPhase(sa_index* i, float* tgt) : idx(i), target(tgt)
+    {
+        if (!idx->timing) return;
+        a = sa_take_event(idx);
+        b = sa_take_event(idx);
+        cudaEventRecord(a, idx->stream);
+    }
+    ~ScopedPhase()
+    {
+        if (!idx->timing) return;
+        cudaEventRecord(b, idx->stream);
+        idx->timers.push_back(PhaseTimer{a, b, target});
+    }
+};
+
+int sa_build_resident(sa_index* idx, uint32_t flags);

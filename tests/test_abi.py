@@ -1,0 +1,66 @@
+"""The C-ABI library loads on a machine without a GPU and exports every symbol that
+include/sa_cuda.h declares; with no device every entry point fails loudly (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, _cuda_available
+from suffixarray_b200 import _lib as S
+
+HEADER = os.path.join(ROOT, "include", "sa_cuda.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(sa_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_are_exported():
+    lib = ctypes.CDLL(S.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in sa_cuda.h but not exported"
+    assert sorted(S.EXPORTS) == names
+
+
+def test_abi_version():
+    assert S.lib().sa_abi_version() == 1
+
+
+def test_stats_struct_matches_header():
+    src = open(HEADER).read()
+    body = re.search(r"typedef struct sa_stats \{(.*?)\} sa_stats;", src, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    fields = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        typ, names = decl.split(None, 1)
+        fields += [(n.strip(), typ) for n in names.split(",")]
+    ctype = {"uint64_t": ctypes.c_uint64, "uint32_t": ctypes.c_uint32, "float": ctypes.c_float}
+    assert [(n, ctype[t]) for n, t in fields] == list(S.SaStats._fields_)
+
+
+@pytest.mark.skipif(_cuda_available(), reason="checks the no-GPU failure mode")
+def test_fails_loudly_without_gpu():
+    with pytest.raises(S.SaCudaError) as ei:
+        S.Index(32)
+    assert ei.value.code == -3 and "no CPU fallback" in str(ei.value)
+
+
+def test_invalid_arguments_do_not_crash():
+    L = S.lib()
+    assert L.sa_create(None, 32, 0) == -1
+    h = ctypes.c_void_p()
+    assert L.sa_create(ctypes.byref(h), 5000, 0) == -5
+    assert L.sa_size(None) == 0
+    assert L.sa_num_docs(None) == 0
+    L.sa_destroy(None)
+    out = np.zeros(4, np.uint32)
+    assert L.sa_copy_sa_u32(None, out.ctypes.data_as(ctypes.c_void_p), 4) == -1

@@ -1,0 +1,101 @@
+"""Pins the oracle (oracle/sa_oracle.c) against the UNMODIFIED reference compiled into
+oracle/_ref/libsa_ref.so (oracle/Makefile; built from /root/reference where it lies).  The
+reference's own tests hold no golden vectors (tests/test.py has no asserts), so this side-by-side
+run plus tests/golden/ is what pins parity."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+
+from conftest import GRID_L, GRID_N, GRID_SIGMA, random_text, safe_queries_for
+from oracle import pyoracle as O
+from suffixarray_b200 import workloads as W
+
+needs_ref = pytest.mark.skipif(not O.have_ref(), reason="oracle/_ref/libsa_ref.so not built (no /root/reference)")
+
+
+@needs_ref
+@pytest.mark.parametrize("sigma", GRID_SIGMA)
+def test_build_grid(sigma):
+    rng = np.random.default_rng(sigma)
+    for n in GRID_N:
+        for L in GRID_L:
+            t = random_text(rng, n, sigma)
+            assert np.array_equal(O.oracle_build(t, L), O.ref_build(t, L)), (n, sigma, L)
+
+
+@needs_ref
+def test_build_edge_texts():
+    rng = np.random.default_rng(3)
+    cases = [
+        np.full(3000, ord("a"), np.uint8), np.full(300, 10, np.uint8), np.full(300, 255, np.uint8),
+        np.tile(np.frombuffer(b"abcabcabd\n", np.uint8), 300),
+        rng.integers(1, 256, 5000).astype(np.uint8),
+        np.frombuffer("naïve café\nüber straße\n日本語\n".encode() * 30, np.uint8),
+        np.frombuffer(b"\n\n\nab\n\n\nab\n\n" * 20, np.uint8),
+    ]
+    for t in cases:
+        for L in (1, 8, 9, 16, 17, 32, 64):
+            assert np.array_equal(O.oracle_build(t, L), O.ref_build(t, L)), L
+
+
+@needs_ref
+def test_build_company_names():
+    text, _ = W.company_names_joined(50_000, seed=41, upper=False)
+    for L in (8, 32, 64):
+        assert np.array_equal(O.oracle_build(text, L), O.ref_build(text, L))
+
+
+@needs_ref
+@pytest.mark.parametrize("sigma,L", [(2, 8), (3, 16), (8, 32), (26, 32), (26, 64)])
+def test_query_matches_reference(sigma, L):
+    rng = np.random.default_rng(50 + sigma + L)
+    for n in (40, 500, 20000):
+        t = random_text(rng, n, sigma)
+        t[0] = 10
+        sa = O.ref_build(t, L)
+        qs = safe_queries_for(t, rng, 300, max_len=70)
+        s, e = O.oracle_query(t, sa, L, qs)
+        rs, re_, skipped = O.ref_query(t, sa, L, qs)
+        keep = skipped == 0
+        assert keep.sum() > 200
+        assert np.array_equal(s[keep], rs[keep]) and np.array_equal(e[keep], re_[keep])
+
+
+@needs_ref
+def test_csv_scan_and_remap_match_reference():
+    data = W.csv_file_bytes(3000, seed=43, quoted_fraction=0.2)
+    with tempfile.NamedTemporaryFile(suffix=".csv", delete=False) as f:
+        f.write(data)
+        path = f.name
+    try:
+        for col, name in enumerate(["id", "name", "city", "score"]):
+            text, mp, qd = O.oracle_csv_scan(data, col, 4)
+            sa = O.oracle_build(text, 32)
+            sa_file, q_rank = O.oracle_csv_remap(sa, mp, qd)
+            rsa, rq = O.ref_csv_build(path, name, 32, cap=len(data) + 16)
+            assert rsa.size == text.size, name
+            assert np.array_equal(sa_file, rsa), name
+            assert np.array_equal(q_rank, rq), name
+    finally:
+        os.unlink(path)
+
+
+def test_hits_are_first_k_in_rank_order():
+    text = np.frombuffer(b"\nabab abab\nabab\nxx", np.uint8)
+    sa = O.oracle_build(text, 32)
+    s, e = O.oracle_query(text, sa, 32, [b"ab", b"zz", b"xx"])
+    off, pos, doc = O.oracle_hits(text, sa, s, e, 3)
+    assert off.tolist() == [0, 3, 3, 4]
+    assert pos[:3].tolist() == sa[s[0]:s[0] + 3].tolist()
+    assert doc[3] == 3
+
+
+def test_known_answer_banana():
+    # produced by the reference itself during the survey
+    t = np.frombuffer(b"banana\nbandana", np.uint8)
+    sa = O.oracle_build(t, 32)
+    assert sa.tolist() == [6, 13, 5, 11, 3, 1, 8, 0, 7, 10, 12, 4, 2, 9]
+    s, e = O.oracle_query(t, sa, 32, [b"ana", b"ban"])
+    assert (s.tolist(), e.tolist()) == ([3, 7], [5, 8])
