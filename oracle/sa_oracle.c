@@ -362,9 +362,13 @@ uint64_t sao_csv_scan(const uint8_t* file, uint64_t size, uint32_t column_idx, u
 void sao_csv_remap(uint32_t* sa, uint64_t n, const uint32_t* map, const uint8_t* quoted_by_text,
                    uint8_t* quoted_by_rank)
 {
+    /* copy_buffer_bit (engine.c:256-261) copies buffer_bit_idx / 8 whole bytes into a zeroed
+     * buffer, so the flags of the last n % 8 text bytes read back as 0 in the permutation loop
+     * (engine.c:632-645). */
+    const uint64_t copied = n & ~(uint64_t)7;
     for (uint64_t i = 0; i < n; ++i) {
         uint32_t p = sa[i];
-        quoted_by_rank[i] = quoted_by_text[p];
+        quoted_by_rank[i] = (p < copied) ? quoted_by_text[p] : 0;
         sa[i] = map[p];
     }
 }

@@ -300,7 +300,9 @@ __global__ void remap_kernel(const uint32_t* __restrict__ sa, uint32_t n, const 
     bool qd = false;
     if (i < n) {
         const uint32_t p = sa[i];
-        qd = quoted_by_text[p] != 0;
+        // copy_buffer_bit (engine.c:256-261) copies only n / 8 whole bytes of the flags, so the
+        // last n % 8 text bytes read as "not quoted" in the reference's permutation loop
+        qd = (p < (n & ~7u)) && quoted_by_text[p] != 0;
         sa_out[i] = map[p];
     }
     const uint32_t b = __ballot_sync(0xffffffffu, qd);
