@@ -1,0 +1,445 @@
+#!/usr/bin/env python
+"""bench.py -- SA build Mchars/s + batched substring queries/s (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1]
+
+A "step" is one pass of the hot path over one batch of synthetic input: build the truncated
+suffix array of the workload text (max_suffix_length = 32) and answer the workload's query batch
+(ranges + hit lists).  Default workload = BASELINE.json configs[1]: a 100 M-char synthetic
+English document list + a 1 M-query batch.
+
+* `value`   : build Mchars/s with the text already resident in HBM (device-timed, CUDA events on
+              the library's stream, max over ranks).  `queries_per_s` is the query half of the
+              metric on the same footing (query batch resident in HBM).
+* `e2e`     : the same two numbers through the C-ABI calls a user of the drop-in makes
+              (sa_build_text / sa_query_ranges / sa_query_hits) with PINNED HOST buffers, the
+              host->device and device->host copies inside the timed region.
+* `roofline`: the dominant kernel (onesweep radix scatter pass): algorithmic bytes per launch
+              (24 B per record moved: read 8+4, write 8+4) / average launch time, against the
+              measured HBM copy peak in MEASURED_PEAKS.json.
+* `cpu_baseline`: the reference's own engine.c (oracle/_ref/libsa_ref.so, built from
+              /root/reference in the authoring container) timed on the host cores, rank 0, N = 1.
+
+N > 1 (torchrun, one process per GPU): the reference partitions a large text into independent
+sub-indexes (suffix_array.pyx:148-180); each rank builds and queries its own partition of the
+same size (weak scaling, no data-path collective).  Aggregation of the times is a
+torch.distributed all-reduce(MAX) over NCCL.
+
+`--impl reference` times the reference CPU path on a bounded sample, rank 0 only.
+The oracle/ directory is used here ONLY for the cpu_baseline / reference arm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "SA build Mchars/s and batched substring queries/s at 1/2/4/8 B200 vs CPU"
+L_DEFAULT = 32
+K_HITS = 1000
+
+WORKLOADS = {
+    # name: (text chars, queries, description)
+    "c2": (100_000_000, 1_000_000, "100M-char synthetic English document list, max_suffix_length=32, 1M-query batch"),
+    "c1": (0, 10_000, "1M synthetic company-name strings, max_suffix_length=32, 10k whole-name queries"),
+    "small": (4_000_000, 50_000, "4M-char synthetic English (debug size)"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--max-suffix-length", type=int, default=L_DEFAULT)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def make_workload(name: str, rank: int):
+    """-> (text u8, qbytes u8, qoff u64, needs_lowercase).  Seeds follow SURVEY 8(d); rank r of a
+    multi-GPU run gets its own partition (seed + r)."""
+    from suffixarray_b200 import workloads as W
+    n_chars, nq, _ = WORKLOADS[name]
+    if name == "c1":
+        text, starts = W.company_names_joined(1_000_000, seed=1001 + rank, upper=True)
+        qs = W.whole_name_queries(text, starts, nq, seed=1002 + rank)
+        lens = np.fromiter((len(q) for q in qs), dtype=np.uint64, count=len(qs))
+        qoff = np.zeros(len(qs) + 1, dtype=np.uint64)
+        np.cumsum(lens, out=qoff[1:])
+        qbytes = np.frombuffer(b"".join(qs), dtype=np.uint8).copy()
+        return text, qbytes, qoff, True
+    text = W.english_documents(n_chars, seed=2001 + rank)
+    qbytes, qoff = W.substring_queries(text, nq, seed=2002 + rank)
+    return text, qbytes, qoff, False
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def load_ncu_traffic():
+    """Per-launch DRAM bytes of the onesweep kernel from the committed `ncu --set full` capture
+    (profiles/ncu_traffic.json, written by profiles/summarise.py); None when absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one process per GPU)")
+    return world, rank, local
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from suffixarray_b200 import _lib as S
+
+    world, rank, local = dist_setup(args)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (libsa_cuda has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    S.lib()   # fail loudly when the extension is missing
+    L = args.max_suffix_length
+
+    text, qbytes, qoff, lower = make_workload(args.workload, rank)
+    n, nq = int(text.size), int(qoff.size - 1)
+    flags_dev = S.SA_FLAG_TIMING | (S.SA_FLAG_LOWERCASE if lower else 0)
+    flags_e2e = S.SA_FLAG_LOWERCASE if lower else 0
+
+    # pinned host staging (the e2e leg copies from / into these inside the timed region)
+    h_text = torch.from_numpy(text).pin_memory()
+    h_q = torch.from_numpy(qbytes).pin_memory()
+    h_qoff = torch.from_numpy(qoff.view(np.int64)).pin_memory()
+    h_start = torch.empty(nq, dtype=torch.int32, pin_memory=True)
+    h_end = torch.empty(nq, dtype=torch.int32, pin_memory=True)
+    h_hoff = torch.empty(nq + 1, dtype=torch.int64, pin_memory=True)
+    d_text = torch.from_numpy(text).cuda()          # the `value` leg starts with the text in HBM
+
+    idx_dev = S.Index(L, device=local)              # device-resident leg
+    idx_e2e = S.Index(L, device=local)              # host-buffer leg
+    lib = S.lib()
+    vp = S._vp
+
+    h_hits = {"pos": None, "doc": None, "cap": 0}
+
+    def ensure_hit_bufs(total):
+        if total > h_hits["cap"]:
+            cap = int(total * 1.1) + 1024
+            h_hits["pos"] = torch.empty(cap, dtype=torch.int32, pin_memory=True)
+            h_hits["doc"] = torch.empty(cap, dtype=torch.int32, pin_memory=True)
+            h_hits["cap"] = cap
+
+    def step():
+        r = {}
+        # ---- value leg: text resident in HBM, device-timed
+        idx_dev.build_text_device(d_text.data_ptr(), n, flags_dev)
+        st = idx_dev.stats()
+        r["build_dev_ms"] = st["ms_total"]
+        r["build_launches"] = st["kernel_launches"]
+        r["onesweep_ms"] = st["ms_onesweep_sum"]
+        r["onesweep_launches"] = st["radix_passes"]
+        r["onesweep_elems"] = st["onesweep_elems"]
+        r["phases"] = {k: round(st[k], 3) for k in ("ms_pack", "ms_hist", "ms_sort0", "ms_refine", "ms_finish",
+                                                       "ms_docs", "ms_onesweep_sum")}
+        r["rounds"] = st["rounds"]
+        # ---- e2e leg: host text in, index ready (H2D inside)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        idx_e2e.build_text_ptr(h_text.data_ptr(), n, flags_e2e | S.SA_FLAG_TIMING)
+        torch.cuda.synchronize()
+        r["build_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        r["build_launches"] += idx_e2e.stats()["kernel_launches"]
+        # ---- queries through the C ABI with host buffers; the library's CUDA events give the
+        #      device-only time of the same kernels
+        t0 = time.perf_counter()
+        S.check(lib.sa_query_ranges(idx_e2e._h, vp(h_q.data_ptr()), vp(h_qoff.data_ptr()), nq, K_HITS,
+                                    vp(h_start.data_ptr()), vp(h_end.data_ptr()), vp(h_hoff.data_ptr())))
+        total = int(h_hoff[nq])
+        ensure_hit_bufs(total)
+        S.check(lib.sa_query_hits(idx_e2e._h, vp(h_hits["pos"].data_ptr()), vp(h_hits["doc"].data_ptr()),
+                                  h_hits["cap"]))
+        torch.cuda.synchronize()
+        r["query_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        st = idx_e2e.stats()
+        r["query_dev_ms"] = st["ms_query"] + st["ms_hits"]
+        r["query_kernel_ms"] = st["ms_query"]
+        r["query_launches"] = st["kernel_launches"]
+        r["hits"] = total
+        return r
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ensure_hit_bufs(1 << 20)
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t_wall0 = time.perf_counter()
+    recs = [step() for _ in range(args.steps)]
+    barrier()
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+
+    K = args.steps
+    sums = torch.tensor([sum(r["build_dev_ms"] for r in recs), sum(r["query_dev_ms"] for r in recs),
+                         sum(r["build_e2e_ms"] for r in recs), sum(r["query_e2e_ms"] for r in recs), wall_ms],
+                        dtype=torch.float64, device="cuda")
+    counts = torch.tensor([float(n), float(nq)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(sums, op=dist.ReduceOp.MAX)     # max over ranks
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM)   # units all ranks processed per step
+    build_ms, query_ms, build_e2e_ms, query_e2e_ms, wall_ms = (sums / K).tolist()[:4] + [sums[4].item()]
+    n_all, nq_all = counts.tolist()
+    result = None
+    if rank == 0:
+        result = assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_e2e_ms, query_e2e_ms,
+                          wall_ms, clocks, qbytes.size, text, qbytes, qoff, lower)
+    idx_dev.close()
+    idx_e2e.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return result
+
+
+# ------------------------------------------------------------------------------ CPU reference legs
+def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample=200_000, threads=0):
+    """Times the reference's own CPU path (engine.c through oracle/_ref/libsa_ref.so when present,
+    else the oracle port) on the host cores.  -> dict."""
+    from oracle import pyoracle as O
+    nq_all = int(qoff.size - 1)
+    nqs = min(nq_all, query_sample)
+    low = O.oracle_lowercase(text) if lower else text
+    n = int(low.size)
+    kind = "reference" if O.have_ref() else "port"
+    cores = O.ref_max_threads() if kind == "reference" else 1
+    if kind == "reference":
+        tp = np.zeros(n + O.REF_PAD, dtype=np.uint8)
+        tp[:n] = low
+        sa = np.empty(n, dtype=np.uint32)
+        best = float("inf")
+        for _ in range(build_reps):
+            t0 = time.perf_counter()
+            O.ref_build_padded(tp, n, L, sa)
+            best = min(best, time.perf_counter() - t0)
+        # query sample: NUL-terminated C strings, an omp parallel-for over the batch
+        lens = (qoff[1:nqs + 1] - qoff[:nqs]).astype(np.int64)
+        zoff = np.zeros(nqs + 1, dtype=np.uint64)
+        np.cumsum(lens + 1, out=zoff[1:].view(np.int64))
+        zbytes = np.zeros(int(zoff[nqs]), dtype=np.uint8)
+        src = qbytes[: int(qoff[nqs])]
+        dst_idx = np.arange(src.size, dtype=np.int64) + np.repeat(np.arange(nqs, dtype=np.int64), lens)
+        zbytes[dst_idx] = src
+        start = np.empty(nqs, dtype=np.uint32)
+        end = np.empty(nqs, dtype=np.uint32)
+        skipped = np.zeros(nqs, dtype=np.uint8)
+        import ctypes as C
+        rl = O.ref_lib()
+        t0 = time.perf_counter()
+        rl.ref_query_batch(tp.ctypes.data, sa.ctypes.data_as(C.POINTER(C.c_uint32)), n, L, zbytes.ctypes.data,
+                           zoff.ctypes.data_as(C.POINTER(C.c_uint64)), nqs,
+                           start.ctypes.data_as(C.POINTER(C.c_uint32)), end.ctypes.data_as(C.POINTER(C.c_uint32)),
+                           skipped.ctypes.data_as(C.POINTER(C.c_uint8)), threads)
+        tq = time.perf_counter() - t0
+    else:
+        t0 = time.perf_counter()
+        sa = O.oracle_build(low, L)
+        best = time.perf_counter() - t0
+        from suffixarray_b200 import workloads as W
+        qs = W.unpack_queries(qbytes[: int(qoff[nqs])], qoff[: nqs + 1])
+        t0 = time.perf_counter()
+        O.oracle_query(low, sa, L, qs)
+        tq = time.perf_counter() - t0
+    return {"kind": kind, "cores": int(cores), "n": n, "build_s": best, "build_mchars_s": n / best / 1e6,
+            "query_sample": nqs, "query_s": tq, "queries_per_s": nqs / tq}
+
+
+def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_e2e_ms, query_e2e_ms, wall_ms,
+             clocks, qbytes_len, text, qbytes, qoff, lower):
+    K = args.steps
+    peak, peak_src = load_peaks()
+    os_ms = sum(r["onesweep_ms"] for r in recs)
+    os_launches = sum(r["onesweep_launches"] for r in recs)
+    os_elems = sum(r["onesweep_elems"] for r in recs)
+    os_bytes_per_launch = 24.0 * os_elems / max(os_launches, 1)
+    os_avg_ms = os_ms / max(os_launches, 1)
+    achieved = os_bytes_per_launch / (os_avg_ms * 1e-3) / 1e9 if os_avg_ms > 0 else 0.0
+    traffic = load_ncu_traffic()
+    hits = recs[-1]["hits"]
+    h2d = n + qbytes_len + (nq + 1) * 8
+    d2h = nq * 8 + (nq + 1) * 8 + hits * 8
+    out = {
+        "metric": METRIC,
+        "value": round(n_all / (build_ms * 1e-3) / 1e6, 2),
+        "unit": "Mchars/s (SA build)",
+        "queries_per_s": round(nq_all / (query_ms * 1e-3), 1),
+        "n_gpus": world, "steps": K, "warmup": args.warmup,
+        "ms_per_step": round(build_ms + query_ms, 3),
+        "build_ms_per_step": round(build_ms, 3), "query_ms_per_step": round(query_ms, 3),
+        "wall_ms_timed_region": round(wall_ms, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8 text / u64 keys / u32 positions (integer compare + scatter)",
+        "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload][2], "name": args.workload, "n_chars_per_gpu": n,
+                   "queries_per_gpu": nq, "max_suffix_length": args.max_suffix_length, "k": K_HITS,
+                   "hits_per_batch": hits, "sharding": "one independent partition per GPU (suffix_array.pyx:148-180)",
+                   "l2": "inputs larger than L2 (keys 8n + positions 4n = 1.2 GB per pass vs 126 MB L2)"},
+        "e2e": {"value": round(n_all / (build_e2e_ms * 1e-3) / 1e6, 2), "unit": "Mchars/s (SA build)",
+                "queries_per_s": round(nq_all / (query_e2e_ms * 1e-3), 1),
+                "build_ms": round(build_e2e_ms, 3), "query_ms": round(query_e2e_ms, 3),
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "api": "sa_build_text + sa_query_ranges + sa_query_hits (pinned host buffers)"},
+        "gpu_launches": int(sum(r["build_launches"] + r["query_launches"] for r in recs)),
+        "roofline": {"kernel": "onesweep_kernel (radix scatter pass)", "bound": "hbm",
+                     "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(achieved / peak, 4), "peak_source": peak_src,
+                     "bytes_per_launch": int(os_bytes_per_launch), "avg_launch_ms": round(os_avg_ms, 4),
+                     "launches_per_step": os_launches / K,
+                     "traffic": (traffic or {}).get("onesweep_kernel_bytes_per_launch")},
+        "roofline_build_model": {"bytes": 213 * n, "achieved": round(213.0 * n / (build_ms * 1e-3) / 1e9, 1),
+                                 "frac": round(213.0 * n / (build_ms * 1e-3) / 1e9 / peak, 4),
+                                 "note": "SURVEY 8(d) B_build = 213 n bytes over the whole device build"},
+        "phases_ms_last_step": recs[-1]["phases"],
+        "refine_rounds": recs[-1]["rounds"],
+        "query_kernel_ms": round(sum(r["query_kernel_ms"] for r in recs) / K, 3),
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cb = cpu_reference_times(text, qbytes, qoff, lower, args.max_suffix_length)
+        out["cpu_baseline"] = {"value": round(cb["build_mchars_s"], 2), "unit": "Mchars/s (SA build)",
+                               "queries_per_s": round(cb["queries_per_s"], 1), "cores": cb["cores"],
+                               "kind": cb["kind"],
+                               "sample": f"build: the full {cb['n']}-char text once ({cb['build_s']:.2f} s); "
+                                         f"queries: first {cb['query_sample']} of the batch ({cb['query_s']:.2f} s), "
+                                         "get_substring_positions under an omp parallel-for"}
+    return out
+
+
+def run_reference(args):
+    """The reference's own CPU implementation (engine.c) on the host cores: rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    text, qbytes, qoff, lower = make_workload(args.workload, 0)
+    # each step = one bounded sample: build over the first `sample_n` chars + 100k queries
+    sample_n = min(int(text.size), 50_000_000)
+    text = text[:sample_n]
+    nqs = min(int(qoff.size - 1), 100_000)
+    recs = []
+    for i in range(args.warmup + args.steps):
+        cb = cpu_reference_times(text, qbytes, qoff, lower, args.max_suffix_length, query_sample=nqs)
+        if i >= args.warmup:
+            recs.append(cb)
+    K = len(recs)
+    bs = sum(r["build_s"] for r in recs) / K
+    qs = sum(r["query_s"] for r in recs) / K
+    v = sample_n / bs / 1e6
+    return {"impl": "reference", "metric": METRIC, "value": round(v, 2), "unit": "Mchars/s (SA build)",
+            "queries_per_s": round(nqs / qs, 1), "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round((bs + qs) * 1e3, 2), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8 text / u32 positions", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][2], "name": args.workload,
+                       "max_suffix_length": args.max_suffix_length},
+            "cpu_baseline": {"value": round(v, 2), "unit": "Mchars/s (SA build)", "kind": recs[0]["kind"],
+                             "cores": recs[0]["cores"], "queries_per_s": round(nqs / qs, 1),
+                             "sample": f"per step: build over the first {sample_n} chars of the workload text + the "
+                                       f"first {nqs} queries of its batch (searched in that prefix)"},
+            "e2e": {"value": round(v, 2), "unit": "Mchars/s (SA build)", "queries_per_s": round(nqs / qs, 1),
+                    "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+
+
+def main():
+    args = parse_args()
+    res = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if res is not None:
+        print(json.dumps(res), flush=True)
+
+
+if __name__ == "__main__":
+    main()
