@@ -1,0 +1,165 @@
+"""Host-side mirror of the reference's Cython ``SuffixArray`` class, re-pointed at libsa_cuda.so.
+
+Same names, argument meaning and error behaviour as ``suffix_array/suffix_array.pyx:110-267``
+(the reference toolchain for this layer is Cython; the image has it, but the class holds no
+arithmetic of its own, so the mirror is plain Python over the C ABI -- INTEGRATION.md shows the
+``cdef extern from "sa_cuda.h"`` block a maintainer would drop into the .pyx instead):
+
+* ``SuffixArray(max_suffix_length=64)``                                  pyx:125
+* ``SuffixArray(documents=docs, max_suffix_length=32)``                  README.md:23
+* ``SuffixArray(csv_file=f, search_column=c, max_suffix_length=32)``     README.md:40-44
+* ``construct_truncated_suffix_array_documents(documents)``              pyx:129-180
+* ``construct_truncated_suffix_array_from_csv(filename, search_column)`` pyx:183-207
+* ``query_records(substring, k=1000)``                                   pyx:209-267
+* ``query_records_batch(substrings, k=1000)``  (new: the batched entry the GPU path wants)
+
+All index arithmetic (build, bisection, hit expansion, doc ids) runs in the CUDA library; this
+file only joins / encodes strings and turns (hit position, record id) pairs back into records.
+There is no CPU fallback: without the built library or a GPU every call raises.
+"""
+from __future__ import annotations
+
+import csv
+import mmap
+import os
+
+import numpy as np
+
+from . import _lib as S
+
+
+class SuffixArray:
+    def __init__(self, max_suffix_length: int = 64, documents=None, csv_file: str | None = None,
+                 search_column: str | None = None, device: int = 0):
+        self.max_suffix_length = int(max_suffix_length)
+        self._idx = S.Index(self.max_suffix_length, device=device)
+        self._mode = None            # "documents" | "csv"
+        self._text = None            # documents: the joined, lower-cased utf-8 bytes (host copy)
+        self._doc_starts = None
+        self.columns = None          # csv: header cells (pyx:189-194)
+        self._csv_path = None
+        self._csv_mm = None
+        self._row_starts = None
+        if documents is not None and csv_file is not None:
+            raise ValueError("pass either documents= or csv_file=, not both")
+        if documents is not None:
+            self.construct_truncated_suffix_array_documents(documents)
+        elif csv_file is not None:
+            if search_column is None:
+                raise ValueError("csv_file= needs search_column=")
+            self.construct_truncated_suffix_array_from_csv(csv_file, search_column)
+
+    # ------------------------------------------------------------------ builds
+    def construct_truncated_suffix_array_documents(self, documents) -> None:
+        """pyx:129-180: '\\n'.join(documents) -> utf-8 -> ASCII lower-case -> build."""
+        if not isinstance(documents, list):
+            try:
+                documents = list(documents)                     # pyx:130-134
+            except Exception:
+                raise ValueError("Documents must be a list of strings")
+        joined = "\n".join(documents).encode("utf-8")           # pyx:143 (no trailing '\n')
+        text = np.frombuffer(joined, dtype=np.uint8)
+        # lowercase_string (pyx:103-107) runs on the device copy: SA_FLAG_LOWERCASE
+        self._idx.build_text(text, lowercase=True)
+        self._text = self._idx.text().tobytes()                 # the bytes that were indexed
+        self._doc_starts = self._idx.doc_starts().astype(np.int64)
+        self._mode = "documents"
+
+    def construct_truncated_suffix_array_from_csv(self, filename: str, search_column: str) -> None:
+        """pyx:183-207 -> engine.c:1454: mmap scan of one column, build, remap to file offsets."""
+        if not os.path.exists(filename):
+            raise FileNotFoundError(filename)
+        with open(filename, "r", newline="") as f:              # pyx:189-194
+            self.columns = f.readline().strip().split(",")
+        self._idx.build_csv(filename, search_column)
+        self._csv_path = filename
+        self._open_csv(filename)
+        self._mode = "csv"
+
+    def _open_csv(self, filename: str) -> None:
+        f = open(filename, "rb")
+        self._csv_mm = mmap.mmap(f.fileno(), 0, access=mmap.ACCESS_READ)
+        f.close()
+        data = np.frombuffer(self._csv_mm, dtype=np.uint8)
+        # record boundaries: '\n' outside quotes (RFC 4180; the reference seeks for them per hit,
+        # engine.c:1217-1323).  Row 0 is the header line, as in the reference's scan (engine.c:513).
+        in_quotes = (np.cumsum(data == ord('"'), dtype=np.int64) & 1).astype(bool)
+        nl = np.flatnonzero((data == ord("\n")) & ~in_quotes)
+        starts = np.concatenate([[0], nl + 1]).astype(np.int64)
+        if starts[-1] >= data.size:
+            starts = starts[:-1]
+        self._row_starts = starts
+        self._row_ends = np.concatenate([nl, [data.size]]).astype(np.int64)[: starts.size]
+
+    # ------------------------------------------------------------------ queries
+    def query_records(self, substring: str, k: int = 1000):
+        if substring == "":                                      # pyx:210-211
+            return []
+        return self.query_records_batch([substring], k)[0]
+
+    def query_records_batch(self, substrings, k: int = 1000):
+        """One list of records per query: the first min(k, matches) hits in suffix-array order,
+        duplicates kept (engine.c:1185-1211 / :1356-1388)."""
+        if self._mode is None:
+            raise RuntimeError("no suffix array has been constructed")
+        qs = [s.lower().encode("utf-8") for s in substrings]    # pyx:228
+        nonempty = [i for i, q in enumerate(qs) if q]
+        out = [[] for _ in qs]
+        if not nonempty:
+            return out
+        start, end, off = self._idx.query_ranges([qs[i] for i in nonempty], k=int(k))
+        total = int(off[-1])
+        pos, doc = self._idx.query_hits(total)
+        for j, i in enumerate(nonempty):
+            lo, hi = int(off[j]), int(off[j + 1])
+            out[i] = self._materialise(doc[lo:hi])
+        return out
+
+    def query_positions(self, substrings, k: int = 1000):
+        """-> (start, end, hit_off, hit_pos, hit_doc) NumPy arrays straight from the C ABI."""
+        qs = [s.lower().encode("utf-8") if isinstance(s, str) else bytes(s) for s in substrings]
+        start, end, off = self._idx.query_ranges(qs, k=int(k))
+        pos, doc = self._idx.query_hits(int(off[-1]))
+        return start, end, off, pos, doc
+
+    def _materialise(self, docs: np.ndarray):
+        if self._mode == "documents":
+            ds, text = self._doc_starts, self._text
+            recs = []
+            for d in docs.tolist():
+                a = int(ds[d])
+                b = int(ds[d + 1]) - 1 if d + 1 < ds.size else len(text)
+                recs.append(text[a:b].decode("utf-8", "replace"))
+            return recs
+        rows = []
+        for d in docs.tolist():
+            line = self._csv_mm[int(self._row_starts[d]): int(self._row_ends[d])].decode("utf-8", "replace")
+            rows.append(line.rstrip("\r"))
+        return [dict(zip(self.columns, row)) for row in csv.reader(rows)]   # pyx:258-260
+
+    # ------------------------------------------------------------------ misc
+    @property
+    def suffix_array(self) -> np.ndarray:
+        """uint32 array as SuffixArray_struct.suffix_array holds it (file offsets on the CSV path)."""
+        return self._idx.sa()
+
+    def stats(self) -> dict:
+        return self._idx.stats()
+
+    def close(self) -> None:
+        if self._idx is not None:
+            self._idx.close()
+            self._idx = None
+        if self._csv_mm is not None:
+            self._row_starts = self._row_ends = None
+            try:
+                self._csv_mm.close()
+            except BufferError:
+                pass
+            self._csv_mm = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

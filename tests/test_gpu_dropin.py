@@ -1,0 +1,80 @@
+"""Drop-in class tests: suffixarray_b200.SuffixArray mirrors suffix_array.pyx:110-267 and the
+README snippets (README.md:14-28, :34-50); record lists are checked against the oracle's hit
+lists and against brute-force substring search."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as O
+from suffixarray_b200 import SuffixArray
+from suffixarray_b200 import workloads as W
+
+pytestmark = pytest.mark.gpu
+
+
+def test_readme_documents_snippet():
+    docs = ["Hello World", "hello there", "Goodbye", "say hello", ""]
+    sa = SuffixArray(documents=docs, max_suffix_length=32)
+    got = sa.query_records("hello", k=10)
+    assert sorted(got) == sorted(["hello world", "hello there", "say hello"])
+    assert sa.query_records("") == []
+    assert sa.query_records("zebra") == []
+    assert sa.query_records("HELLO T") == ["hello there"]      # query is lower-cased (pyx:228)
+    sa.close()
+
+
+def test_head_methods_and_value_error():
+    sa = SuffixArray(max_suffix_length=16)
+    with pytest.raises(ValueError):
+        sa.construct_truncated_suffix_array_documents(12345)   # pyx:130-134
+    with pytest.raises(RuntimeError):
+        sa.query_records("x")
+    sa.construct_truncated_suffix_array_documents(("ab", "cab", "b"))   # non-list is list()-ed
+    assert sorted(sa.query_records("ab")) == ["ab", "cab"]
+    sa.close()
+
+
+def test_documents_hits_match_oracle_order():
+    names = W.company_names(3000, seed=77, upper=True)
+    docs = [b.decode() for b in names]
+    sa = SuffixArray(documents=docs, max_suffix_length=32)
+    text = O.oracle_lowercase(np.frombuffer("\n".join(docs).encode(), np.uint8))
+    want_sa = O.oracle_build(text, 32)
+    assert np.array_equal(sa.suffix_array, want_sa)
+    qs = ["inc", "group", docs[5].lower(), docs[17][:4].lower(), "qqqq"]
+    s, e = O.oracle_query(text, want_sa, 32, [q.encode() for q in qs])
+    off, pos, doc = O.oracle_hits(text, want_sa, s, e, 25)
+    got = sa.query_records_batch(qs, k=25)
+    low_docs = [d.lower() for d in docs]
+    for i, q in enumerate(qs):
+        want = [low_docs[d] for d in doc[int(off[i]):int(off[i + 1])]]
+        assert got[i] == want
+        assert all(q in r for r in got[i])
+        n_true = sum(r.count(q) for r in low_docs)
+        assert len(got[i]) == min(25, n_true)
+    sa.close()
+
+
+def test_csv_constructor_rows():
+    data = W.csv_file_bytes(500, seed=9, quoted_fraction=0.3)
+    with tempfile.NamedTemporaryFile(suffix=".csv", delete=False) as f:
+        f.write(data)
+        path = f.name
+    try:
+        sa = SuffixArray(csv_file=path, search_column="name", max_suffix_length=32)
+        assert sa.columns == ["id", "name", "city", "score"]
+        import csv
+        import io
+        rows = list(csv.DictReader(io.StringIO(data.decode())))
+        target = rows[123]["name"].lower()
+        got = sa.query_records(target, k=50)
+        assert any(r["id"] == rows[123]["id"] for r in got)
+        assert all(target in r["name"].lower() for r in got)
+        assert sa.query_records("name") and sa.query_records("name")[0] == dict(zip(sa.columns, sa.columns))  # header is row 0
+        with pytest.raises(Exception):
+            SuffixArray(csv_file=path, search_column="nope")
+        sa.close()
+    finally:
+        os.unlink(path)
