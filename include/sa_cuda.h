@@ -58,6 +58,8 @@ typedef struct sa_stats {
     float ms_onesweep_sum;      /* sum of all onesweep scatter launches */
     float ms_query, ms_hits;    /* last query batch (device time) */
     uint64_t onesweep_elems;    /* total elements moved by those launches */
+    uint32_t code_bits;         /* bits per suffix byte in the sort keys (8 = raw bytes) */
+    uint32_t reserved0;
 } sa_stats;
 
 const char* sa_last_error(void);

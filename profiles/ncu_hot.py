@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Hot SASS instructions of the first kernel in an .ncu-rep (source page, needs -lineinfo):
-    python profiles/ncu_hot.py rep.ncu-rep [top_n] [launch_index]
+    python profiles/ncu_hot.py rep.ncu-rep [top_n] [launch_index | kernel-name substring]
 Prints the instructions with the most stall samples and the dominant stall reason of each."""
 import csv
 import io
@@ -9,7 +9,7 @@ import sys
 
 rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 25
-which = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+which = sys.argv[3] if len(sys.argv) > 3 else "0"
 txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"],
                      capture_output=True, text=True).stdout
 blocks, cur = [], None
@@ -21,7 +21,8 @@ for row in csv.reader(io.StringIO(txt)):
         cur["hdr"] = row
     elif cur is not None and cur["hdr"] and len(row) == len(cur["hdr"]):
         cur["rows"].append(row)
-b = blocks[which]
+blocks = [b for b in blocks if b["rows"]]
+b = blocks[int(which)] if which.isdigit() else [b for b in blocks if which in b["name"]][0]
 h = {k: i for i, k in enumerate(b["hdr"])}
 stall_cols = [k for k in b["hdr"] if k.startswith("stall_") and "Not Issued" not in k]
 tot = sum(float(r[h["# Samples"]] or 0) for r in b["rows"])

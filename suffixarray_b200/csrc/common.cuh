@@ -86,6 +86,71 @@ __device__ __forceinline__ uint32_t pair_lcp(uint64_t a, uint64_t b, uint32_t de
     return v < lprime ? v : lprime;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Compressed alphabet (code_bits < 8).  When the text uses at most 128 distinct byte values the
+// build works on a code array (codes[i] = order-preserving dense rank of text[i], NUL always
+// code 0) and packs `nchars` codes of `bits` bits into a word: chars top-aligned, then ONE flag bit
+// ("a terminator is among these chars") right below them, so nchars * bits <= 63.  Chars after
+// the first terminator are code 0, exactly like masked words.  More suffix bytes per 64-bit key
+// means fewer radix passes per byte and fewer refinement rounds.
+struct CodeInfo {
+    int bits;        // 1..8; 8 = identity (keys are masked words of raw bytes)
+    uint32_t nl;     // code of '\n' (0x100 when absent)
+    uint32_t ff;     // code of 0xFF (0x100 when absent)
+};
+
+// 16 bytes starting at byte offset a (any alignment) as two big-endian words.
+__device__ __forceinline__ void load_be128(const uint8_t* __restrict__ t, uint64_t a, uint64_t& w0, uint64_t& w1)
+{
+    const uint64_t* w = reinterpret_cast<const uint64_t*>(t + (a & ~7ull));
+    const uint64_t x0 = __ldg(w), x1 = __ldg(w + 1);
+    const unsigned sh = (unsigned)(a & 7ull) * 8u;
+    uint64_t lo = x0, hi = x1;
+    if (sh) {
+        const uint64_t x2 = __ldg(w + 2);
+        lo = (x0 >> sh) | (x1 << (64u - sh));
+        hi = (x1 >> sh) | (x2 << (64u - sh));
+    }
+    w0 = bswap64(lo);
+    w1 = bswap64(hi);
+}
+
+// nchars (<= 16, nchars * bits <= 63) codes from the two big-endian code words.
+__device__ __forceinline__ uint64_t pack_chars(uint64_t w0, uint64_t w1, int nchars, CodeInfo ci)
+{
+    uint64_t key = 0;
+    bool term = false;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        if (j < nchars) {
+            uint32_t c = (uint32_t)((j < 8 ? (w0 >> (56 - 8 * j)) : (w1 >> (56 - 8 * (j - 8)))) & 0xFFull);
+            if (term) c = 0;
+            key = (key << ci.bits) | c;
+            term = term || c == ci.nl || c == ci.ff;
+        }
+    }
+    const int used = nchars * ci.bits;
+    key <<= (64 - used);
+    if (term) key |= 1ull << (63 - used);
+    return key;
+}
+
+// LCP contribution of two packed-code words (same nchars) sorted adjacent in one group.
+__device__ __forceinline__ uint32_t pair_lcp_codes(uint64_t a, uint64_t b, uint32_t depth, int nchars, int bits,
+                                                    uint32_t lprime)
+{
+    const uint64_t x = a ^ b;
+    uint32_t v;
+    if (x == 0) {
+        v = ((b >> (63 - nchars * bits)) & 1ull) ? lprime : depth + (uint32_t)nchars;
+    } else {
+        uint32_t cm = (uint32_t)__clzll((long long)x) / (uint32_t)bits;
+        if (cm > (uint32_t)nchars) cm = (uint32_t)nchars;
+        v = depth + cm;
+    }
+    return v < lprime ? v : lprime;
+}
+
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ uint32_t lanemask_lt()
 {

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "common.cuh"
+
 // ---- radix.cu
 uint32_t sa_onesweep_tile_items();
 cudaError_t sa_launch_hist(const uint64_t* keys, uint32_t n, int shift0, int npasses, uint32_t* hist,
@@ -18,8 +20,14 @@ cudaError_t sa_launch_onesweep(const uint64_t* keys_in, const uint32_t* vals_in,
 constexpr uint32_t SA_SCAN_TILE = 4096;   // ranks per block in the group analysis / compaction kernels
 cudaError_t sa_launch_iota(uint32_t* out, uint32_t n, cudaStream_t s);
 cudaError_t sa_launch_lowercase(uint8_t* text, uint64_t n, cudaStream_t s);
-cudaError_t sa_launch_pack0(const uint8_t* text, uint32_t n, int cb, uint64_t* keys, cudaStream_t s);
-cudaError_t sa_launch_lcp0(const uint64_t* sorted_keys, uint32_t n, int cb, uint32_t lprime, uint16_t* lcp,
+// presence (0/1) of every byte value in text[0, n)
+cudaError_t sa_launch_byte_hist(const uint8_t* text, uint64_t n, uint32_t* hist256, int num_sms, cudaStream_t s);
+// codes = table[text] over nbytes_padded (multiple of 16) bytes
+cudaError_t sa_launch_encode(const uint8_t* text, uint64_t nbytes_padded, const uint8_t* table, uint8_t* codes,
+                             cudaStream_t s);
+// src = text (ci.bits == 8) or the code array; cb = suffix bytes per key
+cudaError_t sa_launch_pack0(const uint8_t* src, uint32_t n, int cb, sa::CodeInfo ci, uint64_t* keys, cudaStream_t s);
+cudaError_t sa_launch_lcp0(const uint64_t* sorted_keys, uint32_t n, int cb, int bits, uint32_t lprime, uint16_t* lcp,
                            cudaStream_t s);
 // tie bit r = (lcp[r] == depth); the mask has one zero word in front (bit r lives at bit r+32)
 cudaError_t sa_launch_tie_mask(const uint16_t* lcp, uint32_t n, uint32_t depth, uint32_t* tie_words,
@@ -32,11 +40,11 @@ cudaError_t sa_launch_group_flags(const uint32_t* tie_words, uint32_t nwords_dat
 cudaError_t sa_launch_scan_pairs(uint32_t* counts, uint32_t num, uint32_t* totals, cudaStream_t s);
 cudaError_t sa_launch_compact_gather(const uint32_t* amask, const uint32_t* hmask, uint32_t nwords_data,
                                      const uint32_t* tile_offsets, const uint32_t* sa, const uint8_t* text,
-                                     uint32_t depth, int cb, int gbits, uint32_t* slots, uint64_t* ckeys,
-                                     uint32_t* cvals, cudaStream_t s);
+                                     uint32_t depth, int cb, int gbits, sa::CodeInfo ci, uint32_t* slots,
+                                     uint64_t* ckeys, uint32_t* cvals, cudaStream_t s);
 cudaError_t sa_launch_writeback(const uint32_t* slots, const uint64_t* ckeys, const uint32_t* cvals, uint32_t m,
-                                uint32_t depth, int cb, int gbits, uint32_t lprime, uint32_t* sa, uint16_t* lcp,
-                                cudaStream_t s);
+                                uint32_t depth, int cb, int gbits, int bits, uint32_t lprime, uint32_t* sa,
+                                uint16_t* lcp, cudaStream_t s);
 
 // ---- finish.cu
 cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,

@@ -38,20 +38,72 @@ __global__ void iota_kernel(uint32_t* __restrict__ out, uint32_t n)
     if (i < n) out[i] = i;
 }
 
-// Round-0 keys: masked word of bytes [0, cb) of every suffix.
-__global__ void pack0_kernel(const uint8_t* __restrict__ text, uint32_t n, int cb, uint64_t* __restrict__ keys)
+// 256-bin histogram of the text bytes (which byte values occur decides the code width).
+__global__ void __launch_bounds__(256) byte_hist_kernel(const uint4* __restrict__ text16, uint64_t nvec, uint64_t n,
+                                                        uint32_t* __restrict__ hist)
+{
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+        const uint4 v = text16[i];
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (i * 16 + j < n) {
+                // presence is all that matters: a plain store avoids the atomic
+                h[(w[j >> 2] >> (8 * (j & 3))) & 0xFFu] = 1;
+            }
+        }
+    }
+    __syncthreads();
+    if (h[threadIdx.x]) hist[threadIdx.x] = 1;
+}
+
+// codes[i] = table[text[i]], 16 bytes per thread (the pad after n is written as code 0).
+__global__ void __launch_bounds__(256) encode_kernel(const uint4* __restrict__ text16, uint64_t nvec,
+                                                     const uint8_t* __restrict__ table, uint4* __restrict__ codes16)
+{
+    __shared__ uint8_t tab[256];
+    tab[threadIdx.x] = table[threadIdx.x];
+    __syncthreads();
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nvec) return;
+    uint4 v = text16[i];
+    uint32_t* w = reinterpret_cast<uint32_t*>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t x = w[j];
+        w[j] = (uint32_t)tab[x & 0xFFu] | ((uint32_t)tab[(x >> 8) & 0xFFu] << 8) |
+               ((uint32_t)tab[(x >> 16) & 0xFFu] << 16) | ((uint32_t)tab[x >> 24] << 24);
+    }
+    codes16[i] = v;
+}
+
+// Round-0 keys of every suffix: masked word of bytes [0, cb) (bits == 8) or cb packed codes.
+__global__ void pack0_kernel(const uint8_t* __restrict__ src, uint32_t n, int cb, CodeInfo ci,
+                             uint64_t* __restrict__ keys)
 {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    keys[p] = mask_word(load_be64(text, p), cb);
+    if (ci.bits == 8) {
+        keys[p] = mask_word(load_be64(src, p), cb);
+    } else {
+        uint64_t w0, w1;
+        load_be128(src, p, w0, w1);
+        keys[p] = pack_chars(w0, w1, cb, ci);
+    }
 }
 
-__global__ void lcp0_kernel(const uint64_t* __restrict__ k, uint32_t n, int cb, uint32_t lprime,
+__global__ void lcp0_kernel(const uint64_t* __restrict__ k, uint32_t n, int cb, int bits, uint32_t lprime,
                             uint16_t* __restrict__ lcp)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
-    lcp[r] = r ? (uint16_t)pair_lcp(k[r - 1], k[r], 0, cb, lprime) : (uint16_t)0;
+    uint32_t v = 0;
+    if (r) v = bits == 8 ? pair_lcp(k[r - 1], k[r], 0, cb, lprime) : pair_lcp_codes(k[r - 1], k[r], 0, cb, bits, lprime);
+    lcp[r] = (uint16_t)v;
 }
 
 // word w (w >= 1) holds ranks [32(w-1), 32w); word 0 is a zero pad.
@@ -160,7 +212,7 @@ __global__ void __launch_bounds__(SA_SCAN_TILE / 32)
 compact_gather_kernel(const uint32_t* __restrict__ amask, const uint32_t* __restrict__ hmask,
                       uint32_t nwords_data, const uint32_t* __restrict__ tile_offsets,
                       const uint32_t* __restrict__ sa, const uint8_t* __restrict__ text, uint32_t depth, int cb,
-                      int gbits, uint32_t* __restrict__ slots, uint64_t* __restrict__ ckeys,
+                      int gbits, CodeInfo ci, uint32_t* __restrict__ slots, uint64_t* __restrict__ ckeys,
                       uint32_t* __restrict__ cvals)
 {
     constexpr int T = SA_SCAN_TILE / 32;
@@ -199,7 +251,14 @@ compact_gather_kernel(const uint32_t* __restrict__ amask, const uint32_t* __rest
     for (uint32_t j = t; j < tot; j += T) {
         const uint32_t r = s_rank[j];
         const uint32_t p = sa[r];
-        const uint64_t wd = mask_word(load_be64(text, (uint64_t)p + depth), cb);
+        uint64_t wd;
+        if (ci.bits == 8) {
+            wd = mask_word(load_be64(text, (uint64_t)p + depth), cb);
+        } else {
+            uint64_t w0, w1;
+            load_be128(text, (uint64_t)p + depth, w0, w1);
+            wd = pack_chars(w0, w1, cb, ci);
+        }
         slots[out0 + j] = r;
         cvals[out0 + j] = p;
         ckeys[out0 + j] = ((uint64_t)s_gid[j] << (64 - gbits)) | (wd >> gbits);
@@ -208,7 +267,7 @@ compact_gather_kernel(const uint32_t* __restrict__ amask, const uint32_t* __rest
 
 __global__ void writeback_kernel(const uint32_t* __restrict__ slots, const uint64_t* __restrict__ ckeys,
                                  const uint32_t* __restrict__ cvals, uint32_t m, uint32_t depth, int cb, int gbits,
-                                 uint32_t lprime, uint32_t* __restrict__ sa, uint16_t* __restrict__ lcp)
+                                 int bits, uint32_t lprime, uint32_t* __restrict__ sa, uint16_t* __restrict__ lcp)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= m) return;
@@ -217,7 +276,8 @@ __global__ void writeback_kernel(const uint32_t* __restrict__ slots, const uint6
     if (i == 0) return;
     const uint64_t a = ckeys[i - 1], b = ckeys[i];
     if ((a >> (64 - gbits)) != (b >> (64 - gbits))) return;          // first member of its group
-    lcp[r] = (uint16_t)pair_lcp(a << gbits, b << gbits, depth, cb, lprime);
+    lcp[r] = (uint16_t)(bits == 8 ? pair_lcp(a << gbits, b << gbits, depth, cb, lprime)
+                                  : pair_lcp_codes(a << gbits, b << gbits, depth, cb, bits, lprime));
 }
 
 }  // namespace sa
@@ -238,17 +298,40 @@ cudaError_t sa_launch_lowercase(uint8_t* text, uint64_t n, cudaStream_t s)
     return cudaGetLastError();
 }
 
-cudaError_t sa_launch_pack0(const uint8_t* text, uint32_t n, int cb, uint64_t* keys, cudaStream_t s)
+cudaError_t sa_launch_byte_hist(const uint8_t* text, uint64_t n, uint32_t* hist256, int num_sms, cudaStream_t s)
 {
-    if (!n) return cudaSuccess;
-    sa::pack0_kernel<<<(n + 255) / 256, 256, 0, s>>>(text, n, cb, keys);
+    cudaError_t e = cudaMemsetAsync(hist256, 0, 256 * sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    const uint64_t nvec = (n + 15) / 16;
+    if (!nvec) return cudaSuccess;
+    uint64_t blocks = (nvec + 255) / 256;
+    if (blocks > (uint64_t)num_sms * 8) blocks = (uint64_t)num_sms * 8;
+    sa::byte_hist_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), nvec, n, hist256);
     return cudaGetLastError();
 }
 
-cudaError_t sa_launch_lcp0(const uint64_t* k, uint32_t n, int cb, uint32_t lprime, uint16_t* lcp, cudaStream_t s)
+cudaError_t sa_launch_encode(const uint8_t* text, uint64_t nbytes_padded, const uint8_t* table, uint8_t* codes,
+                             cudaStream_t s)
+{
+    const uint64_t nvec = nbytes_padded / 16;
+    if (!nvec) return cudaSuccess;
+    sa::encode_kernel<<<(unsigned)((nvec + 255) / 256), 256, 0, s>>>(reinterpret_cast<const uint4*>(text), nvec, table,
+                                                                     reinterpret_cast<uint4*>(codes));
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_pack0(const uint8_t* src, uint32_t n, int cb, sa::CodeInfo ci, uint64_t* keys, cudaStream_t s)
 {
     if (!n) return cudaSuccess;
-    sa::lcp0_kernel<<<(n + 255) / 256, 256, 0, s>>>(k, n, cb, lprime, lcp);
+    sa::pack0_kernel<<<(n + 255) / 256, 256, 0, s>>>(src, n, cb, ci, keys);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_lcp0(const uint64_t* k, uint32_t n, int cb, int bits, uint32_t lprime, uint16_t* lcp,
+                           cudaStream_t s)
+{
+    if (!n) return cudaSuccess;
+    sa::lcp0_kernel<<<(n + 255) / 256, 256, 0, s>>>(k, n, cb, bits, lprime, lcp);
     return cudaGetLastError();
 }
 
@@ -279,22 +362,23 @@ cudaError_t sa_launch_scan_pairs(uint32_t* counts, uint32_t num, uint32_t* total
 
 cudaError_t sa_launch_compact_gather(const uint32_t* amask, const uint32_t* hmask, uint32_t nwords_data,
                                      const uint32_t* tile_offsets, const uint32_t* sa_, const uint8_t* text,
-                                     uint32_t depth, int cb, int gbits, uint32_t* slots, uint64_t* ckeys,
-                                     uint32_t* cvals, cudaStream_t s)
+                                     uint32_t depth, int cb, int gbits, sa::CodeInfo ci, uint32_t* slots,
+                                     uint64_t* ckeys, uint32_t* cvals, cudaStream_t s)
 {
     constexpr uint32_t T = SA_SCAN_TILE / 32;
     const uint32_t tiles = (nwords_data + T - 1) / T;
     if (!tiles) return cudaSuccess;
     sa::compact_gather_kernel<<<tiles, T, 0, s>>>(amask, hmask, nwords_data, tile_offsets, sa_, text, depth, cb,
-                                                  gbits, slots, ckeys, cvals);
+                                                  gbits, ci, slots, ckeys, cvals);
     return cudaGetLastError();
 }
 
 cudaError_t sa_launch_writeback(const uint32_t* slots, const uint64_t* ckeys, const uint32_t* cvals, uint32_t m,
-                                uint32_t depth, int cb, int gbits, uint32_t lprime, uint32_t* sa_, uint16_t* lcp,
-                                cudaStream_t s)
+                                uint32_t depth, int cb, int gbits, int bits, uint32_t lprime, uint32_t* sa_,
+                                uint16_t* lcp, cudaStream_t s)
 {
     if (!m) return cudaSuccess;
-    sa::writeback_kernel<<<(m + 255) / 256, 256, 0, s>>>(slots, ckeys, cvals, m, depth, cb, gbits, lprime, sa_, lcp);
+    sa::writeback_kernel<<<(m + 255) / 256, 256, 0, s>>>(slots, ckeys, cvals, m, depth, cb, gbits, bits, lprime, sa_,
+                                                         lcp);
     return cudaGetLastError();
 }

@@ -41,8 +41,12 @@ enum SmallSlot : uint32_t {
     SM_ERR = 4107,          // 1
     SM_RUNCTR = 4108,       // 2 (u64, 8-byte aligned)
     SM_NLTOTAL = 4110,      // 1
-    SM_WORDS = 4112
+    SM_BYTEHIST = 4112,     // 256 presence flags
+    SM_TABLE = 4368,        // 256 bytes = 64 words: byte -> code
+    SM_WORDS = 4432
 };
+
+constexpr size_t H_SMALL_WORDS = 1024;   // [0,64) misc, [256,512) byte presence, [512,576) code table
 
 struct PhaseTimer {
     cudaEvent_t a = nullptr, b = nullptr;
@@ -71,13 +75,15 @@ struct sa_index {
 
     // build scratch (kept between builds so repeated builds do not re-allocate)
     DevBuf keys[2], vals[2], aux[2], lcp, tie, amask, hmask, counts, status, small, nl_counts;
+    DevBuf codes;       // compressed-alphabet copy of the text (code_bits < 8), build scratch
+    sa::CodeInfo code{8, 0x100u, 0x100u};
 
     // query scratch / results of the last batch
     DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
     uint64_t last_nq = 0, last_total_hits = 0;
     bool have_ranges = false;
 
-    uint32_t* h_small = nullptr;   // pinned mirror for tiny read-backs (64 words)
+    uint32_t* h_small = nullptr;   // pinned mirror for tiny read-backs (H_SMALL_WORDS words)
 
     sa_stats stats{};
     std::vector<PhaseTimer> timers;
@@ -89,6 +95,7 @@ struct sa_index {
     int64_t dbg_max_rounds = -1;    // stop refining after this many rounds (-1: no limit)
     int64_t dbg_skip_finish = 0;    // leave the phase-1 order (no <=32 bucket step)
     int64_t dbg_force_gbits = 0;    // use at least this many group-id bits (exercises small cb)
+    int64_t dbg_code_bits = -1;     // -1: choose from the alphabet; 8: never compress; 1..7: at least this width
 };
 
 void sa_set_error(const char* fmt, ...);

@@ -144,3 +144,29 @@ def test_large_properties_20m():
     assert (np.diff(fb.astype(np.int16)) >= 0).all()
     # and the whole array equals the oracle (20 MB finishes in a few seconds)
     assert np.array_equal(sa, O.oracle_build(text, 32))
+
+
+@pytest.mark.parametrize("code_bits", [8, 7, 5, 3])
+def test_alphabet_code_widths(code_bits):
+    """The compressed-alphabet keys (code_bits < 8) and the raw-byte keys (8) give the same SA."""
+    rng = np.random.default_rng(29)
+    cases = [
+        (random_text(rng, 30000, 2, newline_p=0.02), 32),
+        (random_text(rng, 30000, 3), 17),
+        (random_text(rng, 5000, 1, newline_p=0.01), 64),
+        (W.english_documents(300_000, seed=31), 32),
+        (W.company_names_joined(20_000, seed=33, upper=False)[0], 32),
+        (np.frombuffer(b"\n\n\nab\n\n\nab\n\n" * 400, np.uint8), 16),
+        (rng.choice(np.array([10, 255, 0, 97, 98], np.uint8), size=20000), 32),
+    ]
+    for t, L in cases:
+        st = assert_same(t, L, code_bits=code_bits)
+        assert st["code_bits"] >= min(code_bits, 8) or code_bits == 8
+
+
+def test_alphabet_auto_widths():
+    rng = np.random.default_rng(37)
+    for sigma, want_bits in ((1, 2), (2, 2), (6, 3), (26, 5), (100, 7), (200, 8)):
+        t = random_text(rng, 20000, sigma, base=20 if sigma > 26 else ord("a"))
+        st = assert_same(t, 32)
+        assert st["code_bits"] == want_bits, (sigma, st["code_bits"])
