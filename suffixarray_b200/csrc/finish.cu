@@ -5,20 +5,52 @@
 // sorted-by-prefix array those buckets are contiguous, and the depth at which rank r's bucket
 // first has <= 32 members is
 //     d*(r) = 1 + max over the 33-rank windows containing r of (min adjacent LCP inside it)
-// (0 when n <= 32).  Each block takes 1024 ranks (+32 halo each side): sliding min/max over the
-// LCPs in shared memory, a 17-byte window key per member (gathered from the L2-resident text),
-// then every rank counts the members of its own bucket that sort before it.
-//   bucket is left alone when d* >= L' (engine.c:706), when it has one member, or when the
-//   shared d*-byte prefix holds '\n' / 0xFF (such buckets are never entered, engine.c:771-773).
+// (0 when n <= 32).  Each block takes 1024 ranks (+ halo):
+//   A. adjacent LCPs -> shared memory
+//   B. 32-wide sliding minimum, then 33-wide sliding maximum, both by the block-prefix /
+//      block-suffix decomposition (van Herk / Gil-Werman) with warp shuffles: 2 barriers
+//   C. per rank: d*, bucket-head flag (lcp < d*), and -- when the bucket gets re-sorted -- the
+//      17-byte window key at text[pos + d*] (one 32-byte aligned read per rank, the byte in
+//      front of the window tells whether the shared prefix ends in a terminator)
+//   D. bucket bounds from the head bit masks (clz / ffs), rank-by-counting inside the bucket
+// A bucket is left alone when d* >= L' (engine.c:706), when it has one member, or when the
+// shared d*-byte prefix ends in '\n' / 0xFF (such buckets are never entered, engine.c:771-773;
+// a terminator can only sit at byte d*-1: an earlier one would have frozen a larger bucket).
 #include "common.cuh"
 #include "kernels.h"
 
 namespace sa {
 
 constexpr int FT = 1024;             // ranks per block
-constexpr int FEXT = FT + 64;        // ranks with keys: [b0-32, b0+FT+32)
-constexpr int FLCP = FT + 129;       // lcp entries: ranks [b0-64, b0+FT+65)
+constexpr int FEXT = FT + 64;        // ranks with keys: [b0-32, b0+FT+32)            (34 warps' worth)
+constexpr int FLCP = FT + 160;       // lcp entries: ranks [b0-64, b0+FT+96)          (37 * 32)
 constexpr int FTHREADS = 256;
+constexpr int FWARPS = FTHREADS / 32;
+
+__device__ __forceinline__ int warp_prefix_min(int v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v = min(v, y); }
+    return v;
+}
+__device__ __forceinline__ int warp_suffix_min(int v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_down_sync(0xffffffffu, v, o); if (lane + o < 32) v = min(v, y); }
+    return v;
+}
+__device__ __forceinline__ int warp_prefix_max(int v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v = max(v, y); }
+    return v;
+}
+__device__ __forceinline__ int warp_suffix_max(int v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_down_sync(0xffffffffu, v, o); if (lane + o < 32) v = max(v, y); }
+    return v;
+}
 
 __global__ void __launch_bounds__(FTHREADS)
 finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ lcp,
@@ -26,70 +58,86 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
               unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err)
 {
     __shared__ int16_t s_l[FLCP];        // adjacent LCPs, -1 outside [1, n)
-    __shared__ int16_t s_a[FLCP];
-    __shared__ int16_t s_b[FLCP];
-    __shared__ int16_t s_m[FLCP];        // window minima
-    __shared__ uint64_t s_hi[FEXT], s_lo[FEXT];
-    __shared__ uint32_t s_pos[FEXT];
-    __shared__ uint32_t s_meta[FEXT];    // bits 0-7: 17th byte, bit 8: bucket gets re-sorted
-    __shared__ int16_t s_d[FEXT];
+    __shared__ int16_t s_p[FLCP];        // block prefix min of l, later block prefix max of m
+    __shared__ int16_t s_s[FLCP];        // block suffix min of l, later block suffix max of m
+    __shared__ uint64_t s_hi[FEXT], s_lo[FEXT], s_tp[FEXT];   // window key words; tp = byte16 << 32 | pos
+    __shared__ uint32_t s_head[FEXT / 32 + 2], s_sort[FEXT / 32 + 2];
     __shared__ uint32_t s_runs;
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t b0 = (int64_t)blockIdx.x * FT;
     if (tid == 0) s_runs = 0;
     for (int j = tid; j < FLCP; j += FTHREADS) {
         const int64_t r = b0 - 64 + j;
-        s_l[j] = (r >= 1 && r < (int64_t)n) ? (int16_t)lcp[r] : (int16_t)-1;
+        s_l[j] = (r >= 1 && r < (int64_t)n) ? (int16_t)__ldcs(lcp + r) : (int16_t)-1;
     }
     __syncthreads();
-    // m[j] = min(l[j+1 .. j+32]) by doubling: widths 2,4,8,16,32
-    for (int j = tid; j < FLCP; j += FTHREADS) s_a[j] = (j + 2 < FLCP) ? min(s_l[j + 1], s_l[j + 2]) : (int16_t)-1;
+    // B1: per 32-block prefix / suffix minima of l
+    for (int blk = warp; blk < FLCP / 32; blk += FWARPS) {
+        const int j = blk * 32 + lane;
+        const int v = s_l[j];
+        s_p[j] = (int16_t)warp_prefix_min(v, lane);
+        s_s[j] = (int16_t)warp_suffix_min(v, lane);
+    }
     __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_b[j] = (j + 2 < FLCP) ? min(s_a[j], s_a[j + 2]) : (int16_t)-1;
+    // B2: m[j] = min(l[j+1 .. j+32]) = min(suffix[j+1], prefix[j+32]); per 32-block prefix / suffix maxima of m
+    constexpr int MIT = (FLCP / 32 + FWARPS - 1) / FWARPS;
+    int mreg[MIT];
+#pragma unroll
+    for (int it = 0; it < MIT; ++it) {
+        const int j = (warp + it * FWARPS) * 32 + lane;
+        mreg[it] = (j + 32 < FLCP) ? min((int)s_s[j + 1], (int)s_p[j + 32]) : -1;
+    }
     __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_a[j] = (j + 4 < FLCP) ? min(s_b[j], s_b[j + 4]) : (int16_t)-1;
-    __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_b[j] = (j + 8 < FLCP) ? min(s_a[j], s_a[j + 8]) : (int16_t)-1;
-    __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_m[j] = (j + 16 < FLCP) ? min(s_b[j], s_b[j + 16]) : (int16_t)-1;
-    __syncthreads();
-    // M[j] = max(m[j-32 .. j]): widths 2,4,8,16,32 then one more element
-    for (int j = tid; j < FLCP; j += FTHREADS) s_a[j] = (j >= 1) ? max(s_m[j], s_m[j - 1]) : s_m[j];
-    __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_b[j] = (j >= 2) ? max(s_a[j], s_a[j - 2]) : s_a[j];
-    __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_a[j] = (j >= 4) ? max(s_b[j], s_b[j - 4]) : s_b[j];
-    __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_b[j] = (j >= 8) ? max(s_a[j], s_a[j - 8]) : s_a[j];
-    __syncthreads();
-    for (int j = tid; j < FLCP; j += FTHREADS) s_a[j] = (j >= 16) ? max(s_b[j], s_b[j - 16]) : s_b[j];
+#pragma unroll
+    for (int it = 0; it < MIT; ++it) {
+        const int blk = warp + it * FWARPS;
+        if (blk < FLCP / 32) {                                   // warp-uniform
+            const int j = blk * 32 + lane;
+            s_p[j] = (int16_t)warp_prefix_max(mreg[it], lane);
+            s_s[j] = (int16_t)warp_suffix_max(mreg[it], lane);
+        }
+    }
     __syncthreads();
 
-    // keys for ranks [b0-32, b0+FT+32)
+    // C: keys for ranks [b0-32, b0+FT+32), one warp-iteration per 32 consecutive ranks
     const int lim = lprime < 17u ? (int)lprime : 17;
-    for (int e = tid; e < FEXT; e += FTHREADS) {
+    for (int eb = warp; eb < FEXT / 32; eb += FWARPS) {
+        const int e = eb * 32 + lane;
         const int64_t r = b0 - 32 + e;
         const int j = e + 32;                                    // index into the lcp-space arrays
-        uint32_t meta = 0, pos = 0;
-        uint64_t hi = 0, lo = 0;
-        int16_t d = 0;
+        uint64_t hi = 0, lo = 0, tp = 0;
+        bool head = true, resort = false;
         if (r >= 0 && r < (int64_t)n) {
-            d = (int16_t)(max(s_a[j], s_m[j - 32]) + 1);
-            pos = sa_in[r];
-            const bool has_nb = (s_l[j] >= d) || (s_l[j + 1] >= d);
+            // max(m[j-32 .. j]) = max(block suffix max at j-32, block prefix max at j)
+            const int d = max((int)s_s[j - 32], (int)s_p[j]) + 1;
+            const uint32_t pos = __ldcs(sa_in + r);
+            const int lj = s_l[j];
+            head = lj < d;
+            tp = pos;
+            const bool has_nb = (lj >= d) || ((int)s_l[j + 1] >= d);
             if ((uint32_t)d < lprime && has_nb) {
+                // 32 aligned bytes that hold text[pos+d-1 .. pos+d+16]
+                const uint64_t a = (uint64_t)pos + (uint32_t)d;
+                const uint64_t a0 = d ? a - 1 : a;
+                const uint64_t* wp = reinterpret_cast<const uint64_t*>(text + (a0 & ~7ull));
+                const uint64_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3);
+                uint32_t o = (uint32_t)(a - (a0 & ~7ull));       // 0..8: offset of the window in the 32 bytes
                 bool term = false;
-                for (int w = 0; w < d; w += 8) {
-                    uint64_t be = load_be64(text, (uint64_t)pos + w);
-                    const int kb = (d - w) < 8 ? (d - w) : 8;
-                    term |= terminator_bytes(keep_top_bytes(be, kb)) != 0;
+                if (d) {
+                    const uint32_t ob = o - 1;
+                    const uint32_t pb = (uint32_t)((ob < 8 ? w0 : w1) >> (8 * (ob & 7))) & 0xFFu;
+                    term = pb == 0x0Au || pb == 0xFFu;
                 }
                 if (!term) {
-                    const uint64_t q = (uint64_t)pos + (uint32_t)d;
-                    hi = load_be64(text, q);
-                    lo = load_be64(text, q + 8);
-                    uint32_t b16 = text[q + 16];
+                    uint64_t x0 = w0, x1 = w1, x2 = w2;
+                    if (o == 8) { x0 = w1; x1 = w2; x2 = w3; o = 0; }
+                    const uint32_t sh = o * 8;
+                    uint64_t v0 = x0, v1 = x1;
+                    if (sh) { v0 = (x0 >> sh) | (x1 << (64 - sh)); v1 = (x1 >> sh) | (x2 << (64 - sh)); }
+                    hi = bswap64(v0);
+                    lo = bswap64(v1);
+                    uint32_t b16 = (uint32_t)(x2 >> sh) & 0xFFu;
                     // bytes after the first NUL of the 16-byte window do not take part (pcmpistri)
                     uint64_t z = zero_bytes(hi);
                     if (z) {
@@ -104,41 +152,42 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
                     if (lim < 17) b16 = 0;
                     if (lim < 16) lo = (lim > 8) ? keep_top_bytes(lo, lim - 8) : 0ull;
                     if (lim < 8) hi = keep_top_bytes(hi, lim);
-                    meta = b16 | 0x100u;
+                    tp |= (uint64_t)b16 << 32;
+                    resort = true;
                 }
             }
         }
-        s_hi[e] = hi; s_lo[e] = lo; s_pos[e] = pos; s_meta[e] = meta; s_d[e] = d;
+        s_hi[e] = hi; s_lo[e] = lo; s_tp[e] = tp;
+        const uint32_t hb = __ballot_sync(0xffffffffu, head), rb = __ballot_sync(0xffffffffu, resort);
+        if (lane == 0) { s_head[eb] = hb; s_sort[eb] = rb; }
     }
+    if (tid == 0) { s_head[FEXT / 32] = 0xFFFFFFFFu; s_sort[FEXT / 32] = 0; }
     __syncthreads();
 
+    // D: rank inside the bucket
     uint32_t my_runs = 0;
     for (int t = tid; t < FT; t += FTHREADS) {
         const int64_t r = b0 + t;
         if (r >= (int64_t)n) break;
-        const int e = t + 32, j = t + 64;
-        const uint32_t pos = s_pos[e], meta = s_meta[e];
-        if (!(meta & 0x100u)) { sa_out[r] = pos; continue; }
-        const int d = s_d[e];
-        int back = 0, fwd = 0;
-        while (back < SA_SMALL && s_l[j - back] >= d) ++back;      // members before r
-        while (fwd < SA_SMALL && s_l[j + 1 + fwd] >= d) ++fwd;      // members after r
-        if (back + fwd + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); sa_out[r] = pos; continue; }
+        const int e = t + 32, q = e >> 5, i = e & 31;
+        const uint64_t tp = s_tp[e];
+        const uint32_t pos = (uint32_t)tp;
+        if (!((s_sort[q] >> i) & 1u)) { __stcs(sa_out + r, pos); continue; }
+        // bucket = [first, last]: last head at or before e, next head after e
+        const uint64_t X = (((uint64_t)s_head[q] << 32) | s_head[q - 1]) & (~0ull >> (31 - i));
+        const int first = (q - 1) * 32 + (63 - __clzll((long long)X));
+        const uint64_t Y = ((((uint64_t)s_head[q + 1] << 32) | s_head[q]) >> i) >> 1;
+        const int last = Y ? e + __ffsll((long long)Y) - 1 : e + 32;
+        if (X == 0 || last - first + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); __stcs(sa_out + r, pos); continue; }
         const uint64_t hi = s_hi[e], lo = s_lo[e];
-        const uint32_t b16 = meta & 0xFFu;
         uint32_t rank = 0;
-        for (int x = e - back; x <= e + fwd; ++x) {
-            const uint64_t h2 = s_hi[x], l2 = s_lo[x];
-            const uint32_t c2 = s_meta[x] & 0xFFu, p2 = s_pos[x];
-            bool less;
-            if (h2 != hi) less = h2 < hi;
-            else if (l2 != lo) less = l2 < lo;
-            else if (c2 != b16) less = c2 < b16;
-            else less = p2 < pos;
+        for (int x = first; x <= last; ++x) {
+            const uint64_t h2 = s_hi[x], l2 = s_lo[x], t2 = s_tp[x];
+            const bool less = (h2 < hi) || (h2 == hi && ((l2 < lo) || (l2 == lo && t2 < tp)));
             rank += less;
         }
-        sa_out[r - back + rank] = pos;
-        if (back == 0) ++my_runs;
+        __stcs(sa_out + (r - (e - first) + rank), pos);
+        if (e == first) ++my_runs;
     }
     if (my_runs) atomicAdd(&s_runs, my_runs);
     __syncthreads();
