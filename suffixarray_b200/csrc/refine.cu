@@ -87,12 +87,63 @@ __global__ void pack0_kernel(const uint8_t* __restrict__ src, uint32_t n, int cb
 {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    if (ci.bits == 8) {
-        keys[p] = mask_word(load_be64(src, p), cb);
+    keys[p] = mask_word(load_be64(src, p), cb);
+}
+
+// Compressed alphabet: one thread packs the keys of 8 consecutive suffixes from 32 code bytes.
+// F_k = the cb codes starting at k (unmasked) slides by one code per suffix; the masked key keeps
+// the fields up to and including the first terminator at or after k.
+__global__ void __launch_bounds__(256)
+pack0_codes_kernel(const uint8_t* __restrict__ codes, uint32_t n, int cb, CodeInfo ci, uint64_t* __restrict__ keys)
+{
+    const uint32_t p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 8u;
+    if (p0 >= n) return;
+    // 8 + 16 = 24 code bytes needed (p0 is a multiple of 8; the allocation is padded)
+    const uint64_t* c8 = reinterpret_cast<const uint64_t*>(codes + p0);
+    const uint64_t W0 = c8[0], W1 = c8[1], W2 = c8[2];
+    auto code_at = [&](int i) -> uint32_t {
+        const uint64_t ww = i < 8 ? W0 : (i < 16 ? W1 : W2);
+        return (uint32_t)(ww >> (8 * (i & 7))) & 0xFFu;
+    };
+    // bit i of termmask: code i is a terminator
+    uint32_t termmask = 0;
+#pragma unroll
+    for (int i = 0; i < 24; ++i) {
+        const uint32_t c = code_at(i);
+        termmask |= (uint32_t)(c == ci.nl || c == ci.ff) << i;
+    }
+    const int used = cb * ci.bits;
+    const uint64_t fmask = used >= 64 ? ~0ull : ((1ull << used) - 1ull);
+    uint64_t F = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+        if (i < cb) F = (F << ci.bits) | code_at(i);
+    uint64_t out[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t tm = (termmask >> k) & ((cb >= 32) ? 0xFFFFFFFFu : ((1u << cb) - 1u));
+        uint64_t key = F;
+        if (tm) {
+            const int t = __ffs((int)tm) - 1;                     // first terminator inside the window
+            key &= ~((1ull << (ci.bits * (cb - 1 - t))) - 1ull);
+        }
+        key <<= (64 - used);
+        if (tm) key |= 1ull << (63 - used);
+        out[k] = key;
+        // slide: drop the oldest code, append code k + cb
+        F = ((F << ci.bits) & fmask) | code_at(k + cb);
+    }
+    if (p0 + 8 <= n) {
+        uint4* o = reinterpret_cast<uint4*>(keys + p0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint4 v;
+            v.x = (uint32_t)out[2 * k]; v.y = (uint32_t)(out[2 * k] >> 32);
+            v.z = (uint32_t)out[2 * k + 1]; v.w = (uint32_t)(out[2 * k + 1] >> 32);
+            o[k] = v;
+        }
     } else {
-        uint64_t w0, w1;
-        load_be128(src, p, w0, w1);
-        keys[p] = pack_chars(w0, w1, cb, ci);
+        for (int k = 0; k < 8 && p0 + k < n; ++k) keys[p0 + k] = out[k];
     }
 }
 
@@ -323,7 +374,12 @@ cudaError_t sa_launch_encode(const uint8_t* text, uint64_t nbytes_padded, const 
 cudaError_t sa_launch_pack0(const uint8_t* src, uint32_t n, int cb, sa::CodeInfo ci, uint64_t* keys, cudaStream_t s)
 {
     if (!n) return cudaSuccess;
-    sa::pack0_kernel<<<(n + 255) / 256, 256, 0, s>>>(src, n, cb, ci, keys);
+    if (ci.bits == 8) {
+        sa::pack0_kernel<<<(n + 255) / 256, 256, 0, s>>>(src, n, cb, ci, keys);
+    } else {
+        const uint32_t threads = (n + 7) / 8;
+        sa::pack0_codes_kernel<<<(threads + 255) / 256, 256, 0, s>>>(src, n, cb, ci, keys);
+    }
     return cudaGetLastError();
 }
 
