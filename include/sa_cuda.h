@@ -119,6 +119,27 @@ int sa_query_ranges_device(sa_index* idx, const uint8_t* d_qbytes, const uint64_
 uint64_t sa_num_docs(const sa_index* idx);
 int sa_copy_doc_starts(sa_index* idx, uint32_t* out, uint64_t cap);
 
+/* ---- One suffix array over several GPUs (sample sort; one sa_index per GPU / process, the text
+ * replicated).  No reference counterpart: the reference only cuts the text into independent 2 GiB
+ * partitions (suffix_array.pyx:148-180).  Call order on every rank:
+ *   sa_shard_begin -> sa_shard_pack (+ all-reduce of the 65536-bin histogram, splitter choice on
+ *   the host) -> sa_shard_split -> all-to-all of the (key, position) records over NCCL ->
+ *   sa_shard_sort -> sa_shard_edges (+ all-gather of the edges) -> sa_shard_finish ->
+ *   all-gather of the slices -> sa_adopt_sa (queries).  suffixarray_b200/sharded.py drives it. */
+int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, uint32_t flags);
+int sa_shard_pack(sa_index* idx, uint64_t pos_begin, uint64_t pos_end, uint64_t* d_keys, uint32_t* d_pos,
+                  uint32_t* d_hist16);
+int sa_shard_split(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m,
+                   const uint8_t* bin2rank, int nranks, uint64_t* d_keys_out, uint32_t* d_pos_out,
+                   uint64_t* counts_out);
+int sa_shard_sort(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m);
+int sa_shard_edges(sa_index* idx, uint32_t edge, uint32_t* head_pos, uint16_t* head_lcp, uint32_t* tail_pos,
+                   uint16_t* tail_lcp);
+int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
+                    uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp, uint32_t nright,
+                    uint32_t* d_sa_out);
+int sa_adopt_sa(sa_index* idx, const uint32_t* d_sa_full, uint64_t n);
+
 /* Debug / parity hooks (used by tests to localise a mismatch; not part of the drop-in). */
 int sa_debug_copy_lcp(sa_index* idx, uint16_t* out, uint64_t cap);
 int sa_debug_set(sa_index* idx, const char* key, int64_t value);

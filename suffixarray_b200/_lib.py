@@ -27,6 +27,8 @@ EXPORTS = [
     "sa_build_csv", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
     "sa_copy_quoted_bits", "sa_copy_text", "sa_device_sa", "sa_get_stats", "sa_query_ranges", "sa_query_hits",
     "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
+    "sa_shard_begin", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
+    "sa_adopt_sa",
 ]
 
 
@@ -95,6 +97,13 @@ def lib():
     L.sa_query_hits.argtypes = [_vp, _vp, _vp, C.c_uint64]
     L.sa_query_ranges_device.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint64, C.c_uint32, _vp, _vp]
     L.sa_debug_set.argtypes = [_vp, C.c_char_p, C.c_int64]
+    L.sa_shard_begin.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
+    L.sa_shard_pack.argtypes = [_vp, C.c_uint64, C.c_uint64, _vp, _vp, _vp]
+    L.sa_shard_split.argtypes = [_vp, _vp, _vp, C.c_uint64, _vp, C.c_int, _vp, _vp, _vp]
+    L.sa_shard_sort.argtypes = [_vp, _vp, _vp, C.c_uint64]
+    L.sa_shard_edges.argtypes = [_vp, C.c_uint32, _vp, _vp, _vp, _vp]
+    L.sa_shard_finish.argtypes = [_vp, _vp, _vp, C.c_uint32, C.c_uint32, _vp, _vp, C.c_uint32, _vp]
+    L.sa_adopt_sa.argtypes = [_vp, _vp, C.c_uint64]
     _lib = L
     return L
 

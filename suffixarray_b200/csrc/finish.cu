@@ -54,8 +54,8 @@ __device__ __forceinline__ int warp_suffix_max(int v, int lane)
 
 __global__ void __launch_bounds__(FTHREADS)
 finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ lcp,
-              const uint8_t* __restrict__ text, uint32_t n, uint32_t lprime, uint32_t* __restrict__ sa_out,
-              unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err)
+              const uint8_t* __restrict__ text, uint32_t n, uint32_t lprime, uint32_t r_begin, uint32_t r_end,
+              uint32_t* __restrict__ sa_out, unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err)
 {
     __shared__ int16_t s_l[FLCP];        // adjacent LCPs, -1 outside [1, n)
     __shared__ int16_t s_p[FLCP];        // block prefix min of l, later block prefix max of m
@@ -169,6 +169,7 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
     for (int t = tid; t < FT; t += FTHREADS) {
         const int64_t r = b0 + t;
         if (r >= (int64_t)n) break;
+        if (r < (int64_t)r_begin || r >= (int64_t)r_end) continue;    // halo record of a shard
         const int e = t + 32, q = e >> 5, i = e & 31;
         const uint64_t tp = s_tp[e];
         const uint32_t pos = (uint32_t)tp;
@@ -197,11 +198,12 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
 }  // namespace sa
 
 cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,
-                             uint32_t lprime, uint32_t* sa_out, unsigned long long* run_counter, uint32_t* err,
-                             cudaStream_t s)
+                             uint32_t lprime, uint32_t r_begin, uint32_t r_end, uint32_t* sa_out,
+                             unsigned long long* run_counter, uint32_t* err, cudaStream_t s)
 {
     if (!n) return cudaSuccess;
     const uint32_t blocks = (n + sa::FT - 1) / sa::FT;
-    sa::finish_kernel<<<blocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, sa_out, run_counter, err);
+    sa::finish_kernel<<<blocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, sa_out, run_counter,
+                                                      err);
     return cudaGetLastError();
 }

@@ -77,6 +77,13 @@ struct sa_index {
     DevBuf keys[2], vals[2], aux[2], lcp, tie, amask, hmask, counts, status, small, nl_counts;
     DevBuf codes;       // compressed-alphabet copy of the text (code_bits < 8), build scratch
     sa::CodeInfo code{8, 0x100u, 0x100u};
+    int cb0 = 8, max_chars = 8;   // suffix bytes in the round-0 key / per key word
+
+    // sharded (multi-GPU) build state, see sa_shard.cu
+    bool shard_prepared = false;
+    uint32_t shard_m = 0;          // records this rank sorts
+    uint32_t* shard_sa = nullptr;  // their positions in prefix order (points into vals[])
+    DevBuf ext_sa, ext_lcp, ext_out;
 
     // query scratch / results of the last batch
     DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
@@ -132,3 +139,10 @@ struct ScopedPhase {
 };
 
 int sa_build_resident(sa_index* idx, uint32_t flags);
+int sa_stage_prepare(sa_index* idx, uint32_t flags);
+const uint8_t* sa_key_source(const sa_index* idx);
+int sa_ensure_scratch(sa_index* idx, uint32_t m);
+int sa_stage_sort_refine(sa_index* idx, uint32_t m, bool identity, uint32_t** sa_sorted);
+int sa_stage_finish(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
+                    uint32_t r_end, uint32_t* out);
+int sa_check_device_error(sa_index* idx);

@@ -1,0 +1,360 @@
+// sa_shard.cu -- building ONE suffix array over several GPUs as a sample sort.
+//
+// One sa_index per GPU (one process per GPU); the text is replicated.  Rank g packs the round-0
+// keys of its slice of text positions, the ranks agree on splitters from the all-reduced
+// histogram of the keys' top 16 bits (so equal keys -- and therefore whole tied groups -- always
+// land on one rank), records are split by destination (stable, so every run stays in ascending
+// position order), exchanged with one all-to-all over NVLink (NCCL; done by the host side between
+// sa_shard_split and sa_shard_sort), and every rank then runs the ordinary pipeline on what it
+// received: LSD radix sort, tie refinement, and the <= 32 bucket finish -- the latter on its
+// records plus a 128-record halo from each neighbour, because ORDER-E's bucket depths d* depend on
+// the 32 ranks either side (sa_stage_finish places only the ranks it owns).  The final array is
+// the concatenation of the per-rank slices.
+//
+// The reference has no counterpart: its only split is the sequential 2 GiB partitioning into
+// independent indexes (suffix_array.pyx:148-180).
+#include <string.h>
+
+#include "sa_index.h"
+
+namespace sa {
+
+__global__ void iota_offset_kernel(uint32_t* __restrict__ out, uint32_t m, uint32_t first)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) out[i] = first + i;
+}
+
+// top-16-bit histogram of the keys (global reductions; the bins are far too many for shared memory)
+__global__ void hist16_kernel(const uint64_t* __restrict__ keys, uint32_t m, uint32_t* __restrict__ hist)
+{
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride)
+        atomicAdd(hist + (uint32_t)(ld_stream_u64(keys + i) >> 48), 1u);
+}
+
+constexpr int SPLIT_THREADS = 256, SPLIT_IPT = 8, SPLIT_TILE = SPLIT_THREADS * SPLIT_IPT, SPLIT_MAXR = 16;
+
+// counts[g * tiles + tile] = records of the tile whose destination is rank g
+__global__ void __launch_bounds__(SPLIT_THREADS)
+split_count_kernel(const uint64_t* __restrict__ keys, uint32_t m, const uint8_t* __restrict__ bin2rank, int nranks,
+                   uint32_t tiles, uint32_t* __restrict__ counts)
+{
+    __shared__ uint32_t s_cnt[SPLIT_MAXR];
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < SPLIT_MAXR) s_cnt[tid] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * SPLIT_TILE + (tid >> 5) * (32 * SPLIT_IPT) + lane;
+    uint32_t cnt[SPLIT_MAXR];
+#pragma unroll
+    for (int g = 0; g < SPLIT_MAXR; ++g) cnt[g] = 0;
+#pragma unroll
+    for (int i = 0; i < SPLIT_IPT; ++i) {
+        const uint32_t idx = base + i * 32;
+        const uint32_t d = idx < m ? bin2rank[(uint32_t)(ld_stream_u64(keys + idx) >> 48)] : 0xFFu;
+#pragma unroll
+        for (int g = 0; g < SPLIT_MAXR; ++g)
+            if (g < nranks) cnt[g] += __popc(__ballot_sync(0xffffffffu, d == (uint32_t)g));
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int g = 0; g < SPLIT_MAXR; ++g)
+            if (g < nranks && cnt[g]) atomicAdd(&s_cnt[g], cnt[g]);
+    }
+    __syncthreads();
+    if (tid < nranks) counts[(size_t)tid * tiles + blockIdx.x] = s_cnt[tid];
+}
+
+// offsets = exclusive scan of counts in (rank-major, tile-minor) order: stable scatter
+__global__ void __launch_bounds__(SPLIT_THREADS)
+split_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ pos, uint32_t m,
+                     const uint8_t* __restrict__ bin2rank, int nranks, uint32_t tiles,
+                     const uint32_t* __restrict__ offsets, uint64_t* __restrict__ keys_out,
+                     uint32_t* __restrict__ pos_out)
+{
+    constexpr int WARPS = SPLIT_THREADS / 32;
+    __shared__ uint32_t s_wcnt[WARPS][SPLIT_MAXR];
+    __shared__ uint32_t s_wbase[WARPS][SPLIT_MAXR];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lt = lanemask_lt();
+    const uint32_t base = blockIdx.x * SPLIT_TILE + warp * (32 * SPLIT_IPT) + lane;
+    uint64_t key[SPLIT_IPT];
+    uint32_t d[SPLIT_IPT], rk[SPLIT_IPT];
+    uint32_t cnt[SPLIT_MAXR];
+#pragma unroll
+    for (int g = 0; g < SPLIT_MAXR; ++g) cnt[g] = 0;
+#pragma unroll
+    for (int i = 0; i < SPLIT_IPT; ++i) {
+        const uint32_t idx = base + i * 32;
+        key[i] = idx < m ? ld_stream_u64(keys + idx) : 0ull;
+        d[i] = idx < m ? bin2rank[(uint32_t)(key[i] >> 48)] : 0xFFu;
+        rk[i] = 0;
+#pragma unroll
+        for (int g = 0; g < SPLIT_MAXR; ++g) {
+            if (g < nranks) {
+                const uint32_t b = __ballot_sync(0xffffffffu, d[i] == (uint32_t)g);
+                if (d[i] == (uint32_t)g) rk[i] = cnt[g] + __popc(b & lt);
+                cnt[g] += __popc(b);
+            }
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int g = 0; g < SPLIT_MAXR; ++g) s_wcnt[warp][g] = cnt[g];
+    }
+    __syncthreads();
+    if (tid < nranks) {
+        uint32_t run = offsets[(size_t)tid * tiles + blockIdx.x];
+        for (int w = 0; w < WARPS; ++w) { s_wbase[w][tid] = run; run += s_wcnt[w][tid]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < SPLIT_IPT; ++i) {
+        const uint32_t idx = base + i * 32;
+        if (idx < m) {
+            const uint32_t o = s_wbase[warp][d[i]] + rk[i];
+            keys_out[o] = key[i];
+            pos_out[o] = ld_stream_u32(pos + idx);
+        }
+    }
+}
+
+// ext arrays for the finish: [left halo | own | right halo]
+__global__ void ext_fill_kernel(const uint32_t* __restrict__ own_sa, const uint16_t* __restrict__ own_lcp, uint32_t m,
+                                const uint32_t* __restrict__ halo_pos, const uint16_t* __restrict__ halo_lcp,
+                                uint32_t nleft, uint32_t nright, uint32_t lcp_first, uint32_t* __restrict__ ext_sa,
+                                uint16_t* __restrict__ ext_lcp)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t total = nleft + m + nright;
+    if (i >= total) return;
+    if (i < nleft) {
+        ext_sa[i] = halo_pos[i];
+        ext_lcp[i] = halo_lcp[i];
+    } else if (i < nleft + m) {
+        const uint32_t j = i - nleft;
+        ext_sa[i] = own_sa[j];
+        ext_lcp[i] = j == 0 ? (uint16_t)lcp_first : own_lcp[j];
+    } else {
+        const uint32_t j = i - nleft - m;
+        ext_sa[i] = halo_pos[nleft + j];
+        ext_lcp[i] = halo_lcp[nleft + j];
+    }
+}
+
+}  // namespace sa
+
+#define SH_REQUIRE(cond, code, ...)            \
+    do {                                       \
+        if (!(cond)) {                         \
+            sa_set_error(__VA_ARGS__);         \
+            return (code);                     \
+        }                                      \
+    } while (0)
+
+// Upload the (replicated) text and run the preparation stage.  Replaces nothing in the reference.
+extern "C" int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, uint32_t flags)
+{
+    SH_REQUIRE(idx && (text || n == 0), SA_ERR_INVALID, "sa_shard_begin: NULL argument");
+    SH_REQUIRE(n > 0 && n < 0xFFFFFFFFull - 1024ull, SA_ERR_LIMIT, "sa_shard_begin: n out of range");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    idx->timing = (flags & SA_FLAG_TIMING) != 0;
+    idx->n = n;
+    idx->built = false;
+    idx->have_ranges = false;
+    idx->csv = false;
+    idx->shard_prepared = false;
+    memset(&idx->stats, 0, sizeof idx->stats);
+    idx->lprime = idx->L < n ? idx->L : (uint32_t)n;
+    idx->stats.n = n; idx->stats.max_suffix_length = idx->L; idx->stats.lprime = idx->lprime;
+    const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
+    SA_CU(idx->text.ensure(bytes));
+    const size_t pad_from = (size_t)n & ~(size_t)15;
+    SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + pad_from, 0, bytes - pad_from, s));
+    {
+        ScopedPhase ph(idx, &idx->stats.ms_h2d);
+        SA_CU(cudaMemcpyAsync(idx->text.p, text, n, cudaMemcpyHostToDevice, s));
+    }
+    int rc = sa_stage_prepare(idx, flags);
+    if (rc != SA_OK) return rc;
+    SH_REQUIRE(idx->lprime > 0, SA_ERR_INVALID, "sa_shard_begin: max_suffix_length 0 needs no sharded build");
+    idx->shard_prepared = true;
+    return SA_OK;
+}
+
+// Round-0 keys + positions of the suffixes in [pos_begin, pos_end) into caller-owned device
+// buffers; optionally accumulates the top-16-bit key histogram (65536 u32, caller zeroes it).
+extern "C" int sa_shard_pack(sa_index* idx, uint64_t pos_begin, uint64_t pos_end, uint64_t* d_keys, uint32_t* d_pos,
+                             uint32_t* d_hist16)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_pack: call sa_shard_begin first");
+    SH_REQUIRE(pos_begin <= pos_end && pos_end <= idx->n, SA_ERR_INVALID, "sa_shard_pack: bad slice");
+    SH_REQUIRE((pos_begin & 15) == 0, SA_ERR_INVALID, "sa_shard_pack: pos_begin must be a multiple of 16");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = (uint32_t)(pos_end - pos_begin);
+    if (m == 0) return SA_OK;
+    SH_REQUIRE(d_keys && d_pos, SA_ERR_INVALID, "sa_shard_pack: NULL buffer");
+    {
+        ScopedPhase ph(idx, &idx->stats.ms_pack);
+        SA_CU(sa_launch_pack0(sa_key_source(idx) + pos_begin, m, idx->cb0, idx->code, d_keys, s));
+        sa::iota_offset_kernel<<<(m + 255) / 256, 256, 0, s>>>(d_pos, m, (uint32_t)pos_begin);
+        if (d_hist16) sa::hist16_kernel<<<idx->num_sms * 8, 256, 0, s>>>(d_keys, m, d_hist16);
+        SA_CU(cudaGetLastError());
+        idx->stats.kernel_launches += d_hist16 ? 3 : 2;
+    }
+    SA_CU(cudaStreamSynchronize(s));
+    return SA_OK;
+}
+
+// Stable split of m records by destination rank = bin2rank[key >> 48] (host table, 65536 bytes).
+// Output: records grouped by destination in rank order; counts_out[g] = records for rank g.
+extern "C" int sa_shard_split(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m64,
+                              const uint8_t* bin2rank, int nranks, uint64_t* d_keys_out, uint32_t* d_pos_out,
+                              uint64_t* counts_out)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_split: call sa_shard_begin first");
+    SH_REQUIRE(bin2rank && counts_out, SA_ERR_INVALID, "sa_shard_split: NULL argument");
+    SH_REQUIRE(nranks >= 1 && nranks <= sa::SPLIT_MAXR, SA_ERR_LIMIT, "sa_shard_split: 1..16 ranks supported");
+    SH_REQUIRE(m64 < (1ull << 32), SA_ERR_LIMIT, "sa_shard_split: too many records");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = (uint32_t)m64;
+    for (int g = 0; g < nranks; ++g) counts_out[g] = 0;
+    if (m == 0) return SA_OK;
+    const uint32_t tiles = (m + sa::SPLIT_TILE - 1) / sa::SPLIT_TILE;
+    // scratch: table (64 KiB) + counts/offsets (nranks * tiles + 1 words), in the aux buffers
+    SA_CU(idx->aux[0].ensure(65536));
+    SA_CU(idx->aux[1].ensure(((size_t)nranks * tiles + 2) * sizeof(uint32_t)));
+    uint8_t* d_table = idx->aux[0].as<uint8_t>();
+    uint32_t* d_counts = idx->aux[1].as<uint32_t>();
+    uint32_t* sm = idx->small.as<uint32_t>();
+    SA_CU(cudaMemcpyAsync(d_table, bin2rank, 65536, cudaMemcpyHostToDevice, s));
+    sa::split_count_kernel<<<tiles, sa::SPLIT_THREADS, 0, s>>>(d_keys, m, d_table, nranks, tiles, d_counts);
+    SA_CU(cudaGetLastError());
+    SA_CU(sa_launch_scan_u32(d_counts, (uint32_t)nranks * tiles, sm + SM_NLTOTAL, s));
+    sa::split_scatter_kernel<<<tiles, sa::SPLIT_THREADS, 0, s>>>(d_keys, d_pos, m, d_table, nranks, tiles, d_counts,
+                                                                 d_keys_out, d_pos_out);
+    SA_CU(cudaGetLastError());
+    idx->stats.kernel_launches += 3;
+    // per-rank totals = differences of the scanned offsets at tile 0 of each rank
+    std::vector<uint32_t> first((size_t)nranks + 1, 0);
+    for (int g = 0; g < nranks; ++g)
+        SA_CU(cudaMemcpyAsync(&first[g], d_counts + (size_t)g * tiles, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaStreamSynchronize(s));
+    first[nranks] = m;
+    for (int g = 0; g < nranks; ++g) counts_out[g] = first[g + 1] - first[g];
+    return SA_OK;
+}
+
+// Sort + refine the m records this rank received (device buffers, runs in ascending position
+// order per source rank, sources in rank order).
+extern "C" int sa_shard_sort(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m64)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_sort: call sa_shard_begin first");
+    SH_REQUIRE(m64 < (1ull << 30), SA_ERR_LIMIT, "sa_shard_sort: %llu records exceed the 2^30 per-GPU limit",
+               (unsigned long long)m64);
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = (uint32_t)m64;
+    idx->shard_m = m;
+    idx->shard_sa = nullptr;
+    if (m == 0) return SA_OK;
+    int rc = sa_ensure_scratch(idx, m);
+    if (rc != SA_OK) return rc;
+    SA_CU(cudaMemcpyAsync(idx->keys[0].p, d_keys, (size_t)m * 8, cudaMemcpyDeviceToDevice, s));
+    SA_CU(cudaMemcpyAsync(idx->vals[0].p, d_pos, (size_t)m * 4, cudaMemcpyDeviceToDevice, s));
+    rc = sa_stage_sort_refine(idx, m, false, &idx->shard_sa);
+    if (rc != SA_OK) return rc;
+    SA_CU(cudaStreamSynchronize(s));
+    return SA_OK;
+}
+
+// First and last min(edge, m) records (position + adjacent LCP) of the sorted shard, to the host.
+extern "C" int sa_shard_edges(sa_index* idx, uint32_t edge, uint32_t* head_pos, uint16_t* head_lcp,
+                              uint32_t* tail_pos, uint16_t* tail_lcp)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_edges: no sorted shard");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = idx->shard_m, k = edge < m ? edge : m;
+    if (k == 0) return SA_OK;
+    const uint16_t* lcp = idx->lcp.as<uint16_t>();
+    SA_CU(cudaMemcpyAsync(head_pos, idx->shard_sa, (size_t)k * 4, cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaMemcpyAsync(head_lcp, lcp, (size_t)k * 2, cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaMemcpyAsync(tail_pos, idx->shard_sa + (m - k), (size_t)k * 4, cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaMemcpyAsync(tail_lcp, lcp + (m - k), (size_t)k * 2, cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaStreamSynchronize(s));
+    return SA_OK;
+}
+
+// Finish the shard with its halos.  left_*: the nleft records that precede this shard in the
+// global order (left_lcp[0] is ignored), lcp_first = LCP(last left record, first own record);
+// right_*: the nright records that follow (right_lcp[0] = LCP(last own record, first right record)).
+// The m placed positions go to d_sa_out (device).
+extern "C" int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
+                               uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp,
+                               uint32_t nright, uint32_t* d_sa_out)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_finish: no sorted shard");
+    SH_REQUIRE(nleft <= 4096 && nright <= 4096, SA_ERR_LIMIT, "sa_shard_finish: halo too large");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = idx->shard_m;
+    if (m == 0) return SA_OK;
+    SH_REQUIRE(d_sa_out, SA_ERR_INVALID, "sa_shard_finish: d_sa_out is NULL");
+    const uint32_t total = nleft + m + nright;
+    SA_CU(idx->ext_sa.ensure((size_t)total * 4));
+    SA_CU(idx->ext_lcp.ensure((size_t)total * 2 + 64));
+    SA_CU(idx->ext_out.ensure((size_t)total * 4));
+    // halo records: pinned staging is overkill for <= 8192 records; a pageable copy is synchronous
+    const uint32_t nh = nleft + nright;
+    SA_CU(idx->aux[0].ensure((size_t)(nh + 1) * 4));
+    SA_CU(idx->aux[1].ensure((size_t)(nh + 1) * 2));
+    if (nleft) {
+        SA_CU(cudaMemcpyAsync(idx->aux[0].p, left_pos, (size_t)nleft * 4, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaMemcpyAsync(idx->aux[1].p, left_lcp, (size_t)nleft * 2, cudaMemcpyHostToDevice, s));
+    }
+    if (nright) {
+        SA_CU(cudaMemcpyAsync(idx->aux[0].as<uint32_t>() + nleft, right_pos, (size_t)nright * 4, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaMemcpyAsync(idx->aux[1].as<uint16_t>() + nleft, right_lcp, (size_t)nright * 2, cudaMemcpyHostToDevice, s));
+    }
+    sa::ext_fill_kernel<<<(total + 255) / 256, 256, 0, s>>>(idx->shard_sa, idx->lcp.as<uint16_t>(), m,
+                                                            idx->aux[0].as<uint32_t>(), idx->aux[1].as<uint16_t>(), nleft,
+                                                            nright, lcp_first, idx->ext_sa.as<uint32_t>(),
+                                                            idx->ext_lcp.as<uint16_t>());
+    SA_CU(cudaGetLastError());
+    idx->stats.kernel_launches += 1;
+    const uint32_t r_begin = nleft - (nleft < 32 ? nleft : 32);
+    const uint32_t r_end = nleft + m + (nright < 32 ? nright : 32);
+    int rc = sa_stage_finish(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end,
+                             idx->ext_out.as<uint32_t>());
+    if (rc != SA_OK) return rc;
+    SA_CU(cudaMemcpyAsync(d_sa_out, idx->ext_out.as<uint32_t>() + nleft, (size_t)m * 4, cudaMemcpyDeviceToDevice, s));
+    rc = sa_check_device_error(idx);
+    sa_time_collect(idx);
+    return rc;
+}
+
+// Install a complete suffix array (n entries, e.g. the all-gathered shard outputs) so that the
+// index answers queries: every rank then holds text + SA and takes a share of each query batch.
+extern "C" int sa_adopt_sa(sa_index* idx, const uint32_t* d_sa_full, uint64_t n)
+{
+    SH_REQUIRE(idx && d_sa_full, SA_ERR_INVALID, "sa_adopt_sa: NULL argument");
+    SH_REQUIRE(idx->shard_prepared && n == idx->n, SA_ERR_INVALID, "sa_adopt_sa: the index holds no text of %llu bytes",
+               (unsigned long long)n);
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    SA_CU(idx->sa_final.ensure((size_t)n * 4));
+    SA_CU(cudaMemcpyAsync(idx->sa_final.p, d_sa_full, (size_t)n * 4, cudaMemcpyDeviceToDevice, idx->stream));
+    SA_CU(cudaStreamSynchronize(idx->stream));
+    idx->built = true;
+    return SA_OK;
+}

@@ -1,0 +1,63 @@
+"""The multi-GPU sample-sort build, emulated rank by rank on ONE GPU (collectives = tensor copies),
+must give the oracle's suffix array bit for bit; plus CPU checks of the host logic."""
+import numpy as np
+import pytest
+
+from conftest import random_text
+from oracle import pyoracle as O
+from suffixarray_b200 import sharded as SH
+from suffixarray_b200 import workloads as W
+
+
+def test_slice_bounds_and_splitters():
+    b = SH.slice_bounds(1000, 4)
+    assert b[0] == 0 and b[-1] == 1000 and all(x % 16 == 0 for x in b[:-1]) and b == sorted(b)
+    rng = np.random.default_rng(1)
+    hist = rng.integers(0, 50, SH.NBINS)
+    hist[1234] = 40000                                   # one heavy bin stays whole
+    t = SH.choose_bin2rank(hist, 8)
+    assert (np.diff(t.astype(int)) >= 0).all() and t.min() == 0 and t.max() == 7
+    share = np.bincount(t, weights=hist, minlength=8)
+    assert share.max() <= hist.sum() / 8 + 40000 + 50
+
+
+def test_boundary_lcp_rules():
+    t = np.frombuffer(b"abcd\nxyz abcd\nqqq abcx", np.uint8)
+    assert SH.boundary_lcp(t, 0, 9, 32, False) == 32      # equal through the newline: tied for good
+    assert SH.boundary_lcp(t, 0, 18, 32, False) == 3
+    assert SH.boundary_lcp(t, 0, 18, 2, False) == 2       # capped at L'
+    assert SH.boundary_lcp(np.frombuffer(b"ABc abC", np.uint8), 0, 4, 8, True) == 3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_emulated_ranks_match_oracle(world):
+    rng = np.random.default_rng(50 + world)
+    cases = [
+        (W.english_documents(300_000, seed=41), 32, False),
+        (W.company_names_joined(30_000, seed=42, upper=True)[0], 32, True),
+        (random_text(rng, 50_000, 2, newline_p=0.02), 16, False),
+        (random_text(rng, 20_000, 26), 64, False),
+        (rng.integers(0, 256, 30_000).astype(np.uint8), 32, False),       # raw-byte keys (code_bits 8)
+        (np.full(5000, ord("a"), np.uint8), 32, False),                   # everything lands on one rank
+        (random_text(rng, 700, 3), 8, False),                             # shards smaller than the halo
+        (random_text(rng, 40, 2), 32, False),
+    ]
+    for text, L, lower in cases:
+        full, ranks = SH.build_emulated(text, L, world, lowercase=lower)
+        want_text = O.oracle_lowercase(text) if lower else text
+        want = O.oracle_build(want_text, L)
+        got = full.cpu().numpy().astype(np.uint32)
+        assert got.size == want.size
+        if not np.array_equal(want, got):
+            bad = np.flatnonzero(want != got)
+            ms = [r.m for r in ranks]
+            raise AssertionError(f"world={world} n={text.size} L={L}: {bad.size} ranks differ, first {bad[:8]} shard sizes {ms}")
+        # every rank answers queries on the adopted array exactly like a single-GPU index
+        qs = [bytes(want_text[p:p + 5]).split(b"\n")[0] or b"a" for p in rng.integers(0, max(1, text.size - 5), 20)]
+        ws, we = O.oracle_query(want_text, want, L, qs)
+        for r in ranks[:2]:
+            s, e, _ = r.idx.query_ranges(qs)
+            assert np.array_equal(s, ws) and np.array_equal(e, we)
+        for r in ranks:
+            r.close()
