@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--max-suffix-length", type=int, default=L_DEFAULT)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="global", choices=["global", "partition"],
+                    help="N > 1: one global index built as a sample sort (default) or one independent "
+                         "partition per GPU (the reference's own partitioning, suffix_array.pyx:148-180)")
     return ap.parse_args()
 
 
@@ -180,6 +183,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     S.lib()   # fail loudly when the extension is missing
     L = args.max_suffix_length
+    if world > 1 and args.mode == "global":
+        return run_ours_global(args, world, rank, local)
 
     text, qbytes, qoff, lower = make_workload(args.workload, rank)
     n, nq = int(text.size), int(qoff.size - 1)
@@ -284,6 +289,131 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    return result
+
+
+def run_ours_global(args, world, rank, local):
+    """N > 1: ONE index over the concatenation of the N per-rank workload texts (weak scaling of a
+    single global index), built as a sample sort with an NCCL all-to-all; every rank then answers
+    its own query batch against the adopted (replicated) array."""
+    import torch
+    import torch.distributed as dist
+    from suffixarray_b200 import _lib as S
+    from suffixarray_b200 import sharded as SH
+
+    L = args.max_suffix_length
+    dev = torch.device("cuda", local)
+    text_r, qbytes, qoff, lower = make_workload(args.workload, rank)
+    # all ranks need the whole text: all-gather the per-rank partitions (joined by '\n')
+    part = np.concatenate([text_r, np.frombuffer(b"\n", np.uint8)]) if rank < world - 1 else text_r
+    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(sizes, torch.tensor([part.size], dtype=torch.int64, device=dev))
+    sizes = [int(x.item()) for x in sizes]
+    mx = max(sizes)
+    pad = torch.zeros(mx, dtype=torch.uint8, device=dev)
+    pad[: part.size] = torch.from_numpy(part).to(dev)
+    allp = torch.empty(world * mx, dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(allp, pad)
+    d_text = torch.cat([allp[g * mx: g * mx + sizes[g]] for g in range(world)]).contiguous()
+    del allp, pad
+    h_text_t = d_text.cpu().pin_memory()
+    h_text = h_text_t.numpy()
+    n = int(h_text.size)
+    nq = int(qoff.size - 1)
+    h_q = torch.from_numpy(qbytes).pin_memory()
+    h_qoff = torch.from_numpy(qoff.view(np.int64)).pin_memory()
+    h_start = torch.empty(nq, dtype=torch.int32, pin_memory=True)
+    h_end = torch.empty(nq, dtype=torch.int32, pin_memory=True)
+    h_hoff = torch.empty(nq + 1, dtype=torch.int64, pin_memory=True)
+    hits = {"doc": None, "pos": None, "cap": 0}
+    lib, vp = S.lib(), S._vp
+    builders = {"dev": None, "e2e": None}
+
+    def build(kind):
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        b, phases = SH.build_distributed(h_text, L, local, lowercase=lower, timing=True,
+                                         device_text=d_text if kind == "dev" else None, builder=builders[kind])
+        builders[kind] = b
+        torch.cuda.synchronize()
+        return b, (time.perf_counter() - t0) * 1e3, phases
+
+    def step():
+        r = {}
+        b, r["build_dev_ms"], r["phases"] = build("dev")
+        st = b.idx.stats()
+        r["onesweep_ms"], r["onesweep_launches"], r["onesweep_elems"] = st["ms_onesweep_sum"], st["radix_passes"], st["onesweep_elems"]
+        r["build_launches"] = st["kernel_launches"]
+        r["rounds"], r["m"], r["exchange_bytes"] = st["rounds"], b.m, b.exchange_bytes
+        b2, r["build_e2e_ms"], _ = build("e2e")
+        r["build_launches"] += b2.idx.stats()["kernel_launches"]
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        S.check(lib.sa_query_ranges(b2.idx._h, vp(h_q.data_ptr()), vp(h_qoff.data_ptr()), nq, K_HITS,
+                                    vp(h_start.data_ptr()), vp(h_end.data_ptr()), vp(h_hoff.data_ptr())))
+        total = int(h_hoff[nq])
+        if total > hits["cap"]:
+            hits["cap"] = int(total * 1.1) + 1024
+            hits["pos"] = torch.empty(hits["cap"], dtype=torch.int32, pin_memory=True)
+            hits["doc"] = torch.empty(hits["cap"], dtype=torch.int32, pin_memory=True)
+        S.check(lib.sa_query_hits(b2.idx._h, vp(hits["pos"].data_ptr()), vp(hits["doc"].data_ptr()), hits["cap"]))
+        torch.cuda.synchronize()
+        r["query_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        st = b2.idx.stats()
+        r["query_dev_ms"] = st["ms_query"] + st["ms_hits"]
+        r["query_kernel_ms"] = st["ms_query"]
+        r["query_launches"] = st["kernel_launches"]
+        r["hits"] = total
+        return r
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dist.barrier()
+    torch.cuda.synchronize()
+    t_wall0 = time.perf_counter()
+    recs = [step() for _ in range(args.steps)]
+    dist.barrier()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+    K = args.steps
+    phase_names = list(recs[-1]["phases"].keys())
+    sums = torch.tensor([sum(r["build_dev_ms"] for r in recs), sum(r["query_dev_ms"] for r in recs),
+                         sum(r["build_e2e_ms"] for r in recs), sum(r["query_e2e_ms"] for r in recs), wall_ms] +
+                        [sum(r["phases"][p] for r in recs) for p in phase_names], dtype=torch.float64, device=dev)
+    dist.all_reduce(sums, op=dist.ReduceOp.MAX)
+    ms = torch.tensor([float(recs[-1]["m"]), float(recs[-1]["exchange_bytes"])], dtype=torch.float64, device=dev)
+    ms_all = [torch.zeros_like(ms) for _ in range(world)]
+    dist.all_gather(ms_all, ms)
+    result = None
+    if rank == 0:
+        build_ms, query_ms, build_e2e_ms, query_e2e_ms = (sums[:4] / K).tolist()
+        phases = {p: round(v / K, 3) for p, v in zip(phase_names, sums[5:].tolist())}
+        result = assemble(args, world, recs, n // world, nq, float(n), float(nq * world), build_ms, query_ms,
+                          build_e2e_ms, query_e2e_ms, sums[4].item(), clocks, qbytes.size, None, None, None, lower)
+        result["e2e"]["h2d_bytes_per_step"] = int(n + qbytes.size + (nq + 1) * 8)     # per rank: the replicated text
+        shard_sizes = [int(x[0].item()) for x in ms_all]
+        xbytes = [int(x[1].item()) for x in ms_all]
+        xms = phases.get("exchange", 0.0)
+        result["config"]["sharding"] = ("one global index over the N concatenated partitions: sample sort, splitters from "
+                                        "the all-reduced 65536-bin key histogram, NCCL all-to-all of (key, pos) records, "
+                                        "128-record halos for the bucket finish, all-gather of the slices")
+        result["config"]["n_chars_total"] = n
+        result["timing"] = "wall clock between barrier + cudaDeviceSynchronize pairs, max over ranks (the build is host-driven across collectives)"
+        result["multi_gpu"] = {"phases_ms_max_over_ranks": phases, "shard_records": shard_sizes,
+                               "imbalance": round(max(shard_sizes) * world / max(sum(shard_sizes), 1), 4),
+                               "exchange_bytes_sent_per_rank": xbytes,
+                               "exchange_gbs_per_rank": round(max(xbytes) / (xms * 1e-3) / 1e9, 1) if xms > 0 else None,
+                               "nvlink_peak_gbs_per_direction": 770.0}
+    for b in builders.values():
+        if b is not None:
+            b.close()
+    dist.barrier()
+    dist.destroy_process_group()
     return result
 
 

@@ -38,6 +38,7 @@ typedef enum sa_status {
 #define SA_FLAG_LOWERCASE 1u   /* ASCII A-Z -> a-z on the device copy of the text: replaces
                                   lowercase_string, suffix_array.pyx:103-107 */
 #define SA_FLAG_TIMING    2u   /* record per-phase CUDA-event times into sa_stats */
+#define SA_FLAG_DEVICE_TEXT 4u /* sa_shard_begin: `text` is a device pointer (copied device to device) */
 
 /* Opaque index: owns the device text, the SA, the doc-offset table and all scratch.
  * Replaces SuffixArray_struct (engine.h:123-130) / SuffixArrayIndex (engine.h:163-172). */

@@ -19,6 +19,7 @@ CSRC = os.path.join(_HERE, "csrc")
 SA_OK = 0
 SA_FLAG_LOWERCASE = 1
 SA_FLAG_TIMING = 2
+SA_FLAG_DEVICE_TEXT = 4
 UINT32_MAX = 0xFFFFFFFF
 
 # every symbol include/sa_cuda.h declares (checked by tests/test_abi.py)

@@ -175,7 +175,8 @@ extern "C" int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, ui
     SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + pad_from, 0, bytes - pad_from, s));
     {
         ScopedPhase ph(idx, &idx->stats.ms_h2d);
-        SA_CU(cudaMemcpyAsync(idx->text.p, text, n, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaMemcpyAsync(idx->text.p, text, n,
+                              (flags & SA_FLAG_DEVICE_TEXT) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
     }
     int rc = sa_stage_prepare(idx, flags);
     if (rc != SA_OK) return rc;

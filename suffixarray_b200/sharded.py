@@ -139,21 +139,32 @@ class ShardBuilder:
     """The per-rank phases.  Buffers that cross a collective are torch CUDA tensors."""
 
     def __init__(self, text: np.ndarray, max_suffix_length: int, rank: int, world: int, device: int,
-                 lowercase: bool = False, timing: bool = False):
+                 lowercase: bool = False, timing: bool = False, device_text=None):
+        """text: the whole text on the host (also used for the few boundary LCPs); device_text: an
+        optional torch CUDA uint8 tensor holding the same bytes, to skip the host-to-device copy."""
         import torch
         self.torch = torch
-        self.text = np.ascontiguousarray(text, dtype=np.uint8)
-        self.n = int(self.text.size)
         self.rank, self.world, self.device = rank, world, device
-        self.lowercase = lowercase
         self.L = int(max_suffix_length)
-        self.lprime = min(self.L, self.n)
         self.dev = torch.device("cuda", device)
         self.idx = S.Index(self.L, device=device)
+        self.begin(text, lowercase, timing, device_text)
+
+    def begin(self, text: np.ndarray, lowercase: bool = False, timing: bool = False, device_text=None):
+        """(Re)start a build on this rank's index; scratch from an earlier build is reused."""
+        self.text = np.ascontiguousarray(text, dtype=np.uint8)
+        self.n = int(self.text.size)
+        self.lowercase = lowercase
+        self.lprime = min(self.L, self.n)
         flags = (S.SA_FLAG_LOWERCASE if lowercase else 0) | (S.SA_FLAG_TIMING if timing else 0)
-        S.check(S.lib().sa_shard_begin(self.idx._h, self.text.ctypes.data_as(S._vp), self.n, flags))
-        b = slice_bounds(self.n, world)
-        self.pos_begin, self.pos_end = b[rank], b[rank + 1]
+        if device_text is not None:
+            assert device_text.numel() == self.n and device_text.is_cuda
+            S.check(S.lib().sa_shard_begin(self.idx._h, S._vp(device_text.data_ptr()), self.n,
+                                           flags | S.SA_FLAG_DEVICE_TEXT))
+        else:
+            S.check(S.lib().sa_shard_begin(self.idx._h, self.text.ctypes.data_as(S._vp), self.n, flags))
+        b = slice_bounds(self.n, self.world)
+        self.pos_begin, self.pos_end = b[self.rank], b[self.rank + 1]
         self.m_local = self.pos_end - self.pos_begin
 
     def _p(self, t):
@@ -272,7 +283,7 @@ def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lo
 
 
 def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool = False, timing: bool = False,
-                      adopt: bool = True, group=None):
+                      adopt: bool = True, group=None, device_text=None, builder=None):
     """This process's rank of the sample-sort build under torch.distributed (NCCL).
     -> (ShardBuilder with the complete SA adopted, dict of per-phase wall times in ms)."""
     import time
@@ -291,7 +302,11 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
         t[name] = (now - t0) * 1e3
         t0 = now
 
-    r = ShardBuilder(text, max_suffix_length, rank, world, device, lowercase, timing)
+    if builder is None:
+        r = ShardBuilder(text, max_suffix_length, rank, world, device, lowercase, timing, device_text)
+    else:
+        r = builder
+        r.begin(text, lowercase, timing, device_text)
     lap("begin")
     hist = r.pack().to(torch.int64)
     dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
