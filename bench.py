@@ -65,6 +65,8 @@ def parse_args():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--max-suffix-length", type=int, default=L_DEFAULT)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="global mode: fused split + peer stores through CUDA IPC (default) or split + NCCL all-to-all")
     ap.add_argument("--mode", default="global", choices=["global", "partition"],
                     help="N > 1: one global index built as a sample sort (default) or one independent "
                          "partition per GPU (the reference's own partitioning, suffix_array.pyx:148-180)")
@@ -334,7 +336,8 @@ def run_ours_global(args, world, rank, local):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         b, phases = SH.build_distributed(h_text, L, local, lowercase=lower, timing=True,
-                                         device_text=d_text if kind == "dev" else None, builder=builders[kind])
+                                         device_text=d_text if kind == "dev" else None, builder=builders[kind],
+                                         exchange=args.exchange)
         builders[kind] = b
         torch.cuda.synchronize()
         return b, (time.perf_counter() - t0) * 1e3, phases
@@ -402,6 +405,9 @@ def run_ours_global(args, world, rank, local):
         result["config"]["sharding"] = ("one global index over the N concatenated partitions: sample sort, splitters from "
                                         "the all-reduced 65536-bin key histogram, NCCL all-to-all of (key, pos) records, "
                                         "128-record halos for the bucket finish, all-gather of the slices")
+        result["config"]["exchange"] = ("split kernel stores records straight into the destination GPU's sort buffers "
+                                        "(CUDA IPC peer stores over NVLink)" if args.exchange == "p2p"
+                                        else "split into send buffers + NCCL all_to_all_single")
         result["config"]["n_chars_total"] = n
         result["timing"] = "wall clock between barrier + cudaDeviceSynchronize pairs, max over ranks (the build is host-driven across collectives)"
         result["multi_gpu"] = {"phases_ms_max_over_ranks": phases, "shard_records": shard_sizes,

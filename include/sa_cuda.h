@@ -140,6 +140,17 @@ int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const uint16_t* lef
                     uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp, uint32_t nright,
                     uint32_t* d_sa_out);
 int sa_adopt_sa(sa_index* idx, const uint32_t* d_sa_full, uint64_t n);
+/* Fused split + exchange for ranks on one node: instead of sa_shard_split + NCCL all-to-all, the
+ * split kernel stores every record straight into its destination rank's sort buffers, mapped
+ * through CUDA IPC (peer stores over NVLink).  sa_shard_count -> all-gather of the counts ->
+ * sa_shard_recv_prepare (exports two 64-byte handles) -> all-gather of the handles ->
+ * sa_shard_scatter_p2p -> barrier -> sa_shard_sort_recv. */
+int sa_shard_count(sa_index* idx, const uint64_t* d_keys, uint64_t m, const uint8_t* bin2rank, int nranks,
+                   uint64_t* counts_out);
+int sa_shard_recv_prepare(sa_index* idx, uint64_t m_recv, uint8_t* handle_keys, uint8_t* handle_pos);
+int sa_shard_scatter_p2p(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m, int nranks,
+                         int my_rank, const uint8_t* handles, const uint64_t* dst_offset);
+int sa_shard_sort_recv(sa_index* idx, uint64_t m);
 
 /* Debug / parity hooks (used by tests to localise a mismatch; not part of the drop-in). */
 int sa_debug_copy_lcp(sa_index* idx, uint16_t* out, uint64_t cap);

@@ -30,11 +30,13 @@ cases = [
 ]
 ok = True
 builder = None
-for name, text, L, lower in cases:
+for name, text, L, lower in [c for c in cases for _ in (0, 1)]:
+    exchange = "nccl" if getattr(builder, "_last", None) == (name, "p2p") else "p2p"
     if builder is not None and builder.L != L:
         builder.close()
         builder = None
-    builder, phases = SH.build_distributed(text, L, local, lowercase=lower, builder=builder)
+    builder, phases = SH.build_distributed(text, L, local, lowercase=lower, builder=builder, exchange=exchange)
+    builder._last = (name, exchange)
     got = builder.idx.sa()
     want_text = O.oracle_lowercase(text) if lower else text
     want = O.oracle_build(want_text, L)
@@ -42,7 +44,7 @@ for name, text, L, lower in cases:
     flags = torch.tensor([int(same)], device="cuda")
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print(f"{name}: n={text.size} world={world} shard m={builder.m} -> {'OK' if flags.item() else 'MISMATCH'}  "
+        print(f"{name} [{exchange}]: n={text.size} world={world} shard m={builder.m} -> {'OK' if flags.item() else 'MISMATCH'}  "
               + " ".join(f"{k}={v:.1f}ms" for k, v in phases.items()), flush=True)
     ok = ok and bool(flags.item())
 builder.close()

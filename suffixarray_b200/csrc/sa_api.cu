@@ -159,6 +159,7 @@ extern "C" int sa_debug_set(sa_index* idx, const char* key, int64_t value)
     else if (!strcmp(key, "skip_finish")) idx->dbg_skip_finish = value;
     else if (!strcmp(key, "force_gbits")) idx->dbg_force_gbits = value;
     else if (!strcmp(key, "code_bits")) idx->dbg_code_bits = value;
+    else if (!strcmp(key, "same_process")) idx->dbg_same_process = value;
     else { sa_set_error("unknown debug key %s", key); return SA_ERR_INVALID; }
     return SA_OK;
 }

@@ -83,7 +83,12 @@ struct sa_index {
     bool shard_prepared = false;
     uint32_t shard_m = 0;          // records this rank sorts
     uint32_t* shard_sa = nullptr;  // their positions in prefix order (points into vals[])
-    DevBuf ext_sa, ext_lcp, ext_out;
+    DevBuf ext_sa, ext_lcp, ext_out, split_table, split_offsets;
+    // peers' receive buffers (their keys[0] / vals[0]) mapped through CUDA IPC for the fused split + exchange
+    void* peer_keys[16] = {};
+    void* peer_pos[16] = {};
+    cudaIpcMemHandle_t peer_hk[16] = {}, peer_hp[16] = {};
+    bool peer_mapped[16] = {};
 
     // query scratch / results of the last batch
     DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
@@ -102,6 +107,7 @@ struct sa_index {
     int64_t dbg_max_rounds = -1;    // stop refining after this many rounds (-1: no limit)
     int64_t dbg_skip_finish = 0;    // leave the phase-1 order (no <=32 bucket step)
     int64_t dbg_force_gbits = 0;    // use at least this many group-id bits (exercises small cb)
+    int64_t dbg_same_process = 0;   // sharded build: peers live in this process (raw pointers instead of IPC)
     int64_t dbg_code_bits = -1;     // -1: choose from the alphabet; 8: never compress; 1..7: at least this width
 };
 

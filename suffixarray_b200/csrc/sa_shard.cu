@@ -25,12 +25,15 @@ __global__ void iota_offset_kernel(uint32_t* __restrict__ out, uint32_t m, uint3
     if (i < m) out[i] = first + i;
 }
 
-// top-16-bit histogram of the keys (global reductions; the bins are far too many for shared memory)
+// top-16-bit histogram of every HIST_STRIDE-th key (global reductions; the bins are far too many
+// for shared memory, and a 1-in-16 sample balances the shards to well under a percent)
+constexpr uint32_t HIST_STRIDE = 16;
 __global__ void hist16_kernel(const uint64_t* __restrict__ keys, uint32_t m, uint32_t* __restrict__ hist)
 {
     const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride)
-        atomicAdd(hist + (uint32_t)(ld_stream_u64(keys + i) >> 48), 1u);
+    const uint32_t ms = (m + HIST_STRIDE - 1) / HIST_STRIDE;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ms; i += stride)
+        atomicAdd(hist + (uint32_t)(__ldg(keys + (size_t)i * HIST_STRIDE) >> 48), 1u);
 }
 
 constexpr int SPLIT_THREADS = 256, SPLIT_IPT = 8, SPLIT_TILE = SPLIT_THREADS * SPLIT_IPT, SPLIT_MAXR = 16;
@@ -115,6 +118,72 @@ split_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restri
             const uint32_t o = s_wbase[warp][d[i]] + rk[i];
             keys_out[o] = key[i];
             pos_out[o] = ld_stream_u32(pos + idx);
+        }
+    }
+}
+
+// Fused split + exchange: the same stable split, but every record is stored straight into its
+// destination rank's receive buffer (that rank's keys[0] / vals[0], mapped through CUDA IPC), so the
+// transfer over NVLink happens inside the scatter, tile by tile.  dst[g] = receive-buffer pointers
+// of rank g already advanced to where this rank's run starts there.
+struct PeerTable {
+    uint64_t* keys[SPLIT_MAXR];
+    uint32_t* pos[SPLIT_MAXR];
+    uint32_t first[SPLIT_MAXR];      // offsets[g * tiles] of the local scan (start of the rank-g run)
+};
+
+__global__ void __launch_bounds__(SPLIT_THREADS)
+split_scatter_p2p_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ pos, uint32_t m,
+                         const uint8_t* __restrict__ bin2rank, int nranks, uint32_t tiles,
+                         const uint32_t* __restrict__ offsets, PeerTable pt)
+{
+    constexpr int WARPS = SPLIT_THREADS / 32;
+    __shared__ uint32_t s_wcnt[WARPS][SPLIT_MAXR];
+    __shared__ uint32_t s_wbase[WARPS][SPLIT_MAXR];
+    __shared__ uint64_t* s_k[SPLIT_MAXR];
+    __shared__ uint32_t* s_p[SPLIT_MAXR];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < SPLIT_MAXR) { s_k[tid] = pt.keys[tid]; s_p[tid] = pt.pos[tid]; }
+    const uint32_t lt = lanemask_lt();
+    const uint32_t base = blockIdx.x * SPLIT_TILE + warp * (32 * SPLIT_IPT) + lane;
+    uint64_t key[SPLIT_IPT];
+    uint32_t d[SPLIT_IPT], rk[SPLIT_IPT];
+    uint32_t cnt[SPLIT_MAXR];
+#pragma unroll
+    for (int g = 0; g < SPLIT_MAXR; ++g) cnt[g] = 0;
+#pragma unroll
+    for (int i = 0; i < SPLIT_IPT; ++i) {
+        const uint32_t idx = base + i * 32;
+        key[i] = idx < m ? ld_stream_u64(keys + idx) : 0ull;
+        d[i] = idx < m ? bin2rank[(uint32_t)(key[i] >> 48)] : 0xFFu;
+        rk[i] = 0;
+#pragma unroll
+        for (int g = 0; g < SPLIT_MAXR; ++g) {
+            if (g < nranks) {
+                const uint32_t b = __ballot_sync(0xffffffffu, d[i] == (uint32_t)g);
+                if (d[i] == (uint32_t)g) rk[i] = cnt[g] + __popc(b & lt);
+                cnt[g] += __popc(b);
+            }
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int g = 0; g < SPLIT_MAXR; ++g) s_wcnt[warp][g] = cnt[g];
+    }
+    __syncthreads();
+    if (tid < nranks) {
+        // position inside the run this rank sends to rank `tid`
+        uint32_t run = offsets[(size_t)tid * tiles + blockIdx.x] - pt.first[tid];
+        for (int w = 0; w < WARPS; ++w) { s_wbase[w][tid] = run; run += s_wcnt[w][tid]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < SPLIT_IPT; ++i) {
+        const uint32_t idx = base + i * 32;
+        if (idx < m) {
+            const uint32_t o = s_wbase[warp][d[i]] + rk[i];
+            s_k[d[i]][o] = key[i];
+            s_p[d[i]][o] = ld_stream_u32(pos + idx);
         }
     }
 }
@@ -357,5 +426,145 @@ extern "C" int sa_adopt_sa(sa_index* idx, const uint32_t* d_sa_full, uint64_t n)
     SA_CU(cudaMemcpyAsync(idx->sa_final.p, d_sa_full, (size_t)n * 4, cudaMemcpyDeviceToDevice, idx->stream));
     SA_CU(cudaStreamSynchronize(idx->stream));
     idx->built = true;
+    return SA_OK;
+}
+
+// ------------------------------------------------------------------------------ fused split + exchange (CUDA IPC)
+// 1. sa_shard_count: how many local records go to each rank (counts_out[nranks]); the scanned
+//    per-tile offsets stay on the device for step 3.
+extern "C" int sa_shard_count(sa_index* idx, const uint64_t* d_keys, uint64_t m64, const uint8_t* bin2rank, int nranks,
+                              uint64_t* counts_out)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_count: call sa_shard_begin first");
+    SH_REQUIRE(bin2rank && counts_out, SA_ERR_INVALID, "sa_shard_count: NULL argument");
+    SH_REQUIRE(nranks >= 1 && nranks <= sa::SPLIT_MAXR, SA_ERR_LIMIT, "sa_shard_count: 1..16 ranks supported");
+    SH_REQUIRE(m64 < (1ull << 32), SA_ERR_LIMIT, "sa_shard_count: too many records");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = (uint32_t)m64;
+    for (int g = 0; g < nranks; ++g) counts_out[g] = 0;
+    if (m == 0) return SA_OK;
+    const uint32_t tiles = (m + sa::SPLIT_TILE - 1) / sa::SPLIT_TILE;
+    SA_CU(idx->split_table.ensure(65536));
+    SA_CU(idx->split_offsets.ensure(((size_t)nranks * tiles + 2) * sizeof(uint32_t)));
+    uint8_t* d_table = idx->split_table.as<uint8_t>();
+    uint32_t* d_counts = idx->split_offsets.as<uint32_t>();
+    uint32_t* sm = idx->small.as<uint32_t>();
+    SA_CU(cudaMemcpyAsync(d_table, bin2rank, 65536, cudaMemcpyHostToDevice, s));
+    sa::split_count_kernel<<<tiles, sa::SPLIT_THREADS, 0, s>>>(d_keys, m, d_table, nranks, tiles, d_counts);
+    SA_CU(cudaGetLastError());
+    SA_CU(sa_launch_scan_u32(d_counts, (uint32_t)nranks * tiles, sm + SM_NLTOTAL, s));
+    idx->stats.kernel_launches += 2;
+    uint32_t* first = idx->h_small + 64;                       // pinned, [64, 64 + nranks]
+    for (int g = 0; g < nranks; ++g)
+        SA_CU(cudaMemcpyAsync(first + g, d_counts + (size_t)g * tiles, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaStreamSynchronize(s));
+    first[nranks] = m;
+    for (int g = 0; g < nranks; ++g) counts_out[g] = first[g + 1] - first[g];
+    return SA_OK;
+}
+
+// 2. sa_shard_recv_prepare: size this rank's receive buffers (its sort buffers keys[0] / vals[0])
+//    for m_recv records and export their CUDA IPC handles (64 bytes each).
+extern "C" int sa_shard_recv_prepare(sa_index* idx, uint64_t m_recv, uint8_t* handle_keys, uint8_t* handle_pos)
+{
+    SH_REQUIRE(idx && idx->shard_prepared && handle_keys && handle_pos, SA_ERR_INVALID, "sa_shard_recv_prepare: bad argument");
+    SH_REQUIRE(m_recv < (1ull << 30), SA_ERR_LIMIT, "sa_shard_recv_prepare: %llu records exceed the 2^30 per-GPU limit",
+               (unsigned long long)m_recv);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    SA_CU(cudaStreamSynchronize(idx->stream));                  // nothing of an earlier build still uses them
+    int rc = sa_ensure_scratch(idx, m_recv ? (uint32_t)m_recv : 1u);
+    if (rc != SA_OK) return rc;
+    if (idx->dbg_same_process) {                                // emulated ranks share one process: raw pointers
+        memset(handle_keys, 0, 64);
+        memset(handle_pos, 0, 64);
+        memcpy(handle_keys, "SAMEPROC", 8);
+        memcpy(handle_pos, "SAMEPROC", 8);
+        memcpy(handle_keys + 8, &idx->keys[0].p, sizeof(void*));
+        memcpy(handle_pos + 8, &idx->vals[0].p, sizeof(void*));
+        return SA_OK;
+    }
+    cudaIpcMemHandle_t hk, hp;
+    SA_CU(cudaIpcGetMemHandle(&hk, idx->keys[0].p));
+    SA_CU(cudaIpcGetMemHandle(&hp, idx->vals[0].p));
+    memcpy(handle_keys, &hk, 64);
+    memcpy(handle_pos, &hp, 64);
+    return SA_OK;
+}
+
+// 3. sa_shard_scatter_p2p: handles[g] = the two handles rank g exported (128 bytes per rank, keys
+//    then positions); dst_offset[g] = record index in rank g's buffers where this rank's run starts
+//    (sum of the counts of lower ranks for destination g).  Stores go over NVLink / the local HBM.
+extern "C" int sa_shard_scatter_p2p(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m64,
+                                    int nranks, int my_rank, const uint8_t* handles, const uint64_t* dst_offset)
+{
+    SH_REQUIRE(idx && idx->shard_prepared && handles && dst_offset, SA_ERR_INVALID, "sa_shard_scatter_p2p: bad argument");
+    SH_REQUIRE(nranks >= 1 && nranks <= sa::SPLIT_MAXR && my_rank >= 0 && my_rank < nranks, SA_ERR_INVALID,
+               "sa_shard_scatter_p2p: bad rank");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = (uint32_t)m64;
+    sa::PeerTable pt{};
+    for (int g = 0; g < nranks; ++g) {
+        void *pk = nullptr, *pp = nullptr;
+        if (g == my_rank) {
+            pk = idx->keys[0].p; pp = idx->vals[0].p;
+        } else {
+            const uint8_t* h = handles + (size_t)g * 128;
+            if (memcmp(h, "SAMEPROC", 8) == 0) {               // single-process emulation: raw device pointers
+                memcpy(&pk, h + 8, sizeof pk);
+                memcpy(&pp, h + 64 + 8, sizeof pp);
+                pt.keys[g] = static_cast<uint64_t*>(pk) + dst_offset[g];
+                pt.pos[g] = static_cast<uint32_t*>(pp) + dst_offset[g];
+                continue;
+            }
+            if (!idx->peer_mapped[g] || memcmp(&idx->peer_hk[g], h, 64) != 0 || memcmp(&idx->peer_hp[g], h + 64, 64) != 0) {
+                if (idx->peer_mapped[g]) {
+                    cudaIpcCloseMemHandle(idx->peer_keys[g]);
+                    cudaIpcCloseMemHandle(idx->peer_pos[g]);
+                    idx->peer_mapped[g] = false;
+                }
+                memcpy(&idx->peer_hk[g], h, 64);
+                memcpy(&idx->peer_hp[g], h + 64, 64);
+                SA_CU(cudaIpcOpenMemHandle(&idx->peer_keys[g], idx->peer_hk[g], cudaIpcMemLazyEnablePeerAccess));
+                SA_CU(cudaIpcOpenMemHandle(&idx->peer_pos[g], idx->peer_hp[g], cudaIpcMemLazyEnablePeerAccess));
+                idx->peer_mapped[g] = true;
+            }
+            pk = idx->peer_keys[g]; pp = idx->peer_pos[g];
+        }
+        pt.keys[g] = static_cast<uint64_t*>(pk) + dst_offset[g];
+        pt.pos[g] = static_cast<uint32_t*>(pp) + dst_offset[g];
+    }
+    if (m == 0) return SA_OK;
+    const uint32_t tiles = (m + sa::SPLIT_TILE - 1) / sa::SPLIT_TILE;
+    const uint32_t* first = idx->h_small + 64;                  // left there by sa_shard_count
+    for (int g = 0; g < nranks; ++g) pt.first[g] = first[g];
+    sa::split_scatter_p2p_kernel<<<tiles, sa::SPLIT_THREADS, 0, s>>>(d_keys, d_pos, m, idx->split_table.as<uint8_t>(),
+                                                                     nranks, tiles, idx->split_offsets.as<uint32_t>(), pt);
+    SA_CU(cudaGetLastError());
+    idx->stats.kernel_launches += 1;
+    SA_CU(cudaStreamSynchronize(s));
+    return SA_OK;
+}
+
+// 4. sa_shard_sort_recv: after a barrier (every rank's scatter has completed), sort + refine the
+//    m records that now sit in this rank's keys[0] / vals[0].
+extern "C" int sa_shard_sort_recv(sa_index* idx, uint64_t m64)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_sort_recv: call sa_shard_begin first");
+    SH_REQUIRE(m64 < (1ull << 30), SA_ERR_LIMIT, "sa_shard_sort_recv: too many records");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    const uint32_t m = (uint32_t)m64;
+    idx->shard_m = m;
+    idx->shard_sa = nullptr;
+    if (m == 0) return SA_OK;
+    int rc = sa_stage_sort_refine(idx, m, false, &idx->shard_sa);
+    if (rc != SA_OK) return rc;
+    SA_CU(cudaStreamSynchronize(idx->stream));
     return SA_OK;
 }

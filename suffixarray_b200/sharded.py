@@ -194,6 +194,36 @@ class ShardBuilder:
         self.send_counts = counts.astype(np.int64)
         return self.send_counts
 
+    # ---- fused split + exchange (peer stores through CUDA IPC)
+    def count(self, global_hist_np: np.ndarray):
+        self.bin2rank = choose_bin2rank(global_hist_np, self.world)
+        counts = np.zeros(self.world, dtype=np.uint64)
+        self.torch.cuda.synchronize(self.dev)
+        S.check(S.lib().sa_shard_count(self.idx._h, self._p(self.keys), self.m_local,
+                                       self.bin2rank.ctypes.data_as(S._vp), self.world, counts.ctypes.data_as(S._vp)))
+        self.send_counts = counts.astype(np.int64)
+        return self.send_counts
+
+    def recv_prepare(self, m_recv: int) -> np.ndarray:
+        """-> 128 bytes: the IPC handles of this rank's receive (= sort) buffers."""
+        self.m = int(m_recv)
+        h = np.zeros(128, dtype=np.uint8)
+        S.check(S.lib().sa_shard_recv_prepare(self.idx._h, self.m, h[:64].ctypes.data_as(S._vp),
+                                              h[64:].ctypes.data_as(S._vp)))
+        return h
+
+    def scatter_p2p(self, all_handles: np.ndarray, counts_matrix: np.ndarray):
+        """counts_matrix[src, dst]; this rank's run starts in rank d's buffers after the runs of lower ranks."""
+        dst_off = counts_matrix[: self.rank, :].sum(axis=0).astype(np.uint64)
+        handles = np.ascontiguousarray(all_handles, dtype=np.uint8).reshape(-1)
+        S.check(S.lib().sa_shard_scatter_p2p(self.idx._h, self._p(self.keys), self._p(self.pos), self.m_local,
+                                             self.world, self.rank, handles.ctypes.data_as(S._vp),
+                                             dst_off.ctypes.data_as(S._vp)))
+        self.keys = self.pos = None
+
+    def sort_recv(self):
+        S.check(S.lib().sa_shard_sort_recv(self.idx._h, self.m))
+
     def sort(self, recv_keys, recv_pos, m: int):
         self.m = int(m)
         self.torch.cuda.synchronize(self.dev)
@@ -250,7 +280,7 @@ def _array_to_edges(row: np.ndarray) -> dict:
 
 # ----------------------------------------------------------------------------- drivers
 def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lowercase: bool = False,
-                   adopt: bool = True):
+                   adopt: bool = True, exchange: str = "p2p"):
     """G ranks in lock step inside one process on ONE GPU (collectives = tensor copies).
     -> (full SA as a torch int32 CUDA tensor, list of ShardBuilder).  Test tier only."""
     import torch
@@ -259,6 +289,22 @@ def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lo
     ranks = [ShardBuilder(text, max_suffix_length, g, world, device, lowercase) for g in range(world)]
     hist = sum(r.pack().to(torch.int64) for r in ranks)                       # all-reduce
     hist_np = hist.cpu().numpy()
+    if exchange == "p2p":
+        for r in ranks:
+            r.idx.debug_set("same_process", 1)
+        counts = np.stack([r.count(hist_np) for r in ranks])                   # all-gather of the counts
+        handles = np.stack([r.recv_prepare(int(counts[:, d].sum())) for d, r in enumerate(ranks)])   # all-gather
+        for r in ranks:
+            r.scatter_p2p(handles, counts)
+        for r in ranks:                                                        # barrier
+            r.sort_recv()
+        edges = [_array_to_edges(_edges_to_array(r.edges())) for r in ranks]
+        slices = [r.finish(edges) for r in ranks]
+        full = torch.cat(slices)
+        if adopt:
+            for r in ranks:
+                r.adopt(full)
+        return full, ranks
     counts = np.stack([r.split(hist_np) for r in ranks])                       # [src, dst]
     for d, r in enumerate(ranks):                                              # all-to-all
         parts_k, parts_p = [], []
@@ -283,7 +329,7 @@ def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lo
 
 
 def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool = False, timing: bool = False,
-                      adopt: bool = True, group=None, device_text=None, builder=None):
+                      adopt: bool = True, group=None, device_text=None, builder=None, exchange: str = "p2p"):
     """This process's rank of the sample-sort build under torch.distributed (NCCL).
     -> (ShardBuilder with the complete SA adopted, dict of per-phase wall times in ms)."""
     import time
@@ -312,6 +358,25 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
     dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
     hist_np = hist.cpu().numpy()
     lap("pack+hist")
+    if exchange == "p2p":
+        send_counts = r.count(hist_np)
+        sc = torch.from_numpy(send_counts.copy()).to(r.dev)
+        rows_c = [torch.empty_like(sc) for _ in range(world)]
+        dist.all_gather(rows_c, sc, group=group)
+        cm = np.stack([x.cpu().numpy() for x in rows_c])                       # [src, dst]
+        m = int(cm[:, rank].sum())
+        hnd = torch.from_numpy(r.recv_prepare(m)).to(r.dev)
+        rows_h = [torch.empty_like(hnd) for _ in range(world)]
+        dist.all_gather(rows_h, hnd, group=group)                             # also: every rank's buffers are idle now
+        handles = np.stack([x.cpu().numpy() for x in rows_h])
+        lap("split")
+        r.scatter_p2p(handles, cm)
+        dist.barrier(group=group)                                              # all peer stores have landed
+        lap("exchange")
+        r.sort_recv()
+        lap("sort+refine")
+        r.exchange_bytes = int((send_counts.sum() - send_counts[rank]) * 12)
+        return _finish_distributed(r, t, lap, adopt, group)
     send_counts = r.split(hist_np)
     sc = torch.from_numpy(send_counts.copy()).to(r.dev)
     rc = torch.empty_like(sc)
@@ -328,6 +393,14 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
     r.sort(recv_keys, recv_pos, m)
     del recv_keys, recv_pos
     lap("sort+refine")
+    r.exchange_bytes = int((send_counts.sum() - send_counts[rank]) * 12)
+    return _finish_distributed(r, t, lap, adopt, group)
+
+
+def _finish_distributed(r, t, lap, adopt, group):
+    import torch
+    import torch.distributed as dist
+    world = r.world
     mine = torch.from_numpy(_edges_to_array(r.edges())).to(r.dev)
     rows = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(rows, mine, group=group)
@@ -346,5 +419,4 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
         r.adopt(full)
         del full
         lap("gather+adopt")
-    r.exchange_bytes = int((send_counts.sum() - send_counts[rank]) * 12)
     return r, t
