@@ -237,19 +237,24 @@ def run_ours(args):
         r["build_e2e_ms"] = (time.perf_counter() - t0) * 1e3
         r["build_launches"] += idx_e2e.stats()["kernel_launches"]
         # ---- queries through the C ABI with host buffers; the library's CUDA events give the
-        #      device-only time of the same kernels
+        #      device-only time of the same kernels.  Ranges (sa_query_ranges <-> get_substring_positions)
+        #      and records (+ sa_query_hits <-> the hit loop of get_matching_records) are timed apart.
         t0 = time.perf_counter()
         S.check(lib.sa_query_ranges(idx_e2e._h, vp(h_q.data_ptr()), vp(h_qoff.data_ptr()), nq, K_HITS,
                                     vp(h_start.data_ptr()), vp(h_end.data_ptr()), vp(h_hoff.data_ptr())))
+        torch.cuda.synchronize()
+        r["range_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        st = idx_e2e.stats()
+        r["query_kernel_ms"] = st["ms_query"]
+        r["query_launches"] = st["kernel_launches"]
         total = int(h_hoff[nq])
         ensure_hit_bufs(total)
-        S.check(lib.sa_query_hits(idx_e2e._h, vp(h_hits["pos"].data_ptr()), vp(h_hits["doc"].data_ptr()),
-                                  h_hits["cap"]))
+        t0 = time.perf_counter()
+        S.check(lib.sa_query_hits(idx_e2e._h, None, vp(h_hits["doc"].data_ptr()), h_hits["cap"]))
         torch.cuda.synchronize()
-        r["query_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        r["query_e2e_ms"] = r["range_e2e_ms"] + (time.perf_counter() - t0) * 1e3
         st = idx_e2e.stats()
         r["query_dev_ms"] = st["ms_query"] + st["ms_hits"]
-        r["query_kernel_ms"] = st["ms_query"]
         r["query_launches"] = st["kernel_launches"]
         r["hits"] = total
         return r
@@ -274,18 +279,20 @@ def run_ours(args):
 
     K = args.steps
     sums = torch.tensor([sum(r["build_dev_ms"] for r in recs), sum(r["query_dev_ms"] for r in recs),
-                         sum(r["build_e2e_ms"] for r in recs), sum(r["query_e2e_ms"] for r in recs), wall_ms],
+                         sum(r["build_e2e_ms"] for r in recs), sum(r["query_e2e_ms"] for r in recs), wall_ms,
+                         sum(r["range_e2e_ms"] for r in recs), sum(r["query_kernel_ms"] for r in recs)],
                         dtype=torch.float64, device="cuda")
     counts = torch.tensor([float(n), float(nq)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(sums, op=dist.ReduceOp.MAX)     # max over ranks
         dist.all_reduce(counts, op=dist.ReduceOp.SUM)   # units all ranks processed per step
     build_ms, query_ms, build_e2e_ms, query_e2e_ms, wall_ms = (sums / K).tolist()[:4] + [sums[4].item()]
+    range_e2e_ms, range_dev_ms = (sums[5:7] / K).tolist()
     n_all, nq_all = counts.tolist()
     result = None
     if rank == 0:
         result = assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_e2e_ms, query_e2e_ms,
-                          wall_ms, clocks, qbytes.size, text, qbytes, qoff, lower)
+                          wall_ms, clocks, qbytes.size, text, qbytes, qoff, lower, range_e2e_ms, range_dev_ms)
     idx_dev.close()
     idx_e2e.close()
     if world > 1:
@@ -355,17 +362,19 @@ def run_ours_global(args, world, rank, local):
         t0 = time.perf_counter()
         S.check(lib.sa_query_ranges(b2.idx._h, vp(h_q.data_ptr()), vp(h_qoff.data_ptr()), nq, K_HITS,
                                     vp(h_start.data_ptr()), vp(h_end.data_ptr()), vp(h_hoff.data_ptr())))
+        torch.cuda.synchronize()
+        r["range_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        r["query_kernel_ms"] = b2.idx.stats()["ms_query"]
         total = int(h_hoff[nq])
         if total > hits["cap"]:
             hits["cap"] = int(total * 1.1) + 1024
-            hits["pos"] = torch.empty(hits["cap"], dtype=torch.int32, pin_memory=True)
             hits["doc"] = torch.empty(hits["cap"], dtype=torch.int32, pin_memory=True)
-        S.check(lib.sa_query_hits(b2.idx._h, vp(hits["pos"].data_ptr()), vp(hits["doc"].data_ptr()), hits["cap"]))
+        t0 = time.perf_counter()
+        S.check(lib.sa_query_hits(b2.idx._h, None, vp(hits["doc"].data_ptr()), hits["cap"]))
         torch.cuda.synchronize()
-        r["query_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        r["query_e2e_ms"] = r["range_e2e_ms"] + (time.perf_counter() - t0) * 1e3
         st = b2.idx.stats()
         r["query_dev_ms"] = st["ms_query"] + st["ms_hits"]
-        r["query_kernel_ms"] = st["ms_query"]
         r["query_launches"] = st["kernel_launches"]
         r["hits"] = total
         return r
@@ -386,7 +395,8 @@ def run_ours_global(args, world, rank, local):
     K = args.steps
     phase_names = list(recs[-1]["phases"].keys())
     sums = torch.tensor([sum(r["build_dev_ms"] for r in recs), sum(r["query_dev_ms"] for r in recs),
-                         sum(r["build_e2e_ms"] for r in recs), sum(r["query_e2e_ms"] for r in recs), wall_ms] +
+                         sum(r["build_e2e_ms"] for r in recs), sum(r["query_e2e_ms"] for r in recs), wall_ms,
+                         sum(r["range_e2e_ms"] for r in recs), sum(r["query_kernel_ms"] for r in recs)] +
                         [sum(r["phases"][p] for r in recs) for p in phase_names], dtype=torch.float64, device=dev)
     dist.all_reduce(sums, op=dist.ReduceOp.MAX)
     ms = torch.tensor([float(recs[-1]["m"]), float(recs[-1]["exchange_bytes"])], dtype=torch.float64, device=dev)
@@ -395,9 +405,11 @@ def run_ours_global(args, world, rank, local):
     result = None
     if rank == 0:
         build_ms, query_ms, build_e2e_ms, query_e2e_ms = (sums[:4] / K).tolist()
-        phases = {p: round(v / K, 3) for p, v in zip(phase_names, sums[5:].tolist())}
+        range_e2e_ms, range_dev_ms = (sums[5:7] / K).tolist()
+        phases = {p: round(v / K, 3) for p, v in zip(phase_names, sums[7:].tolist())}
         result = assemble(args, world, recs, n // world, nq, float(n), float(nq * world), build_ms, query_ms,
-                          build_e2e_ms, query_e2e_ms, sums[4].item(), clocks, qbytes.size, None, None, None, lower)
+                          build_e2e_ms, query_e2e_ms, sums[4].item(), clocks, qbytes.size, None, None, None, lower,
+                          range_e2e_ms, range_dev_ms)
         result["e2e"]["h2d_bytes_per_step"] = int(n + qbytes.size + (nq + 1) * 8)     # per rank: the replicated text
         shard_sizes = [int(x[0].item()) for x in ms_all]
         xbytes = [int(x[1].item()) for x in ms_all]
@@ -424,7 +436,8 @@ def run_ours_global(args, world, rank, local):
 
 
 # ------------------------------------------------------------------------------ CPU reference legs
-def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample=200_000, threads=0):
+def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample=200_000, threads=0,
+                        record_sample=20_000):
     """Times the reference's own CPU path (engine.c through oracle/_ref/libsa_ref.so when present,
     else the oracle port) on the host cores.  -> dict."""
     from oracle import pyoracle as O
@@ -434,9 +447,19 @@ def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample
     n = int(low.size)
     kind = "reference" if O.have_ref() else "port"
     cores = O.ref_max_threads() if kind == "reference" else 1
+    rec = {"record_sample": 0, "record_s": 0.0, "records": 0}
     if kind == "reference":
-        tp = np.zeros(n + O.REF_PAD, dtype=np.uint8)
-        tp[:n] = low
+        # The CPU arm indexes '\n' + text (one empty leading record): get_matching_records scans back
+        # to the previous '\n' with a uint32 offset (engine.c:1189-1191) and leaves the buffer for any
+        # hit in record 0.  [ text' | 64 zero bytes | '\n' | slack ] keeps the forward scan
+        # (:1194-1205) and the after-the-record memcpy (:1208) inside the buffer too.
+        GUARD = 1 << 16
+        n = n + 1
+        buf = np.zeros(n + 64 + 1 + GUARD, dtype=np.uint8)
+        buf[0] = 10
+        buf[1:n] = low
+        buf[n + 64] = 10
+        tp = buf
         sa = np.empty(n, dtype=np.uint32)
         best = float("inf")
         for _ in range(build_reps):
@@ -456,12 +479,19 @@ def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample
         skipped = np.zeros(nqs, dtype=np.uint8)
         import ctypes as C
         rl = O.ref_lib()
+        u32p, u64p, u8p = C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint8)
         t0 = time.perf_counter()
-        rl.ref_query_batch(tp.ctypes.data, sa.ctypes.data_as(C.POINTER(C.c_uint32)), n, L, zbytes.ctypes.data,
-                           zoff.ctypes.data_as(C.POINTER(C.c_uint64)), nqs,
-                           start.ctypes.data_as(C.POINTER(C.c_uint32)), end.ctypes.data_as(C.POINTER(C.c_uint32)),
-                           skipped.ctypes.data_as(C.POINTER(C.c_uint8)), threads)
+        rl.ref_query_batch(tp.ctypes.data, sa.ctypes.data_as(u32p), n, L, zbytes.ctypes.data,
+                           zoff.ctypes.data_as(u64p), nqs, start.ctypes.data_as(u32p), end.ctypes.data_as(u32p),
+                           skipped.ctypes.data_as(u8p), threads)
         tq = time.perf_counter() - t0
+        # record path: get_matching_records (bisection + newline scans + malloc/memcpy per hit), smaller sample
+        nrec = min(nqs, record_sample)
+        hits = np.zeros(max(nrec, 1), dtype=np.uint32)
+        t0 = time.perf_counter()
+        total = rl.ref_query_records_batch(tp.ctypes.data, sa.ctypes.data_as(u32p), n, L, zbytes.ctypes.data,
+                                           zoff.ctypes.data_as(u64p), nrec, K_HITS, hits.ctypes.data_as(u32p), threads)
+        rec = {"record_sample": nrec, "record_s": time.perf_counter() - t0, "records": int(total)}
     else:
         t0 = time.perf_counter()
         sa = O.oracle_build(low, L)
@@ -471,12 +501,15 @@ def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample
         t0 = time.perf_counter()
         O.oracle_query(low, sa, L, qs)
         tq = time.perf_counter() - t0
-    return {"kind": kind, "cores": int(cores), "n": n, "build_s": best, "build_mchars_s": n / best / 1e6,
-            "query_sample": nqs, "query_s": tq, "queries_per_s": nqs / tq}
+    out = {"kind": kind, "cores": int(cores), "n": n, "build_s": best, "build_mchars_s": n / best / 1e6,
+           "query_sample": nqs, "query_s": tq, "queries_per_s": nqs / tq}
+    out.update(rec)
+    out["record_queries_per_s"] = rec["record_sample"] / rec["record_s"] if rec["record_s"] > 0 else None
+    return out
 
 
 def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_e2e_ms, query_e2e_ms, wall_ms,
-             clocks, qbytes_len, text, qbytes, qoff, lower):
+             clocks, qbytes_len, text, qbytes, qoff, lower, range_e2e_ms, range_dev_ms):
     K = args.steps
     peak, peak_src = load_peaks()
     os_ms = sum(r["onesweep_ms"] for r in recs)
@@ -488,12 +521,16 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
     traffic = load_ncu_traffic()
     hits = recs[-1]["hits"]
     h2d = n + qbytes_len + (nq + 1) * 8
-    d2h = nq * 8 + (nq + 1) * 8 + hits * 8
+    d2h = nq * 8 + (nq + 1) * 8 + hits * 4
     out = {
         "metric": METRIC,
         "value": round(n_all / (build_ms * 1e-3) / 1e6, 2),
         "unit": "Mchars/s (SA build)",
-        "queries_per_s": round(nq_all / (query_ms * 1e-3), 1),
+        "queries_per_s": round(nq_all / (range_dev_ms * 1e-3), 1),
+        "record_queries_per_s": round(nq_all / (query_ms * 1e-3), 1),
+        "queries_note": "queries_per_s = rank ranges (sa_query_ranges <-> get_substring_positions, engine.c:869); "
+                        "record_queries_per_s adds the first min(k, count) hits per query as record ids "
+                        "(sa_query_hits <-> the hit loop of get_matching_records, engine.c:1185-1211)",
         "n_gpus": world, "steps": K, "warmup": args.warmup,
         "ms_per_step": round(build_ms + query_ms, 3),
         "build_ms_per_step": round(build_ms, 3), "query_ms_per_step": round(query_ms, 3),
@@ -506,8 +543,10 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
                    "hits_per_batch": hits, "sharding": "one independent partition per GPU (suffix_array.pyx:148-180)",
                    "l2": "inputs larger than L2 (keys 8n + positions 4n = 1.2 GB per pass vs 126 MB L2)"},
         "e2e": {"value": round(n_all / (build_e2e_ms * 1e-3) / 1e6, 2), "unit": "Mchars/s (SA build)",
-                "queries_per_s": round(nq_all / (query_e2e_ms * 1e-3), 1),
-                "build_ms": round(build_e2e_ms, 3), "query_ms": round(query_e2e_ms, 3),
+                "queries_per_s": round(nq_all / (range_e2e_ms * 1e-3), 1),
+                "record_queries_per_s": round(nq_all / (query_e2e_ms * 1e-3), 1),
+                "build_ms": round(build_e2e_ms, 3), "range_query_ms": round(range_e2e_ms, 3),
+                "record_query_ms": round(query_e2e_ms, 3),
                 "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "api": "sa_build_text + sa_query_ranges + sa_query_hits (pinned host buffers)"},
         "gpu_launches": int(sum(r["build_launches"] + r["query_launches"] for r in recs)),
@@ -522,17 +561,20 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
                                  "note": "SURVEY 8(d) B_build = 213 n bytes over the whole device build"},
         "phases_ms_last_step": recs[-1]["phases"],
         "refine_rounds": recs[-1]["rounds"],
-        "query_kernel_ms": round(sum(r["query_kernel_ms"] for r in recs) / K, 3),
+        "query_kernel_ms": round(range_dev_ms, 3),
         "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_reference_times(text, qbytes, qoff, lower, args.max_suffix_length)
         out["cpu_baseline"] = {"value": round(cb["build_mchars_s"], 2), "unit": "Mchars/s (SA build)",
-                               "queries_per_s": round(cb["queries_per_s"], 1), "cores": cb["cores"],
-                               "kind": cb["kind"],
+                               "queries_per_s": round(cb["queries_per_s"], 1),
+                               "record_queries_per_s": round(cb["record_queries_per_s"], 1) if cb["record_queries_per_s"] else None,
+                               "cores": cb["cores"], "kind": cb["kind"],
                                "sample": f"build: the full {cb['n']}-char text once ({cb['build_s']:.2f} s); "
                                          f"queries: first {cb['query_sample']} of the batch ({cb['query_s']:.2f} s), "
-                                         "get_substring_positions under an omp parallel-for"}
+                                         "get_substring_positions under an omp parallel-for; records: first "
+                                         f"{cb['record_sample']} queries through get_matching_records, k = {K_HITS} "
+                                         f"({cb['records']} records, {cb['record_s']:.2f} s)"}
     return out
 
 
@@ -555,8 +597,10 @@ def run_reference(args):
     bs = sum(r["build_s"] for r in recs) / K
     qs = sum(r["query_s"] for r in recs) / K
     v = sample_n / bs / 1e6
+    rqs = [r["record_queries_per_s"] for r in recs if r.get("record_queries_per_s")]
+    rq = round(sum(rqs) / len(rqs), 1) if rqs else None
     return {"impl": "reference", "metric": METRIC, "value": round(v, 2), "unit": "Mchars/s (SA build)",
-            "queries_per_s": round(nqs / qs, 1), "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "queries_per_s": round(nqs / qs, 1), "record_queries_per_s": rq, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round((bs + qs) * 1e3, 2), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8 text / u32 positions", "data": "synthetic",
             "config": {"workload": WORKLOADS[args.workload][2], "name": args.workload,
@@ -566,7 +610,7 @@ def run_reference(args):
                              "sample": f"per step: build over the first {sample_n} chars of the workload text + the "
                                        f"first {nqs} queries of its batch (searched in that prefix)"},
             "e2e": {"value": round(v, 2), "unit": "Mchars/s (SA build)", "queries_per_s": round(nqs / qs, 1),
-                    "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    "record_queries_per_s": rq, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
 
 

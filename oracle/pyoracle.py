@@ -94,6 +94,9 @@ def ref_lib():
         lib.ref_query_batch.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_uint32, C.c_void_p, _u64p,
                                         C.c_uint64, _u32p, _u32p, _u8p, C.c_int]
         lib.ref_query_batch.restype = None
+        lib.ref_query_records_batch.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_uint32, C.c_void_p, _u64p, C.c_uint64,
+                                                C.c_uint32, _u32p, C.c_int]
+        lib.ref_query_records_batch.restype = C.c_uint64
         lib.ref_csv_build.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, _u32p, _u8p, C.c_uint64]
         lib.ref_csv_build.restype = C.c_uint32
         lib.ref_libsais.argtypes = [_u8p, _i32p, C.c_int32, C.c_int]

@@ -80,6 +80,46 @@ void ref_query_batch(const char* text_padded, const uint32_t* sa, uint32_t n, ui
     }
 }
 
+/* get_matching_records (engine.c:1168-1214), the reference's in-memory "query -> records" path, for
+ * a batch under an omp parallel-for: bisection + for each of the first min(k, count) hits the
+ * newline scans, malloc and memcpy of the record.  The records are freed at once; the return value
+ * is the total number of records produced (hits[i] = per query).  The caller must provide a '\n'
+ * at text_padded[-1] (the backward scan of a hit in record 0 otherwise leaves the buffer,
+ * engine.c:1190) and a '\n' somewhere after the >= 64 zero bytes that follow the text (the forward
+ * scan of the last record, engine.c:1194-1205), plus max-record-length readable bytes after that
+ * (the memcpy at engine.c:1208 copies from AFTER the record).  Queries the shim refuses
+ * (out-of-bounds wrap, see ref_query) produce no records. */
+uint64_t ref_query_records_batch(const char* text_padded, const uint32_t* sa, uint32_t n,
+                                 uint32_t max_suffix_length, const char* qbytes, const uint64_t* qoff,
+                                 uint64_t nq, uint32_t k, uint32_t* hits, int nthreads)
+{
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+    uint64_t total = 0;
+#pragma omp parallel num_threads(nthreads) reduction(+ : total)
+    {
+        char** recs = (char**)malloc((size_t)k * sizeof(char*));
+        SuffixArray_struct s;
+        memset(&s, 0, sizeof s);
+        s.suffix_array = (uint32_t*)sa;
+        s.max_suffix_length = max_suffix_length;
+        s.n = n;
+#pragma omp for schedule(dynamic, 64)
+        for (long i = 0; i < (long)nq; ++i) {
+            const char* q = qbytes + qoff[i];
+            size_t m = strlen(q);
+            size_t c = m < max_suffix_length ? m : max_suffix_length;
+            hits[i] = 0;
+            if (n == 0 || strncmp(text_padded + sa[0], q, c) >= 0) continue;
+            uint32_t got = get_matching_records(text_padded, &s, q, k, recs);
+            for (uint32_t j = 0; j < got; ++j) free(recs[j]);
+            hits[i] = got;
+            total += got;
+        }
+        free(recs);
+    }
+    return total;
+}
+
 /* CSV path end to end: construct_truncated_suffix_array_from_csv_partitioned_mmap_full
  * (engine.c:1454).  Single-partition files only (< 2 GiB).  Returns n, or 0 when the
  * column was not found; copies the SA (file offsets) and the per-rank quoted bits

@@ -59,7 +59,8 @@ cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint3
                                     uint32_t* nlpos, cudaStream_t s);
 cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa, uint32_t n, uint32_t max_suffix_length,
                             const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
-                            uint32_t* end, cudaStream_t s);
+                            uint32_t* end, int mode /* 0 auto, 1 thread per query, 2 eight lanes per query */,
+                            cudaStream_t s);
 cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k,
                                  uint32_t* counts, cudaStream_t s);
 // exclusive scan of u32 counts into u64 offsets (off[num] = total)

@@ -167,14 +167,19 @@ __global__ void __launch_bounds__(256) newline_write_kernel(const uint4* __restr
 // ------------------------------------------------------------------------------ query
 __device__ __forceinline__ uint64_t load_query_word(const uint8_t* __restrict__ q, uint32_t off, uint32_t c)
 {
-    // bytes [off, off+8) of the query, big-endian, zero past c
+    // bytes [off, off+8) of the query, big-endian, zero past c.  Unconditional (clamped) byte loads
+    // followed by one mask: the per-byte predicated form gave wrong words inside the probe loop of
+    // query_thread_kernel for c = 8k + 1 > 32 with nvcc 12.9 (equal windows compared as "less").
+    if (off >= c) return 0ull;
+    const uint32_t last = c - 1u;
     uint64_t w = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        uint32_t x = (off + i < c) ? q[off + i] : 0u;
-        w = (w << 8) | x;
+        const uint32_t idx = off + i;
+        w = (w << 8) | (uint64_t)q[idx < last ? idx : last];
     }
-    return w;
+    const uint32_t nb = (c - off) < 8u ? (c - off) : 8u;
+    return keep_top_bytes(w, (int)nb);
 }
 
 // sign of strncmp(text + pos, q, c) computed by the 8 lanes of a group.
@@ -255,6 +260,67 @@ query_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, 
     }
     if (start == 0xFFFFFFFFu) end = 0xFFFFFFFFu;                    // engine.c:896-899
     if (sub == 0) { start_out[gq] = start; end_out[gq] = end; }
+}
+
+// Thread-per-query variant: the bisections are chains of dependent loads (SA[mid], then the text
+// window), so throughput is set by how many chains are in flight; one query per lane keeps 32 per
+// warp in flight instead of 4.  The first 32 query bytes live in registers, text words are
+// fetched lazily (most probes differ in the first 8 bytes).  Same probe sequence as above.
+__device__ __forceinline__ int thread_compare(const uint8_t* __restrict__ text, uint32_t pos, const uint8_t* q,
+                                              uint32_t c, uint64_t q0, uint64_t q1, uint64_t q2, uint64_t q3)
+{
+    for (uint32_t off = 0; off < c; off += 8) {
+        const uint32_t nb = (c - off) < 8u ? (c - off) : 8u;
+        const uint64_t tw = keep_top_bytes(load_be64(text, (uint64_t)pos + off), (int)nb);
+        const uint32_t j = off >> 3;
+        // words past the first 32 bytes only exist when max_suffix_length > 32
+        const uint64_t w = j == 0 ? q0 : (j == 1 ? q1 : (j == 2 ? q2 : (j == 3 ? q3 : load_query_word(q, off, c))));
+        if (tw != w) return tw < w ? -1 : 1;
+    }
+    return 0;
+}
+
+__global__ void __launch_bounds__(128)
+query_thread_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, uint32_t n, uint32_t L,
+                    const uint8_t* __restrict__ qbytes, const uint64_t* __restrict__ qoff, uint32_t nq,
+                    uint32_t* __restrict__ start_out, uint32_t* __restrict__ end_out)
+{
+    const uint32_t gq = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gq >= nq) return;
+    const uint64_t qb = qoff[gq];
+    const uint32_t len = (uint32_t)(qoff[gq + 1] - qb);
+    const uint8_t* q = qbytes + qb;
+    // c = min(strlen(q), L) (engine.c:874, :881): a NUL past byte L cannot matter
+    uint32_t c = len < L ? len : L;
+    for (uint32_t i = 0; i < c; ++i)
+        if (q[i] == 0) { c = i; break; }
+    const uint64_t q0 = load_query_word(q, 0, c), q1 = load_query_word(q, 8, c), q2 = load_query_word(q, 16, c),
+                   q3 = load_query_word(q, 24, c);
+
+    uint32_t start = 0xFFFFFFFFu, end = 0xFFFFFFFFu;
+    int64_t f1 = 0, l1 = (int64_t)n - 1, f2 = 0, l2 = (int64_t)n - 1;
+    while (f1 <= l1 || f2 <= l2) {
+        const bool a1 = f1 <= l1, a2 = f2 <= l2;
+        const int64_t m1 = (f1 + l1) / 2, m2 = (f2 + l2) / 2;
+        const bool same = a1 && a2 && m1 == m2;
+        // both SA entries first (independent loads), then the text windows
+        const uint32_t p1 = a1 ? __ldg(sa + m1) : 0u;
+        const uint32_t p2 = (a2 && !same) ? __ldg(sa + m2) : p1;
+        int c1 = 0, c2 = 0;
+        if (a1) c1 = thread_compare(text, p1, q, c, q0, q1, q2, q3);
+        if (a2) c2 = same ? c1 : thread_compare(text, p2, q, c, q0, q1, q2, q3);
+        if (a1) {
+            if (c1 < 0) f1 = m1 + 1;                                // engine.c:887-893
+            else { l1 = m1 - 1; start = (uint32_t)m1; }
+        }
+        if (a2) {
+            if (c2 > 0) l2 = m2 - 1;                                // engine.c:904-913
+            else { f2 = m2 + 1; end = (uint32_t)m2; }
+        }
+    }
+    if (start == 0xFFFFFFFFu) end = 0xFFFFFFFFu;                    // engine.c:896-899
+    start_out[gq] = start;
+    end_out[gq] = end;
 }
 
 // engine.c:1181-1185: first == UINT32_MAX -> 0 hits, else min(k, second - first + 1) in u32
@@ -339,12 +405,17 @@ cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint3
 
 cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa_, uint32_t n, uint32_t max_suffix_length,
                             const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
-                            uint32_t* end, cudaStream_t s)
+                            uint32_t* end, int mode, cudaStream_t s)
 {
     if (!nq) return cudaSuccess;
-    const uint64_t threads = (uint64_t)nq * 8;
-    sa::query_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(text, sa_, n, max_suffix_length, qbytes, qoff,
-                                                                      nq, start, end);
+    if (mode == 1 || (mode == 0 && nq >= 4096)) {        // enough queries to fill the GPU with one query per lane
+        sa::query_thread_kernel<<<(nq + 127) / 128, 128, 0, s>>>(text, sa_, n, max_suffix_length, qbytes, qoff, nq, start,
+                                                                 end);
+    } else {                 // small batches: 8 lanes per query shorten each query's critical path
+        const uint64_t threads = (uint64_t)nq * 8;
+        sa::query_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(text, sa_, n, max_suffix_length, qbytes,
+                                                                          qoff, nq, start, end);
+    }
     return cudaGetLastError();
 }
 

@@ -160,6 +160,7 @@ extern "C" int sa_debug_set(sa_index* idx, const char* key, int64_t value)
     else if (!strcmp(key, "force_gbits")) idx->dbg_force_gbits = value;
     else if (!strcmp(key, "code_bits")) idx->dbg_code_bits = value;
     else if (!strcmp(key, "same_process")) idx->dbg_same_process = value;
+    else if (!strcmp(key, "query_kernel")) idx->dbg_query_kernel = value;
     else { sa_set_error("unknown debug key %s", key); return SA_ERR_INVALID; }
     return SA_OK;
 }
@@ -172,7 +173,7 @@ static int run_ranges(sa_index* idx, const uint8_t* d_q, const uint64_t* d_off, 
     {
         ScopedPhase ph(idx, &idx->stats.ms_query);
         SA_CU(sa_launch_query(idx->text.as<uint8_t>(), idx->sa_final.as<uint32_t>(), (uint32_t)idx->n, idx->L, d_q,
-                              d_off, (uint32_t)nq, d_start, d_end, s));
+                              d_off, (uint32_t)nq, d_start, d_end, (int)idx->dbg_query_kernel, s));
         idx->stats.kernel_launches += 1;
     }
     if (offsets) {

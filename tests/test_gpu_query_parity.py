@@ -19,10 +19,12 @@ def check_queries(text, L, queries, k=1000, ref=False):
     sa = idx.sa()
     want_sa = O.oracle_build(text, L)
     assert np.array_equal(sa, want_sa)
-    s, e, off = idx.query_ranges(queries, k=k)
     ws, we = O.oracle_query(text, want_sa, L, queries)
-    assert np.array_equal(s, ws), f"start differs at {np.flatnonzero(s != ws)[:5]}"
-    assert np.array_equal(e, we), f"end differs at {np.flatnonzero(e != we)[:5]}"
+    for mode in (1, 2):              # one thread per query / eight lanes per query
+        idx.debug_set("query_kernel", mode)
+        s, e, off = idx.query_ranges(queries, k=k)
+        assert np.array_equal(s, ws), f"kernel {mode}: start differs at {np.flatnonzero(s != ws)[:5]}"
+        assert np.array_equal(e, we), f"kernel {mode}: end differs at {np.flatnonzero(e != we)[:5]}"
     woff, wpos, wdoc = O.oracle_hits(text, want_sa, ws, we, k)
     assert np.array_equal(off, woff)
     pos, doc = idx.query_hits(int(off[-1]))
