@@ -555,7 +555,10 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
                      "frac": round(achieved / peak, 4), "peak_source": peak_src,
                      "bytes_per_launch": int(os_bytes_per_launch), "avg_launch_ms": round(os_avg_ms, 4),
                      "launches_per_step": os_launches / K,
-                     "traffic": (traffic or {}).get("onesweep_kernel_bytes_per_launch")},
+                     "traffic": (round((traffic or {}).get("onesweep_dram_bytes_per_record") * os_elems / max(os_launches, 1))
+                                 if (traffic or {}).get("onesweep_dram_bytes_per_record") else None),
+                     "traffic_source": "profiles/ncu_traffic.json: dram__bytes_read+write per record of the captured "
+                                       "100 M-record launches x records per launch here"},
         "roofline_build_model": {"bytes": 213 * n, "achieved": round(213.0 * n / (build_ms * 1e-3) / 1e9, 1),
                                  "frac": round(213.0 * n / (build_ms * 1e-3) / 1e9 / peak, 4),
                                  "note": "SURVEY 8(d) B_build = 213 n bytes over the whole device build"},

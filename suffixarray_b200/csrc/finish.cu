@@ -182,10 +182,10 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
         if (X == 0 || last - first + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); __stcs(sa_out + r, pos); continue; }
         const uint64_t hi = s_hi[e], lo = s_lo[e];
         uint32_t rank = 0;
-        for (int x = first; x <= last; ++x) {
+        for (int x = first; x <= last; ++x) {               // branch-free (key, byte 16, position) compare
             const uint64_t h2 = s_hi[x], l2 = s_lo[x], t2 = s_tp[x];
-            const bool less = (h2 < hi) || (h2 == hi && ((l2 < lo) || (l2 == lo && t2 < tp)));
-            rank += less;
+            const uint32_t lt_t = t2 < tp, lt_l = l2 < lo, eq_l = l2 == lo, lt_h = h2 < hi, eq_h = h2 == hi;
+            rank += lt_h | (eq_h & (lt_l | (eq_l & lt_t)));
         }
         __stcs(sa_out + (r - (e - first) + rank), pos);
         if (e == first) ++my_runs;

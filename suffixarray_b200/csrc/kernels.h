@@ -27,8 +27,9 @@ cudaError_t sa_launch_encode(const uint8_t* text, uint64_t nbytes_padded, const 
                              cudaStream_t s);
 // src = text (ci.bits == 8) or the code array; cb = suffix bytes per key
 cudaError_t sa_launch_pack0(const uint8_t* src, uint32_t n, int cb, sa::CodeInfo ci, uint64_t* keys, cudaStream_t s);
+// also writes the tie mask of the first refinement round (bit r = lcp[r] == cb)
 cudaError_t sa_launch_lcp0(const uint64_t* sorted_keys, uint32_t n, int cb, int bits, uint32_t lprime, uint16_t* lcp,
-                           cudaStream_t s);
+                           uint32_t* tie_words, uint32_t num_tie_words, cudaStream_t s);
 // tie bit r = (lcp[r] == depth); the mask has one zero word in front (bit r lives at bit r+32)
 cudaError_t sa_launch_tie_mask(const uint16_t* lcp, uint32_t n, uint32_t depth, uint32_t* tie_words,
                                uint32_t num_words, cudaStream_t s);
@@ -44,7 +45,7 @@ cudaError_t sa_launch_compact_gather(const uint32_t* amask, const uint32_t* hmas
                                      uint64_t* ckeys, uint32_t* cvals, cudaStream_t s);
 cudaError_t sa_launch_writeback(const uint32_t* slots, const uint64_t* ckeys, const uint32_t* cvals, uint32_t m,
                                 uint32_t depth, int cb, int gbits, int bits, uint32_t lprime, uint32_t* sa,
-                                uint16_t* lcp, cudaStream_t s);
+                                uint16_t* lcp, uint32_t* tie_next, uint32_t num_tie_words, cudaStream_t s);
 
 // ---- finish.cu
 cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,

@@ -147,14 +147,20 @@ pack0_codes_kernel(const uint8_t* __restrict__ codes, uint32_t n, int cb, CodeIn
     }
 }
 
-__global__ void lcp0_kernel(const uint64_t* __restrict__ k, uint32_t n, int cb, int bits, uint32_t lprime,
-                            uint16_t* __restrict__ lcp)
+// Adjacent LCPs after round 0 and, in the same pass, the tie mask of the first refinement round
+// (bit r = lcp[r] == cb; layout as in tie_mask_kernel; the caller zeroes the mask first).
+__global__ void __launch_bounds__(256)
+lcp0_kernel(const uint64_t* __restrict__ k, uint32_t n, int cb, int bits, uint32_t lprime,
+            uint16_t* __restrict__ lcp, uint32_t* __restrict__ tie)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n) return;
     uint32_t v = 0;
-    if (r) v = bits == 8 ? pair_lcp(k[r - 1], k[r], 0, cb, lprime) : pair_lcp_codes(k[r - 1], k[r], 0, cb, bits, lprime);
-    lcp[r] = (uint16_t)v;
+    if (r < n) {
+        if (r) v = bits == 8 ? pair_lcp(k[r - 1], k[r], 0, cb, lprime) : pair_lcp_codes(k[r - 1], k[r], 0, cb, bits, lprime);
+        lcp[r] = (uint16_t)v;
+    }
+    const uint32_t b = __ballot_sync(0xffffffffu, r < n && r > 0 && v == (uint32_t)cb);
+    if ((threadIdx.x & 31) == 0 && (r >> 5) < ((n + 31) >> 5)) tie[(r >> 5) + 1] = b;
 }
 
 // word w (w >= 1) holds ranks [32(w-1), 32w); word 0 is a zero pad.
@@ -318,7 +324,8 @@ compact_gather_kernel(const uint32_t* __restrict__ amask, const uint32_t* __rest
 
 __global__ void writeback_kernel(const uint32_t* __restrict__ slots, const uint64_t* __restrict__ ckeys,
                                  const uint32_t* __restrict__ cvals, uint32_t m, uint32_t depth, int cb, int gbits,
-                                 int bits, uint32_t lprime, uint32_t* __restrict__ sa, uint16_t* __restrict__ lcp)
+                                 int bits, uint32_t lprime, uint32_t* __restrict__ sa, uint16_t* __restrict__ lcp,
+                                 uint32_t* __restrict__ tie_next)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= m) return;
@@ -327,8 +334,11 @@ __global__ void writeback_kernel(const uint32_t* __restrict__ slots, const uint6
     if (i == 0) return;
     const uint64_t a = ckeys[i - 1], b = ckeys[i];
     if ((a >> (64 - gbits)) != (b >> (64 - gbits))) return;          // first member of its group
-    lcp[r] = (uint16_t)(bits == 8 ? pair_lcp(a << gbits, b << gbits, depth, cb, lprime)
-                                  : pair_lcp_codes(a << gbits, b << gbits, depth, cb, bits, lprime));
+    const uint32_t v = bits == 8 ? pair_lcp(a << gbits, b << gbits, depth, cb, lprime)
+                                 : pair_lcp_codes(a << gbits, b << gbits, depth, cb, bits, lprime);
+    lcp[r] = (uint16_t)v;
+    // still tied through the bytes sorted so far: candidate of the next round (mask zeroed by the caller)
+    if (v == depth + (uint32_t)cb) atomicOr(tie_next + (r >> 5) + 1, 1u << (r & 31));
 }
 
 }  // namespace sa
@@ -384,10 +394,12 @@ cudaError_t sa_launch_pack0(const uint8_t* src, uint32_t n, int cb, sa::CodeInfo
 }
 
 cudaError_t sa_launch_lcp0(const uint64_t* k, uint32_t n, int cb, int bits, uint32_t lprime, uint16_t* lcp,
-                           cudaStream_t s)
+                           uint32_t* tie, uint32_t tie_words, cudaStream_t s)
 {
     if (!n) return cudaSuccess;
-    sa::lcp0_kernel<<<(n + 255) / 256, 256, 0, s>>>(k, n, cb, bits, lprime, lcp);
+    cudaError_t e = cudaMemsetAsync(tie, 0, (size_t)tie_words * sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    sa::lcp0_kernel<<<(n + 255) / 256, 256, 0, s>>>(k, n, cb, bits, lprime, lcp, tie);
     return cudaGetLastError();
 }
 
@@ -431,10 +443,12 @@ cudaError_t sa_launch_compact_gather(const uint32_t* amask, const uint32_t* hmas
 
 cudaError_t sa_launch_writeback(const uint32_t* slots, const uint64_t* ckeys, const uint32_t* cvals, uint32_t m,
                                 uint32_t depth, int cb, int gbits, int bits, uint32_t lprime, uint32_t* sa_,
-                                uint16_t* lcp, cudaStream_t s)
+                                uint16_t* lcp, uint32_t* tie_next, uint32_t tie_words, cudaStream_t s)
 {
     if (!m) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(tie_next, 0, (size_t)tie_words * sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
     sa::writeback_kernel<<<(m + 255) / 256, 256, 0, s>>>(slots, ckeys, cvals, m, depth, cb, gbits, bits, lprime, sa_,
-                                                         lcp);
+                                                         lcp, tie_next);
     return cudaGetLastError();
 }
