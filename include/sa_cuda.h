@@ -140,6 +140,7 @@ int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const uint16_t* lef
                     uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp, uint32_t nright,
                     uint32_t* d_sa_out);
 int sa_adopt_sa(sa_index* idx, const uint32_t* d_sa_full, uint64_t n);
+int sa_adopt_sa_parts(sa_index* idx, const uint32_t* d_parts, uint64_t stride, const uint64_t* counts, int nparts);
 /* Fused split + exchange for ranks on one node: instead of sa_shard_split + NCCL all-to-all, the
  * split kernel stores every record straight into its destination rank's sort buffers, mapped
  * through CUDA IPC (peer stores over NVLink).  sa_shard_count -> all-gather of the counts ->

@@ -29,7 +29,7 @@ EXPORTS = [
     "sa_copy_quoted_bits", "sa_copy_text", "sa_device_sa", "sa_get_stats", "sa_query_ranges", "sa_query_hits",
     "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
     "sa_shard_begin", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
-    "sa_adopt_sa", "sa_shard_count", "sa_shard_recv_prepare", "sa_shard_scatter_p2p", "sa_shard_sort_recv",
+    "sa_adopt_sa", "sa_adopt_sa_parts", "sa_shard_count", "sa_shard_recv_prepare", "sa_shard_scatter_p2p", "sa_shard_sort_recv",
 ]
 
 
@@ -105,6 +105,7 @@ def lib():
     L.sa_shard_edges.argtypes = [_vp, C.c_uint32, _vp, _vp, _vp, _vp]
     L.sa_shard_finish.argtypes = [_vp, _vp, _vp, C.c_uint32, C.c_uint32, _vp, _vp, C.c_uint32, _vp]
     L.sa_adopt_sa.argtypes = [_vp, _vp, C.c_uint64]
+    L.sa_adopt_sa_parts.argtypes = [_vp, _vp, C.c_uint64, _vp, C.c_int]
     L.sa_shard_count.argtypes = [_vp, _vp, C.c_uint64, _vp, C.c_int, _vp]
     L.sa_shard_recv_prepare.argtypes = [_vp, C.c_uint64, _vp, _vp]
     L.sa_shard_scatter_p2p.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_int, C.c_int, _vp, _vp]

@@ -139,14 +139,21 @@ split_scatter_p2p_kernel(const uint64_t* __restrict__ keys, const uint32_t* __re
 {
     constexpr int WARPS = SPLIT_THREADS / 32;
     __shared__ uint32_t s_wcnt[WARPS][SPLIT_MAXR];
-    __shared__ uint32_t s_wbase[WARPS][SPLIT_MAXR];
+    __shared__ uint32_t s_wbase[WARPS][SPLIT_MAXR];        // slot of the warp's first record for a destination
+    __shared__ uint32_t s_tstart[SPLIT_MAXR + 1];           // first slot of each destination inside the tile
+    __shared__ uint32_t s_run[SPLIT_MAXR];                  // index in the destination run of the tile's first record
     __shared__ uint64_t* s_k[SPLIT_MAXR];
     __shared__ uint32_t* s_p[SPLIT_MAXR];
+    __shared__ uint64_t s_keys[SPLIT_TILE];                 // tile re-ordered by destination: peer stores become
+    __shared__ uint32_t s_pos[SPLIT_TILE];                  // long coalesced runs instead of 32-byte fragments
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid < SPLIT_MAXR) { s_k[tid] = pt.keys[tid]; s_p[tid] = pt.pos[tid]; }
     const uint32_t lt = lanemask_lt();
-    const uint32_t base = blockIdx.x * SPLIT_TILE + warp * (32 * SPLIT_IPT) + lane;
+    const uint32_t tile_base = blockIdx.x * SPLIT_TILE;
+    const uint32_t tile_n = (m - tile_base) < (uint32_t)SPLIT_TILE ? (m - tile_base) : (uint32_t)SPLIT_TILE;
+    const uint32_t base = tile_base + warp * (32 * SPLIT_IPT) + lane;
     uint64_t key[SPLIT_IPT];
+    uint32_t val[SPLIT_IPT];
     uint32_t d[SPLIT_IPT], rk[SPLIT_IPT];
     uint32_t cnt[SPLIT_MAXR];
 #pragma unroll
@@ -155,6 +162,11 @@ split_scatter_p2p_kernel(const uint64_t* __restrict__ keys, const uint32_t* __re
     for (int i = 0; i < SPLIT_IPT; ++i) {
         const uint32_t idx = base + i * 32;
         key[i] = idx < m ? ld_stream_u64(keys + idx) : 0ull;
+        val[i] = idx < m ? ld_stream_u32(pos + idx) : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < SPLIT_IPT; ++i) {
+        const uint32_t idx = base + i * 32;
         d[i] = idx < m ? bin2rank[(uint32_t)(key[i] >> 48)] : 0xFFu;
         rk[i] = 0;
 #pragma unroll
@@ -171,20 +183,33 @@ split_scatter_p2p_kernel(const uint64_t* __restrict__ keys, const uint32_t* __re
         for (int g = 0; g < SPLIT_MAXR; ++g) s_wcnt[warp][g] = cnt[g];
     }
     __syncthreads();
-    if (tid < nranks) {
-        // position inside the run this rank sends to rank `tid`
-        uint32_t run = offsets[(size_t)tid * tiles + blockIdx.x] - pt.first[tid];
-        for (int w = 0; w < WARPS; ++w) { s_wbase[w][tid] = run; run += s_wcnt[w][tid]; }
+    if (tid == 0) {
+        uint32_t run = 0;
+        for (int g = 0; g < nranks; ++g) {
+            s_tstart[g] = run;
+            for (int w = 0; w < WARPS; ++w) { s_wbase[w][g] = run; run += s_wcnt[w][g]; }
+        }
+        for (int g = nranks; g <= SPLIT_MAXR; ++g) s_tstart[g] = run;
     }
+    if (tid < nranks) s_run[tid] = offsets[(size_t)tid * tiles + blockIdx.x] - pt.first[tid];
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < SPLIT_IPT; ++i) {
         const uint32_t idx = base + i * 32;
         if (idx < m) {
-            const uint32_t o = s_wbase[warp][d[i]] + rk[i];
-            s_k[d[i]][o] = key[i];
-            s_p[d[i]][o] = ld_stream_u32(pos + idx);
+            const uint32_t slot = s_wbase[warp][d[i]] + rk[i];
+            s_keys[slot] = key[i];
+            s_pos[slot] = val[i];
         }
+    }
+    __syncthreads();
+    for (uint32_t j = tid; j < tile_n; j += SPLIT_THREADS) {
+        int g = 0;
+#pragma unroll
+        for (int t = 1; t < SPLIT_MAXR; ++t) g += (t < nranks && j >= s_tstart[t]) ? 1 : 0;
+        const uint32_t o = s_run[g] + (j - s_tstart[g]);
+        s_k[g][o] = s_keys[j];
+        s_p[g][o] = s_pos[j];
     }
 }
 
@@ -566,5 +591,30 @@ extern "C" int sa_shard_sort_recv(sa_index* idx, uint64_t m64)
     int rc = sa_stage_sort_refine(idx, m, false, &idx->shard_sa);
     if (rc != SA_OK) return rc;
     SA_CU(cudaStreamSynchronize(idx->stream));
+    return SA_OK;
+}
+
+// Same, from the padded all-gather layout: part g holds counts[g] entries at d_parts + g * stride.
+extern "C" int sa_adopt_sa_parts(sa_index* idx, const uint32_t* d_parts, uint64_t stride, const uint64_t* counts,
+                                 int nparts)
+{
+    SH_REQUIRE(idx && d_parts && counts && nparts >= 1, SA_ERR_INVALID, "sa_adopt_sa_parts: bad argument");
+    SH_REQUIRE(idx->shard_prepared, SA_ERR_INVALID, "sa_adopt_sa_parts: the index holds no text");
+    uint64_t total = 0;
+    for (int g = 0; g < nparts; ++g) total += counts[g];
+    SH_REQUIRE(total == idx->n, SA_ERR_INVALID, "sa_adopt_sa_parts: parts hold %llu entries, text has %llu bytes",
+               (unsigned long long)total, (unsigned long long)idx->n);
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    SA_CU(idx->sa_final.ensure((size_t)idx->n * 4));
+    uint64_t off = 0;
+    for (int g = 0; g < nparts; ++g) {
+        if (counts[g])
+            SA_CU(cudaMemcpyAsync(idx->sa_final.as<uint32_t>() + off, d_parts + (size_t)g * stride, (size_t)counts[g] * 4,
+                                  cudaMemcpyDeviceToDevice, idx->stream));
+        off += counts[g];
+    }
+    SA_CU(cudaStreamSynchronize(idx->stream));
+    idx->built = true;
     return SA_OK;
 }

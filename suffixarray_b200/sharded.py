@@ -255,6 +255,11 @@ class ShardBuilder:
         self.torch.cuda.synchronize(self.dev)
         S.check(S.lib().sa_adopt_sa(self.idx._h, self._p(full_sa), self.n))
 
+    def adopt_parts(self, gathered, stride: int, counts):
+        c = np.asarray(counts, dtype=np.uint64)
+        self.torch.cuda.synchronize(self.dev)
+        S.check(S.lib().sa_adopt_sa_parts(self.idx._h, self._p(gathered), int(stride), c.ctypes.data_as(S._vp), int(c.size)))
+
     def close(self):
         self.idx.close()
 
@@ -402,21 +407,25 @@ def _finish_distributed(r, t, lap, adopt, group):
     import torch.distributed as dist
     world = r.world
     mine = torch.from_numpy(_edges_to_array(r.edges())).to(r.dev)
-    rows = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(rows, mine, group=group)
-    edges = [_array_to_edges(x.cpu().numpy()) for x in rows]
+    rows = torch.empty(world * mine.numel(), dtype=mine.dtype, device=r.dev)
+    dist.all_gather_into_tensor(rows, mine, group=group)
+    rows_np = rows.cpu().numpy().reshape(world, -1)
+    edges = [_array_to_edges(rows_np[g]) for g in range(world)]
+    lap("edges")
     sl = r.finish(edges)
     lap("finish")
     if adopt:
         ms = [int(e["m"]) for e in edges]
         mmax = max(max(ms), 1)
-        padded = torch.zeros(mmax, dtype=torch.int32, device=r.dev)
-        padded[: r.m] = sl
+        if r.m == mmax:
+            padded = sl
+        else:
+            padded = torch.zeros(mmax, dtype=torch.int32, device=r.dev)
+            padded[: r.m] = sl
         gathered = torch.empty(world * mmax, dtype=torch.int32, device=r.dev)
         dist.all_gather_into_tensor(gathered, padded, group=group)
-        full = torch.cat([gathered[g * mmax: g * mmax + ms[g]] for g in range(world)])
+        lap("gather")
+        r.adopt_parts(gathered, mmax, ms)
         del gathered, padded
-        r.adopt(full)
-        del full
-        lap("gather+adopt")
+        lap("adopt")
     return r, t
