@@ -14,9 +14,13 @@
 
 namespace sa {
 
-constexpr uint32_t ST_PARTIAL = 1u << 30;
-constexpr uint32_t ST_INCLUSIVE = 2u << 30;
-constexpr uint32_t ST_MASK = (1u << 30) - 1u;
+// Look-back status word of one (tile, digit): 0 = not published; bit 31 clear = the tile's own
+// count + 1; bit 31 set = inclusive prefix over tiles 0..t in the low 31 bits (a prefix is at most
+// n - 1 < 2^31 whenever the pass runs at all: a digit that holds every record skips the pass).
+constexpr uint32_t ST_INCLUSIVE = 1u << 31;
+constexpr uint32_t ST_MASK = ST_INCLUSIVE - 1u;
+__device__ __forceinline__ uint32_t st_partial(uint32_t count) { return count + 1u; }
+__device__ __forceinline__ uint32_t st_value(uint32_t v) { return (v & ST_INCLUSIVE) ? (v & ST_MASK) : v - 1u; }
 constexpr uint32_t LOOKBACK_SPIN_LIMIT = 1u << 26;   // a hung look-back sets d_err and exits
 
 // RANK_MODE 0: match.any.sync; 1: eight ballots (CUB-style warp multisplit)
@@ -124,15 +128,15 @@ onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict
         if (tile == 0) {
             *mine = ST_INCLUSIVE | count;
         } else {
-            *mine = ST_PARTIAL | count;
+            *mine = st_partial(count);
             uint32_t spins = 0;
             for (int64_t p = (int64_t)tile - 1; p >= 0; --p) {
                 volatile uint32_t* st = status + (uint64_t)p * 256 + tid;
                 uint32_t v;
-                while (((v = *st) & (ST_PARTIAL | ST_INCLUSIVE)) == 0) {
+                while ((v = *st) == 0) {
                     if (++spins > LOOKBACK_SPIN_LIMIT) { atomicOr(err, SA_DEVERR_LOOKBACK_TIMEOUT); v = ST_INCLUSIVE; break; }
                 }
-                excl += v & ST_MASK;
+                excl += st_value(v);
                 if (v & ST_INCLUSIVE) break;
             }
             *mine = ST_INCLUSIVE | (excl + count);
@@ -288,7 +292,7 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
                 run += c;
             }
             count = run;
-            st_relaxed_gpu(status + (uint64_t)tile * 256 + tid, (tile == 0 ? ST_INCLUSIVE : ST_PARTIAL) | count);
+            st_relaxed_gpu(status + (uint64_t)tile * 256 + tid, tile == 0 ? (ST_INCLUSIVE | count) : st_partial(count));
         }
         uint32_t inc = count;
 #pragma unroll
@@ -333,8 +337,8 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
 #pragma unroll
                     for (int j = 0; j < LBW; ++j) {
                         if (done || used != j) continue;
-                        if ((v[j] & (ST_PARTIAL | ST_INCLUSIVE)) == 0) continue;      // not published yet: re-poll from here
-                        excl += v[j] & ST_MASK;
+                        if (v[j] == 0) continue;                                      // not published yet: re-poll from here
+                        excl += st_value(v[j]);
                         used = j + 1;
                         if (v[j] & ST_INCLUSIVE) done = true;
                     }

@@ -17,8 +17,8 @@ static int prepare_text(sa_index* idx, uint64_t n, uint32_t flags)
 {
     SA_REQUIRE(idx, SA_ERR_INVALID, "index is NULL");
     SA_REQUIRE(n <= SA_MAX_N, SA_ERR_LIMIT, "n = %llu exceeds the uint32 position range", (unsigned long long)n);
-    SA_REQUIRE(n < (1ull << 30), SA_ERR_LIMIT,
-               "n = %llu: this build supports < 2^30 bytes per index (onesweep status words)",
+    SA_REQUIRE(n <= SA_MAX_INDEX_BYTES, SA_ERR_LIMIT,
+               "n = %llu: one index holds at most 2^31 bytes (the reference's partition size, suffix_array.pyx:148)",
                (unsigned long long)n);
     SA_CU(cudaSetDevice(idx->device));
     idx->timing = (flags & SA_FLAG_TIMING) != 0;

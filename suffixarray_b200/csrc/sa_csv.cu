@@ -166,7 +166,7 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
 
     const uint64_t n = scan_column(FileView{m.p, m.size}, (uint32_t)col, (uint32_t)cells.size(), h_text.as<uint8_t>(),
                                    h_map.as<uint32_t>(), h_q.as<uint8_t>());
-    if (n >= (1ull << 30)) { sa_set_error("column text of %llu bytes exceeds the 2^30 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
+    if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
 
     idx->timing = (flags & SA_FLAG_TIMING) != 0;
     idx->n = n;

@@ -46,6 +46,7 @@ enum SmallSlot : uint32_t {
     SM_WORDS = 4432
 };
 
+constexpr uint64_t SA_MAX_INDEX_BYTES = 1ull << 31;   // records per index: look-back prefixes are 31-bit
 constexpr size_t H_SMALL_WORDS = 1024;   // [0,64) misc, [256,512) byte presence, [512,576) code table
 
 struct PhaseTimer {

@@ -351,7 +351,7 @@ extern "C" int sa_shard_split(sa_index* idx, const uint64_t* d_keys, const uint3
 extern "C" int sa_shard_sort(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m64)
 {
     SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_sort: call sa_shard_begin first");
-    SH_REQUIRE(m64 < (1ull << 30), SA_ERR_LIMIT, "sa_shard_sort: %llu records exceed the 2^30 per-GPU limit",
+    SH_REQUIRE(m64 <= SA_MAX_INDEX_BYTES, SA_ERR_LIMIT, "sa_shard_sort: %llu records exceed the 2^31 per-GPU limit",
                (unsigned long long)m64);
     std::lock_guard<std::mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
@@ -495,7 +495,7 @@ extern "C" int sa_shard_count(sa_index* idx, const uint64_t* d_keys, uint64_t m6
 extern "C" int sa_shard_recv_prepare(sa_index* idx, uint64_t m_recv, uint8_t* handle_keys, uint8_t* handle_pos)
 {
     SH_REQUIRE(idx && idx->shard_prepared && handle_keys && handle_pos, SA_ERR_INVALID, "sa_shard_recv_prepare: bad argument");
-    SH_REQUIRE(m_recv < (1ull << 30), SA_ERR_LIMIT, "sa_shard_recv_prepare: %llu records exceed the 2^30 per-GPU limit",
+    SH_REQUIRE(m_recv <= SA_MAX_INDEX_BYTES, SA_ERR_LIMIT, "sa_shard_recv_prepare: %llu records exceed the 2^31 per-GPU limit",
                (unsigned long long)m_recv);
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     std::lock_guard<std::mutex> lock(idx->mu);
@@ -581,7 +581,7 @@ extern "C" int sa_shard_scatter_p2p(sa_index* idx, const uint64_t* d_keys, const
 extern "C" int sa_shard_sort_recv(sa_index* idx, uint64_t m64)
 {
     SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_sort_recv: call sa_shard_begin first");
-    SH_REQUIRE(m64 < (1ull << 30), SA_ERR_LIMIT, "sa_shard_sort_recv: too many records");
+    SH_REQUIRE(m64 <= SA_MAX_INDEX_BYTES, SA_ERR_LIMIT, "sa_shard_sort_recv: too many records");
     std::lock_guard<std::mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     const uint32_t m = (uint32_t)m64;

@@ -29,10 +29,17 @@ from . import _lib as S
 
 
 class SuffixArray:
+    # The reference cuts the joined text every 2 GiB into independent partitions, each with its own
+    # suffix array, and a query walks them in order until k records are found
+    # (suffix_array.pyx:148-180, :221-247).  Same here; tests shrink this to exercise the walk.
+    PARTITION_BYTES = 1 << 31
+
     def __init__(self, max_suffix_length: int = 64, documents=None, csv_file: str | None = None,
                  search_column: str | None = None, device: int = 0):
         self.max_suffix_length = int(max_suffix_length)
+        self._device = device
         self._idx = S.Index(self.max_suffix_length, device=device)
+        self._parts = [self._idx]    # one Index per partition; _idx is partition 0
         self._mode = None            # "documents" | "csv"
         self._text = None            # documents: the joined, lower-cased utf-8 bytes (host copy)
         self._doc_starts = None
@@ -59,10 +66,20 @@ class SuffixArray:
                 raise ValueError("Documents must be a list of strings")
         joined = "\n".join(documents).encode("utf-8")           # pyx:143 (no trailing '\n')
         text = np.frombuffer(joined, dtype=np.uint8)
-        # lowercase_string (pyx:103-107) runs on the device copy: SA_FLAG_LOWERCASE
-        self._idx.build_text(text, lowercase=True)
-        self._text = self._idx.text().tobytes()                 # the bytes that were indexed
-        self._doc_starts = self._idx.doc_starts().astype(np.int64)
+        pb = int(self.PARTITION_BYTES)
+        nparts = max(1, -(-text.size // pb))                    # pyx:148-152
+        for old in self._parts[1:]:
+            old.close()
+        self._parts = [self._idx] + [S.Index(self.max_suffix_length, device=self._device) for _ in range(nparts - 1)]
+        for i, idx in enumerate(self._parts):                   # pyx:173-180: cut at fixed byte offsets
+            # lowercase_string (pyx:103-107) runs on the device copy: SA_FLAG_LOWERCASE
+            idx.build_text(text[i * pb:(i + 1) * pb], lowercase=True)
+        low = text.copy()                                       # host copy of what was indexed
+        up = (low >= 65) & (low <= 90)
+        low[up] += 32
+        self._text = low.tobytes()
+        nl = np.flatnonzero(low == 10).astype(np.int64)
+        self._doc_starts = np.concatenate([[0], nl + 1]).astype(np.int64)
         self._mode = "documents"
 
     def construct_truncated_suffix_array_from_csv(self, filename: str, search_column: str) -> None:
@@ -107,13 +124,33 @@ class SuffixArray:
         out = [[] for _ in qs]
         if not nonempty:
             return out
-        start, end, off = self._idx.query_ranges([qs[i] for i in nonempty], k=int(k))
-        total = int(off[-1])
-        pos, doc = self._idx.query_hits(total)
+        sub = [qs[i] for i in nonempty]
+        start, end, off = self._idx.query_ranges(sub, k=int(k))
+        pos, doc = self._idx.query_hits(int(off[-1]))
+        if len(self._parts) == 1:
+            for j, i in enumerate(nonempty):
+                out[i] = self._materialise(doc[int(off[j]):int(off[j + 1])])
+            return out
+        # several partitions: walk them in order until k records are found (pyx:221-247)
+        pb = int(self.PARTITION_BYTES)
+        docs = [self._docs_of(pos[int(off[j]):int(off[j + 1])].astype(np.int64)) for j in range(len(sub))]
+        for p, idx in enumerate(self._parts[1:], start=1):
+            need = [j for j in range(len(sub)) if len(docs[j]) < k]
+            if not need:
+                break
+            kk = max(int(k) - len(docs[j]) for j in need)
+            s2, e2, off2 = idx.query_ranges([sub[j] for j in need], k=kk)
+            pos2, _ = idx.query_hits(int(off2[-1]))
+            for t, j in enumerate(need):
+                take = pos2[int(off2[t]):int(off2[t + 1])][: int(k) - len(docs[j])].astype(np.int64) + p * pb
+                docs[j] = np.concatenate([docs[j], self._docs_of(take)])
         for j, i in enumerate(nonempty):
-            lo, hi = int(off[j]), int(off[j + 1])
-            out[i] = self._materialise(doc[lo:hi])
+            out[i] = self._materialise(docs[j])
         return out
+
+    def _docs_of(self, global_pos: np.ndarray) -> np.ndarray:
+        """record index of text positions (documents path): number of '\n' before the position."""
+        return np.searchsorted(self._doc_starts, global_pos, side="right") - 1
 
     def query_positions(self, substrings, k: int = 1000):
         """-> (start, end, hit_off, hit_pos, hit_doc) NumPy arrays straight from the C ABI."""
@@ -141,14 +178,16 @@ class SuffixArray:
     @property
     def suffix_array(self) -> np.ndarray:
         """uint32 array as SuffixArray_struct.suffix_array holds it (file offsets on the CSV path)."""
-        return self._idx.sa()
+        return self._idx.sa() if len(self._parts) == 1 else [idx.sa() for idx in self._parts]
 
     def stats(self) -> dict:
         return self._idx.stats()
 
     def close(self) -> None:
         if self._idx is not None:
-            self._idx.close()
+            for idx in self._parts:
+                idx.close()
+            self._parts = []
             self._idx = None
         if self._csv_mm is not None:
             self._row_starts = self._row_ends = None

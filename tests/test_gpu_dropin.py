@@ -78,3 +78,30 @@ def test_csv_constructor_rows():
         sa.close()
     finally:
         os.unlink(path)
+
+
+def test_partitioned_documents_walk(monkeypatch):
+    """suffix_array.pyx:148-180 / :221-247: fixed-size byte partitions, each with its own suffix array
+    (bit-exact vs the oracle per partition); a query walks them in order until k records are found."""
+    names = W.company_names(400, seed=91, upper=True)
+    docs = [b.decode() for b in names]
+    monkeypatch.setattr(SuffixArray, "PARTITION_BYTES", 1500)
+    sa = SuffixArray(documents=docs, max_suffix_length=32)
+    text = O.oracle_lowercase(np.frombuffer("\n".join(docs).encode(), np.uint8))
+    arrays = sa.suffix_array
+    assert len(arrays) == -(-text.size // 1500) and len(arrays) > 3
+    for p, got in enumerate(arrays):
+        assert np.array_equal(got, O.oracle_build(text[p * 1500:(p + 1) * 1500], 32))
+    low = [d.lower() for d in docs]
+    starts = np.concatenate([[0], np.flatnonzero(text == 10) + 1])
+    for q, k in (("inc", 7), ("a", 40), ("group", 1000), (low[13], 5)):
+        want = []
+        for p in range(len(arrays)):                        # the reference's walk, on the oracle
+            part = text[p * 1500:(p + 1) * 1500]
+            s, e = O.oracle_query(part, arrays[p], 32, [q.encode()])
+            off, pos, _ = O.oracle_hits(part, arrays[p], s, e, k - len(want))
+            want += [low[int(np.searchsorted(starts, int(x) + p * 1500, side="right") - 1)] for x in pos]
+            if len(want) >= k:
+                break
+        assert sa.query_records(q, k=k) == want
+    sa.close()
