@@ -205,6 +205,9 @@ def run_ours(args):
     idx_dev = S.Index(L, device=local)              # device-resident leg
     idx_e2e = S.Index(L, device=local)              # host-buffer leg
     lib = S.lib()
+    for kv in (os.environ.get("SA_BENCH_DEBUG") or "").split(","):   # tuning experiments: key=value,...
+        if "=" in kv:
+            idx_dev.debug_set(kv.split("=")[0], int(kv.split("=")[1]))
     vp = S._vp
 
     h_hits = {"pos": None, "doc": None, "cap": 0}

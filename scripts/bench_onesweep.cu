@@ -20,6 +20,8 @@ typedef cudaError_t (*launch_fn)(const uint64_t*, const uint32_t*, uint64_t*, ui
 struct Variant { const char* name; launch_fn fn; int tile; };
 
 #define V2(T, I, M, R, W) Variant{"v2 " #T "x" #I " minb" #M " rank" #R " lbw" #W, sa::launch_onesweep2_cfg<T, I, M, R, W>, T * I}
+#define V3(T, I, M, R, W) Variant{"v3pf " #T "x" #I " minb" #M " rank" #R " lbw" #W, sa::launch_onesweep2_cfg<T, I, M, R, W, true>, T * I}
+#define V4(I, M, W, R) Variant{"v4ws 256x" #I " minb" #M " lbw" #W " lbregs" #R, sa::launch_onesweep4_cfg<I, M, W, R>, 256 * I}
 #define V(T, I, M, R) Variant{#T "x" #I " minb" #M " rank" #R, sa::launch_onesweep_cfg<T, I, M, R>, T * I}
 
 __global__ void pack_text_keys(const uint8_t* text, uint32_t n, uint64_t* keys)
@@ -50,6 +52,11 @@ int main(int argc, char** argv)
     const int first_input = argc > 4 ? atoi(argv[4]) : 0;
     std::vector<Variant> variants = {
         V(256, 16, 2, 0), V(384, 8, 3, 0), V(512, 8, 2, 1),
+        V3(256, 16, 2, 0, 8), V3(256, 16, 2, 1, 8), V3(256, 16, 2, 0, 4), V3(512, 8, 2, 0, 8), V3(512, 8, 2, 1, 8),
+        V3(256, 16, 2, 0, 16), V3(256, 16, 2, 0, 32), V3(256, 16, 2, 1, 16), V3(256, 16, 2, 1, 32),
+        V3(512, 16, 1, 0, 8), V3(512, 16, 1, 0, 4), V3(1024, 8, 1, 0, 8), V3(256, 10, 3, 0, 8), V3(512, 12, 1, 0, 8),
+        V4(12, 2, 8, 32), V4(12, 2, 4, 24), V4(14, 2, 8, 32), V4(14, 2, 4, 24), V4(16, 2, 8, 32), V4(16, 2, 4, 24), V4(10, 2, 8, 32),
+        V3(256, 12, 2, 0, 8), V3(384, 8, 2, 0, 8), V3(256, 8, 4, 0, 8), V3(256, 8, 3, 0, 8), V3(384, 10, 2, 0, 8),
         V2(256, 16, 2, 0, 1), V2(256, 16, 2, 0, 4), V2(256, 16, 2, 0, 8), V2(256, 16, 2, 1, 4),
         V2(384, 8, 3, 0, 4), V2(384, 8, 3, 0, 8), V2(512, 8, 2, 0, 4), V2(512, 8, 2, 1, 4), V2(512, 8, 2, 1, 8),
         V2(256, 8, 4, 0, 4), V2(256, 8, 4, 1, 4), V2(256, 12, 3, 0, 4), V2(384, 10, 2, 0, 4), V2(512, 6, 3, 0, 4),
@@ -121,6 +128,17 @@ int main(int argc, char** argv)
                 CK(cudaEventElapsedTime(&first_pass, ev[0], ev[1]));
                 if (tot / 7 < best) best = tot / 7;
             }
+#ifdef OS_PHASE_CLOCKS
+            {
+                unsigned long long ph[8], z[8] = {0};
+                CK(cudaMemcpyFromSymbol(ph, sa::os_phase_cycles, sizeof ph));
+                CK(cudaMemcpyToSymbol(sa::os_phase_cycles, z, sizeof z));
+                double tot = 0; for (int i = 0; i < 8; ++i) tot += (double)ph[i];
+                printf("   thread-0 cycle shares: zero+sync %.1f%% | load %.1f%% | rank+sync %.1f%% | scan %.1f%% | reorder %.1f%% | lookback(t0)/v4:issue next loads %.1f%% | sync(after lookback)/v4:wait offsets %.1f%% | store %.1f%%   (cycles/tile %.0f)\n",
+                       100 * ph[0] / tot, 100 * ph[1] / tot, 100 * ph[2] / tot, 100 * ph[3] / tot, 100 * ph[4] / tot, 100 * ph[5] / tot,
+                       100 * ph[6] / tot, 100 * ph[7] / tot, tot / (8.0 * reps * ((n + v.tile - 1) / v.tile)));
+            }
+#endif
             printf("%-22s tile %5d  pass %.3f ms  %7.1f GB/s  (identity pass %.3f ms)  %s%s\n", v.name, v.tile, best,
                    24.0 * n / (best * 1e-3) / 1e9, first_pass, bad ? "NOT SORTED " : "ok", herr ? " DEVERR" : "");
             fflush(stdout);

@@ -52,6 +52,37 @@ __device__ __forceinline__ int warp_suffix_max(int v, int lane)
     return v;
 }
 
+// (h2, l2, t2) < (hi, lo, tp) in lexicographic order = the borrow out of the 192-bit subtraction;
+// returns 0xFFFFFFFF when less, else 0.
+__device__ __forceinline__ uint32_t less192(uint64_t h2, uint64_t l2, uint64_t t2, uint64_t hi, uint64_t lo, uint64_t tp)
+{
+    uint32_t r;
+    asm("{\n"
+        ".reg .u32 t;\n"
+        "sub.cc.u32 t, %1, %7;\n"
+        "subc.cc.u32 t, %2, %8;\n"
+        "subc.cc.u32 t, %3, %9;\n"
+        "subc.cc.u32 t, %4, %10;\n"
+        "subc.cc.u32 t, %5, %11;\n"
+        "subc.cc.u32 t, %6, %12;\n"
+        "subc.u32 %0, 0, 0;\n"
+        "}"
+        : "=r"(r)
+        : "r"((uint32_t)t2), "r"((uint32_t)(t2 >> 32)), "r"((uint32_t)l2), "r"((uint32_t)(l2 >> 32)), "r"((uint32_t)h2),
+          "r"((uint32_t)(h2 >> 32)), "r"((uint32_t)tp), "r"((uint32_t)(tp >> 32)), "r"((uint32_t)lo),
+          "r"((uint32_t)(lo >> 32)), "r"((uint32_t)hi), "r"((uint32_t)(hi >> 32)));
+    return r;
+}
+
+// text gathers are the only re-used stream of this kernel: ask L2 to keep them (evict_last), the
+// rank-ordered streams go through with evict-first hints (__ldcs / __stcs)
+__device__ __forceinline__ uint64_t ld_keep_u64(const uint64_t* p, uint64_t policy)
+{
+    uint64_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(policy));
+    return v;
+}
+
 __global__ void __launch_bounds__(FTHREADS)
 finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ lcp,
               const uint8_t* __restrict__ text, uint32_t n, uint32_t lprime, uint32_t r_begin, uint32_t r_end,
@@ -66,6 +97,8 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t b0 = (int64_t)blockIdx.x * FT;
+    uint64_t keep;
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
     if (tid == 0) s_runs = 0;
     for (int j = tid; j < FLCP; j += FTHREADS) {
         const int64_t r = b0 - 64 + j;
@@ -121,7 +154,8 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
                 const uint64_t a = (uint64_t)pos + (uint32_t)d;
                 const uint64_t a0 = d ? a - 1 : a;
                 const uint64_t* wp = reinterpret_cast<const uint64_t*>(text + (a0 & ~7ull));
-                const uint64_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3);
+                const uint64_t w0 = ld_keep_u64(wp, keep), w1 = ld_keep_u64(wp + 1, keep), w2 = ld_keep_u64(wp + 2, keep),
+                               w3 = ld_keep_u64(wp + 3, keep);
                 uint32_t o = (uint32_t)(a - (a0 & ~7ull));       // 0..8: offset of the window in the 32 bytes
                 bool term = false;
                 if (d) {
@@ -182,11 +216,8 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
         if (X == 0 || last - first + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); __stcs(sa_out + r, pos); continue; }
         const uint64_t hi = s_hi[e], lo = s_lo[e];
         uint32_t rank = 0;
-        for (int x = first; x <= last; ++x) {               // branch-free (key, byte 16, position) compare
-            const uint64_t h2 = s_hi[x], l2 = s_lo[x], t2 = s_tp[x];
-            const uint32_t lt_t = t2 < tp, lt_l = l2 < lo, eq_l = l2 == lo, lt_h = h2 < hi, eq_h = h2 == hi;
-            rank += lt_h | (eq_h & (lt_l | (eq_l & lt_t)));
-        }
+        for (int x = first; x <= last; ++x)                 // branch-free (key, byte 16, position) compare
+            rank -= less192(s_hi[x], s_lo[x], s_tp[x], hi, lo, tp);
         __stcs(sa_out + (r - (e - first) + rank), pos);
         if (e == first) ++my_runs;
     }

@@ -213,7 +213,59 @@ __device__ __forceinline__ void st_relaxed_gpu(uint32_t* p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-template <int THREADS, int IPT, int MINB, bool IDENTITY_VALS, int RANK_MODE, int LBW>
+// Per-phase clock accounting for scripts/bench_onesweep.cu (compiled in only with -DOS_PHASE_CLOCKS)
+#ifdef OS_PHASE_CLOCKS
+__device__ unsigned long long os_phase_cycles[8];
+#define OS_CLK(k)                                                                   \
+    do {                                                                            \
+        if (tid == 0) { const long long c_ = clock64(); atomicAdd(&os_phase_cycles[k], (unsigned long long)(c_ - clk_)); clk_ = c_; } \
+    } while (0)
+#define OS_CLK_INIT long long clk_ = clock64()
+#else
+#define OS_CLK(k) do { } while (0)
+#define OS_CLK_INIT do { } while (0)
+#endif
+
+// --- bulk-copy (TMA, 1-D) prefetch of the next tile into a shared-memory stage, completion on an mbarrier
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "W_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@!p bra W_%=;\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+template <int THREADS, int IPT, bool PF>
+constexpr size_t onesweep2_smem_bytes()
+{
+    return onesweep_smem_bytes<THREADS, IPT>() + (PF ? (size_t)THREADS * IPT * 12 + 16 : 0);
+}
+
+// PF: the next tile's keys / values are bulk-copied into a second shared-memory stage while the
+// current tile is scanned, re-ordered and written out (needs 16-byte aligned inputs).
+template <int THREADS, int IPT, int MINB, bool IDENTITY_VALS, int RANK_MODE, int LBW, bool PF>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n, int shift,
@@ -229,20 +281,41 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
     uint32_t* whist = vals_s + TILE;                                           // WARPS*256
     uint32_t* tile_start = whist + WARPS * 256;                                // 256
     uint32_t* gofs = tile_start + 256;                                         // 256
-    uint32_t* wsum = gofs + 256;                                               // 8
+    uint32_t* wsum = gofs + 256;                                               // 16
+    uint64_t* bar = reinterpret_cast<uint64_t*>(wsum + 16);                    // PF: mbarrier
+    uint64_t* stage_k = bar + 2;                                               // PF: TILE keys
+    uint32_t* stage_v = reinterpret_cast<uint32_t*>(stage_k + TILE);           // PF: TILE values
     __shared__ uint32_t s_tile[2];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t lt = lanemask_lt();
     uint32_t* myhist = whist + warp * 256;
-    if (tid == 0) s_tile[0] = atomicAdd(tile_counter, 1u);
+    const uint32_t full_tiles = n / (uint32_t)TILE;          // tiles below this index are complete
+    uint32_t phase = 0, next_tile = 0;
+    if (tid == 0) {
+        const uint32_t t0 = atomicAdd(tile_counter, 1u);
+        s_tile[0] = t0;
+        if (PF) {
+            mbar_init(bar, 1);
+            if (t0 < full_tiles) {
+                mbar_expect_tx(bar, (uint32_t)TILE * (IDENTITY_VALS ? 8u : 12u));
+                bulk_g2s(stage_k, keys_in + (uint64_t)t0 * TILE, (uint32_t)TILE * 8u, bar);
+                if (!IDENTITY_VALS) bulk_g2s(stage_v, vals_in + (uint64_t)t0 * TILE, (uint32_t)TILE * 4u, bar);
+            }
+        }
+    }
     int buf = 0;
+    OS_CLK_INIT;
     for (;;) {
         for (int i = tid; i < WARPS * 256; i += THREADS) whist[i] = 0;
         __syncthreads();                                     // s_tile[buf] + zeroed counters visible
+        OS_CLK(0);
         const uint32_t tile = s_tile[buf];
         if (tile >= num_tiles) return;
-        if (tid == 0) s_tile[buf ^ 1] = atomicAdd(tile_counter, 1u);   // next tile, latency hidden
+        if (tid == 0) {
+            next_tile = atomicAdd(tile_counter, 1u);         // next tile, latency hidden
+            s_tile[buf ^ 1] = next_tile;
+        }
         buf ^= 1;
         const uint32_t base = tile * (uint32_t)TILE;
         const uint32_t tile_n = (n - base) < (uint32_t)TILE ? (n - base) : (uint32_t)TILE;
@@ -252,18 +325,34 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
         uint64_t key[IPT];
         uint32_t val[IPT];
         uint32_t rank[IPT];
+        if (PF && full) {
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+            const int sb = warp * (32 * IPT) + lane;
 #pragma unroll
-        for (int i = 0; i < IPT; ++i) {
-            const uint32_t idx = wbase + i * 32;
-            key[i] = (full || idx < n) ? ld_stream_u64(keys_in + idx) : ~0ull;
-        }
-        if (!IDENTITY_VALS) {
+            for (int i = 0; i < IPT; ++i) key[i] = stage_k[sb + i * 32];
+            if (!IDENTITY_VALS) {
+#pragma unroll
+                for (int i = 0; i < IPT; ++i) val[i] = stage_v[sb + i * 32];
+            }
+        } else {
 #pragma unroll
             for (int i = 0; i < IPT; ++i) {
                 const uint32_t idx = wbase + i * 32;
-                val[i] = (full || idx < n) ? ld_stream_u32(vals_in + idx) : 0u;
+                key[i] = (full || idx < n) ? ld_stream_u64(keys_in + idx) : ~0ull;
+            }
+            if (!IDENTITY_VALS) {
+#pragma unroll
+                for (int i = 0; i < IPT; ++i) {
+                    const uint32_t idx = wbase + i * 32;
+                    val[i] = (full || idx < n) ? ld_stream_u32(vals_in + idx) : 0u;
+                }
             }
         }
+#ifdef OS_PHASE_CLOCKS
+        if (tid == 0 && key[IPT - 1] == 0x123456789ull) clk_ += 1;   // wait for the loads
+#endif
+        OS_CLK(1);
 #pragma unroll
         for (int i = 0; i < IPT; ++i) {
             const bool valid = full || (wbase + i * 32) < n;
@@ -280,6 +369,13 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
             __syncwarp();
         }
         __syncthreads();
+        OS_CLK(2);
+        if (PF && tid == 0 && next_tile < full_tiles) {       // the stage has been consumed: refill it
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_expect_tx(bar, (uint32_t)TILE * (IDENTITY_VALS ? 8u : 12u));
+            bulk_g2s(stage_k, keys_in + (uint64_t)next_tile * TILE, (uint32_t)TILE * 8u, bar);
+            if (!IDENTITY_VALS) bulk_g2s(stage_v, vals_in + (uint64_t)next_tile * TILE, (uint32_t)TILE * 4u, bar);
+        }
 
         // per digit: exclusive scan over warps; publish this tile's count at once
         uint32_t count = 0;
@@ -310,6 +406,7 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
             tile_start[tid] = ts;
         }
         __syncthreads();
+        OS_CLK(3);
         // re-order the tile in shared memory (stable: digit, then warp, then item order)
 #pragma unroll
         for (int i = 0; i < IPT; ++i) {
@@ -321,9 +418,17 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
                 vals_s[lp] = IDENTITY_VALS ? idx : val[i];
             }
         }
+        OS_CLK(4);
         // windowed decoupled look-back, as late as possible
         if (tid < 256) {
             uint32_t excl = 0;
+#ifdef OS_FAKE_LOOKBACK   // timing experiment only (wrong output): no waiting on predecessors
+            if (true) {
+                const uint32_t tot = (tid == 255 ? n : digit_base[tid + 1]) - digit_base[tid];
+                excl = (uint32_t)((uint64_t)tile * tot / num_tiles);
+                if (excl + count > tot) excl = tot > count ? tot - count : 0;
+            } else
+#endif
             if (tile != 0) {
                 uint32_t spins = 0;
                 int64_t p = (int64_t)tile - 1;
@@ -349,7 +454,9 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
             }
             gofs[tid] = digit_base[tid] + excl - ts;     // global index = gofs[d] + position in tile
         }
+        OS_CLK(5);
         __syncthreads();
+        OS_CLK(6);
         if (full) {
 #pragma unroll
             for (int i = 0; i < IPT; ++i) {
@@ -367,11 +474,12 @@ onesweep2_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
                 vals_out[g] = vals_s[j];
             }
         }
+        OS_CLK(7);
         __syncthreads();       // keys_s / gofs / whist are reused by the next tile
     }
 }
 
-template <int THREADS, int IPT, int MINB, int RANK_MODE, int LBW>
+template <int THREADS, int IPT, int MINB, int RANK_MODE, int LBW, bool PF = false>
 cudaError_t launch_onesweep2_cfg(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                                  uint32_t* vals_out, uint32_t n, int shift, const uint32_t* digit_base,
                                  uint32_t* status, uint32_t* tile_counter, uint32_t* err, bool identity_vals,
@@ -379,7 +487,11 @@ cudaError_t launch_onesweep2_cfg(const uint64_t* keys_in, const uint32_t* vals_i
 {
     if (n == 0) return cudaSuccess;
     constexpr uint32_t TILE = THREADS * IPT;
-    constexpr size_t SMEM = onesweep_smem_bytes<THREADS, IPT>();
+    constexpr size_t SMEM = onesweep2_smem_bytes<THREADS, IPT, PF>();
+    if (PF && ((((uintptr_t)keys_in) | ((uintptr_t)vals_in)) & 15u))        // bulk copies need 16-byte alignment
+        return launch_onesweep2_cfg<THREADS, IPT, MINB, RANK_MODE, LBW, false>(keys_in, vals_in, keys_out, vals_out, n, shift,
+                                                                               digit_base, status, tile_counter, err,
+                                                                               identity_vals, s);
     const uint32_t tiles = (n + TILE - 1) / TILE;
     cudaError_t e = cudaMemsetAsync(status, 0, (size_t)tiles * 256 * sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
@@ -387,8 +499,8 @@ cudaError_t launch_onesweep2_cfg(const uint64_t* keys_in, const uint32_t* vals_i
     if (e != cudaSuccess) return e;
     static int grid = 0;
     if (!grid) {
-        auto k1 = onesweep2_kernel<THREADS, IPT, MINB, true, RANK_MODE, LBW>;
-        auto k0 = onesweep2_kernel<THREADS, IPT, MINB, false, RANK_MODE, LBW>;
+        auto k1 = onesweep2_kernel<THREADS, IPT, MINB, true, RANK_MODE, LBW, PF>;
+        auto k0 = onesweep2_kernel<THREADS, IPT, MINB, false, RANK_MODE, LBW, PF>;
         cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
         cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
         int dev = 0, sms = 148, per_sm = 1;
@@ -400,11 +512,285 @@ cudaError_t launch_onesweep2_cfg(const uint64_t* keys_in, const uint32_t* vals_i
     }
     const uint32_t g = tiles < (uint32_t)grid ? tiles : (uint32_t)grid;
     if (identity_vals)
-        onesweep2_kernel<THREADS, IPT, MINB, true, RANK_MODE, LBW><<<g, THREADS, SMEM, s>>>(
+        onesweep2_kernel<THREADS, IPT, MINB, true, RANK_MODE, LBW, PF><<<g, THREADS, SMEM, s>>>(
             keys_in, vals_in, keys_out, vals_out, n, shift, digit_base, status, tile_counter, err, tiles);
     else
-        onesweep2_kernel<THREADS, IPT, MINB, false, RANK_MODE, LBW><<<g, THREADS, SMEM, s>>>(
+        onesweep2_kernel<THREADS, IPT, MINB, false, RANK_MODE, LBW, PF><<<g, THREADS, SMEM, s>>>(
             keys_in, vals_in, keys_out, vals_out, n, shift, digit_base, status, tile_counter, err, tiles);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// v4: warp-specialised pass.  Each persistent CTA has 8 ranking warps and one look-back warp:
+//   * ranking warps: rank + scan + shared-memory re-order of tile i into buffer i&1, then issue the
+//     global loads of tile i+1 into registers, then write tile i-1 out of buffer (i-1)&1
+//   * look-back warp: as soon as tile i's digit counts exist it runs the windowed decoupled
+//     look-back for all 256 digits (8 per lane) and publishes the inclusive prefixes; the result
+//     (global offset per digit) is only needed one tile later, so the chain of L2 round trips the
+//     look-back costs (~3-5 per tile at B200 tile rates) is off the ranking warps' critical path.
+// Named barriers: 1 = ranking warps only; 2+b = "counts of buffer b ready" (ranking warps arrive,
+// look-back warp waits); 4+b = "offsets of buffer b ready" (look-back warp arrives, ranking warps wait).
+__device__ __forceinline__ void named_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void named_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+template <int IPT>
+constexpr size_t onesweep4_smem_bytes()
+{
+    return (size_t)256 * IPT * 12 * 2 + 8 * 256 * 4 + 4 * 256 * 4 + 64;
+}
+
+template <int IPT, int MINB, bool IDENTITY_VALS, int LBW, int LB_REGS>
+__global__ void __launch_bounds__(512, MINB)
+onesweep4_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                 uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n, int shift,
+                 const uint32_t* __restrict__ digit_base, uint32_t* status, uint32_t* tile_counter,
+                 uint32_t* err, uint32_t num_tiles)
+{
+    constexpr int MAIN = 256, WARPS = 8, ALL = 512;
+    constexpr int MAIN_REGS = 128 - LB_REGS;      // 256 * (LB + MAIN) = the CTA's half of the register file
+    static_assert(IPT % 2 == 0, "ranks are packed in pairs");
+    constexpr int TILE = MAIN * IPT;
+    constexpr uint32_t NO_TILE = 0xFFFFFFFFu;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* keys_s = reinterpret_cast<uint64_t*>(smem_raw);                 // 2 * TILE
+    uint32_t* vals_s = reinterpret_cast<uint32_t*>(keys_s + 2 * TILE);        // 2 * TILE
+    uint32_t* whist = vals_s + 2 * TILE;                                       // WARPS * 256
+    uint32_t* tst = whist + WARPS * 256;                                       // 2 * 256: digit start inside the tile
+    uint32_t* cnt = tst + 512;                                                 // 2 * 256: digit count, later global offset
+    uint32_t* wsum = cnt + 512;                                                // 8
+    uint32_t* s_tile = wsum + 8;                                               // 4: ring of tile ids
+    uint32_t* s_lbtile = s_tile + 4;                                           // 2: tile of buffer b for the look-back warp
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (warp >= WARPS) {
+        // ------------------------------------------------------------------ look-back warps (one digit per thread)
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(LB_REGS));
+        const int d = tid - MAIN;
+        const uint32_t dbase = digit_base[d];
+        for (uint32_t it = 0;; ++it) {
+            const int b = it & 1;
+            named_sync(2 + b, ALL);
+            const uint32_t tile = s_lbtile[b];
+            if (tile == NO_TILE) return;
+            const uint32_t count = cnt[b * 256 + d];
+            uint32_t excl = 0;
+            if (tile != 0) {
+                uint32_t spins = 0;
+                int64_t p = (int64_t)tile - 1;
+                bool done = false;
+                while (!done) {
+                    uint32_t v[LBW];
+#pragma unroll
+                    for (int j = 0; j < LBW; ++j)
+                        v[j] = (p - j >= 0) ? ld_relaxed_gpu(status + (uint64_t)(p - j) * 256 + d) : ST_INCLUSIVE;
+                    int used = 0;
+#pragma unroll
+                    for (int j = 0; j < LBW; ++j) {
+                        if (done || used != j) continue;
+                        if (v[j] == 0) continue;
+                        excl += st_value(v[j]);
+                        used = j + 1;
+                        if (v[j] & ST_INCLUSIVE) done = true;
+                    }
+                    p -= used;
+                    if (used == 0 && ++spins > LOOKBACK_SPIN_LIMIT) { atomicOr(err, SA_DEVERR_LOOKBACK_TIMEOUT); done = true; }
+                }
+                st_relaxed_gpu(status + (uint64_t)tile * 256 + d, ST_INCLUSIVE | (excl + count));
+            }
+            cnt[b * 256 + d] = dbase + excl - tst[b * 256 + d];   // global index = offset + position in tile
+            named_arrive(4 + b, ALL);
+        }
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MAIN_REGS));
+
+    // ---------------------------------------------------------------------- ranking warps
+    const uint32_t lt = lanemask_lt();
+    uint32_t* myhist = whist + warp * 256;
+    uint64_t key[IPT];
+    uint32_t val[IPT];
+    uint32_t rank2[IPT / 2];                                 // two 16-bit ranks per register
+    if (tid == 0) s_tile[0] = atomicAdd(tile_counter, 1u);
+    named_sync(1, MAIN);
+    {
+        const uint32_t t0 = s_tile[0];
+        const uint32_t wb = t0 * (uint32_t)TILE + warp * (32 * IPT) + lane;
+        if (t0 < num_tiles) {
+#pragma unroll
+            for (int i = 0; i < IPT; ++i) key[i] = (wb + i * 32 < n) ? ld_stream_u64(keys_in + wb + i * 32) : ~0ull;
+            if (!IDENTITY_VALS) {
+#pragma unroll
+                for (int i = 0; i < IPT; ++i) val[i] = (wb + i * 32 < n) ? ld_stream_u32(vals_in + wb + i * 32) : 0u;
+            }
+        }
+    }
+    uint32_t prev_n = 0;
+    OS_CLK_INIT;
+    for (uint32_t it = 0;; ++it) {
+        const int b = it & 1;
+        for (int i = tid; i < WARPS * 256; i += MAIN) whist[i] = 0;
+        named_sync(1, MAIN);                                  // zeroed counters + s_tile[it & 3] visible
+        OS_CLK(0);
+        const uint32_t tile = s_tile[it & 3];
+        const bool valid = tile < num_tiles;
+        uint32_t tile_n = 0;
+        if (valid) {
+            if (tid == 0) s_tile[(it + 1) & 3] = atomicAdd(tile_counter, 1u);
+            const uint32_t base = tile * (uint32_t)TILE;
+            tile_n = (n - base) < (uint32_t)TILE ? (n - base) : (uint32_t)TILE;
+            const uint32_t wbase = base + warp * (32 * IPT) + lane;
+            const bool full = tile_n == (uint32_t)TILE;
+#ifdef OS_PHASE_CLOCKS
+            if (tid == 0 && key[IPT - 1] == 0x123456789ull) clk_ += 1;   // wait for the loads
+#endif
+            OS_CLK(1);
+#pragma unroll
+            for (int i = 0; i < IPT; ++i) {
+                const bool ok = full || (wbase + i * 32) < n;
+                const uint32_t d = (uint32_t)(key[i] >> shift) & 0xFFu;
+                const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (256u + lane));
+                const int leader = __ffs(peers) - 1;
+                uint32_t bb = 0;
+                if (lane == leader && ok) {
+                    bb = myhist[d];
+                    myhist[d] = bb + __popc(peers);
+                }
+                bb = __shfl_sync(0xffffffffu, bb, leader);
+                const uint32_t r = bb + __popc(peers & lt);   // < 32 * IPT
+                rank2[i >> 1] = (i & 1) ? (rank2[i >> 1] | (r << 16)) : r;
+                __syncwarp();
+            }
+            named_sync(1, MAIN);
+            OS_CLK(2);
+            // per digit (one thread each): exclusive scan over warps, publish the tile's count at once
+            uint32_t count = 0;
+            {
+                uint32_t run = 0;
+#pragma unroll
+                for (int w = 0; w < WARPS; ++w) {
+                    const uint32_t c = whist[w * 256 + tid];
+                    whist[w * 256 + tid] = run;
+                    run += c;
+                }
+                count = run;
+                st_relaxed_gpu(status + (uint64_t)tile * 256 + tid, tile == 0 ? (ST_INCLUSIVE | count) : st_partial(count));
+            }
+            uint32_t inc = count;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += y;
+            }
+            if (lane == 31) wsum[warp] = inc;
+            named_sync(1, MAIN);
+            {
+                uint32_t pre = 0;
+                for (int w = 0; w < warp; ++w) pre += wsum[w];
+                tst[b * 256 + tid] = pre + inc - count;
+                cnt[b * 256 + tid] = count;
+                if (tid == 0) s_lbtile[b] = tile;
+            }
+            named_arrive(2 + b, ALL);                         // the look-back warp may start on this tile
+            named_sync(1, MAIN);
+            OS_CLK(3);
+            // re-order the tile in shared memory (stable: digit, then warp, then item order)
+            uint64_t* kb = keys_s + b * TILE;
+            uint32_t* vb = vals_s + b * TILE;
+#pragma unroll
+            for (int i = 0; i < IPT; ++i) {
+                const uint32_t idx = wbase + i * 32;
+                if (full || idx < n) {
+                    const uint32_t d = (uint32_t)(key[i] >> shift) & 0xFFu;
+                    const uint32_t lp = tst[b * 256 + d] + myhist[d] + ((rank2[i >> 1] >> ((i & 1) * 16)) & 0xFFFFu);
+                    kb[lp] = key[i];
+                    vb[lp] = IDENTITY_VALS ? idx : val[i];
+                }
+            }
+            OS_CLK(4);
+            // the registers are free again: start the loads of the next tile
+            const uint32_t nt = s_tile[(it + 1) & 3];
+            if (nt < num_tiles) {
+                const uint32_t wb = nt * (uint32_t)TILE + warp * (32 * IPT) + lane;
+#pragma unroll
+                for (int i = 0; i < IPT; ++i) key[i] = (wb + i * 32 < n) ? ld_stream_u64(keys_in + wb + i * 32) : ~0ull;
+                if (!IDENTITY_VALS) {
+#pragma unroll
+                    for (int i = 0; i < IPT; ++i) val[i] = (wb + i * 32 < n) ? ld_stream_u32(vals_in + wb + i * 32) : 0u;
+                }
+            }
+        } else {
+            if (tid == 0) s_lbtile[b] = NO_TILE;
+            named_arrive(2 + b, ALL);                         // tells the look-back warp to leave
+        }
+        if (it > 0) {
+            // write the previous tile out of the other buffer
+            const int pb = b ^ 1;
+            OS_CLK(5);
+            named_sync(4 + pb, ALL);
+            OS_CLK(6);
+            const uint64_t* kb = keys_s + pb * TILE;
+            const uint32_t* vb = vals_s + pb * TILE;
+            const uint32_t* gofs = cnt + pb * 256;
+            if (prev_n == (uint32_t)TILE) {
+#pragma unroll
+                for (int i = 0; i < IPT; ++i) {
+                    const uint32_t j = tid + i * MAIN;
+                    const uint64_t k = kb[j];
+                    const uint32_t g = gofs[(uint32_t)(k >> shift) & 0xFFu] + j;
+                    keys_out[g] = k;
+                    vals_out[g] = vb[j];
+                }
+            } else {
+                for (uint32_t j = tid; j < prev_n; j += MAIN) {
+                    const uint64_t k = kb[j];
+                    const uint32_t g = gofs[(uint32_t)(k >> shift) & 0xFFu] + j;
+                    keys_out[g] = k;
+                    vals_out[g] = vb[j];
+                }
+            }
+            OS_CLK(7);
+        } else {
+            named_sync(1, MAIN);                              // the per-warp counters are re-zeroed next
+        }
+        if (!valid) return;
+        prev_n = tile_n;
+    }
+}
+
+template <int IPT, int MINB, int LBW, int LB_REGS>
+cudaError_t launch_onesweep4_cfg(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                                 uint32_t* vals_out, uint32_t n, int shift, const uint32_t* digit_base,
+                                 uint32_t* status, uint32_t* tile_counter, uint32_t* err, bool identity_vals,
+                                 cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    constexpr uint32_t TILE = 256 * IPT;
+    constexpr size_t SMEM = onesweep4_smem_bytes<IPT>();
+    const uint32_t tiles = (n + TILE - 1) / TILE;
+    cudaError_t e = cudaMemsetAsync(status, 0, (size_t)tiles * 256 * sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(tile_counter, 0, sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    static int grid = 0;
+    if (!grid) {
+        auto k1 = onesweep4_kernel<IPT, MINB, true, LBW, LB_REGS>;
+        auto k0 = onesweep4_kernel<IPT, MINB, false, LBW, LB_REGS>;
+        cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
+        cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
+        int dev = 0, sms = 148, per_sm = 1;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k0, 512, SMEM);
+        if (per_sm < 1) per_sm = 1;
+        grid = sms * per_sm;
+    }
+    const uint32_t g = tiles < (uint32_t)grid ? tiles : (uint32_t)grid;
+    if (identity_vals)
+        onesweep4_kernel<IPT, MINB, true, LBW, LB_REGS><<<g, 512, SMEM, s>>>(keys_in, vals_in, keys_out, vals_out, n, shift,
+                                                                   digit_base, status, tile_counter, err, tiles);
+    else
+        onesweep4_kernel<IPT, MINB, false, LBW, LB_REGS><<<g, 512, SMEM, s>>>(keys_in, vals_in, keys_out, vals_out, n, shift,
+                                                                    digit_base, status, tile_counter, err, tiles);
     return cudaGetLastError();
 }
 

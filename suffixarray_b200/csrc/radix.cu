@@ -73,12 +73,15 @@ __global__ void __launch_bounds__(256) scan_hist_kernel(const uint32_t* __restri
 // ------------------------------------------------------------------------------ launchers
 namespace {
 // Configuration chosen on B200 with scripts/bench_onesweep.cu (profiles/r01_onesweep_variants.md):
-// 256 threads x 16 records, 2 CTAs/SM persistent, match.any ranking, 8-wide look-back window.
-constexpr int OS_THREADS = 256, OS_IPT = 16, OS_MINB = 2, OS_RANK = 0, OS_LBW = 8;
-constexpr int OS_TILE = OS_THREADS * OS_IPT;
+// 8 ranking warps x 12 records per thread (3072-record tiles) + 8 look-back warps, 2 persistent
+// CTAs per SM, match.any ranking, 4-wide look-back window, 24 / 104 registers per thread.
+constexpr int OS_IPT = 12, OS_LBW = 4, OS_LB_REGS = 24;
+constexpr int OS_TILE = 256 * OS_IPT;
 }  // namespace
 
-uint32_t sa_onesweep_tile_items() { return OS_TILE; }
+int sa_onesweep_variant = 0;     // sa_debug_set("onesweep_variant"): tuning experiments only
+
+uint32_t sa_onesweep_tile_items() { return OS_TILE; }   // smallest tile of any variant: sizes the status words
 
 cudaError_t sa_launch_hist(const uint64_t* keys, uint32_t n, int shift0, int npasses, uint32_t* hist,
                            int num_sms, cudaStream_t s)
@@ -105,6 +108,15 @@ cudaError_t sa_launch_onesweep(const uint64_t* keys_in, const uint32_t* vals_in,
                                uint32_t* status, uint32_t* tile_counter, uint32_t* err, bool identity_vals,
                                cudaStream_t s)
 {
-    return sa::launch_onesweep2_cfg<OS_THREADS, OS_IPT, OS_MINB, OS_RANK, OS_LBW>(
-        keys_in, vals_in, keys_out, vals_out, n, shift, digit_base, status, tile_counter, err, identity_vals, s);
+    switch (sa_onesweep_variant) {
+    case 1:   // persistent CTAs, in-line look-back, bulk-copy prefetch (the previous default)
+        return sa::launch_onesweep2_cfg<256, 16, 2, 0, 8, true>(keys_in, vals_in, keys_out, vals_out, n, shift, digit_base,
+                                                                status, tile_counter, err, identity_vals, s);
+    case 2:   // same without the prefetch
+        return sa::launch_onesweep2_cfg<256, 16, 2, 0, 8, false>(keys_in, vals_in, keys_out, vals_out, n, shift, digit_base,
+                                                                 status, tile_counter, err, identity_vals, s);
+    default:  // warp-specialised look-back
+        return sa::launch_onesweep4_cfg<OS_IPT, 2, OS_LBW, OS_LB_REGS>(keys_in, vals_in, keys_out, vals_out, n, shift,
+                                                                       digit_base, status, tile_counter, err, identity_vals, s);
+    }
 }
