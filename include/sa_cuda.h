@@ -60,7 +60,9 @@ typedef struct sa_stats {
     float ms_query, ms_hits;    /* last query batch (device time) */
     uint64_t onesweep_elems;    /* total elements moved by those launches */
     uint32_t code_bits;         /* bits per suffix byte in the sort keys (8 = raw bytes) */
-    uint32_t reserved0;
+    uint32_t csv_host_scan;     /* sa_build_csv: 1 when the file took the host column scan (irregular quoting / NUL bytes) */
+    float ms_csv_scan;          /* sa_build_csv: device column scan (three tile passes + scans) */
+    uint32_t reserved1;
 } sa_stats;
 
 const char* sa_last_error(void);

@@ -41,7 +41,7 @@ class SaStats(C.Structure):
         ("ms_pack", C.c_float), ("ms_hist", C.c_float), ("ms_sort0", C.c_float), ("ms_refine", C.c_float),
         ("ms_finish", C.c_float), ("ms_docs", C.c_float), ("ms_remap", C.c_float), ("ms_onesweep_sum", C.c_float),
         ("ms_query", C.c_float), ("ms_hits", C.c_float), ("onesweep_elems", C.c_uint64),
-        ("code_bits", C.c_uint32), ("reserved0", C.c_uint32),
+        ("code_bits", C.c_uint32), ("csv_host_scan", C.c_uint32), ("ms_csv_scan", C.c_float), ("reserved1", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -178,3 +178,6 @@ __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p)
 // error flag bits written by device-side guards (sa_index::d_err)
 #define SA_DEVERR_LOOKBACK_TIMEOUT 1u
 #define SA_DEVERR_RUN_TOO_LONG 2u
+// csv_scan.cu: the file is outside the cases where the tile-parallel scan equals the reference's state machine
+#define SA_CSV_IRREGULAR_NUL 1u
+#define SA_CSV_IRREGULAR_QUOTE 2u

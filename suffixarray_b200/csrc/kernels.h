@@ -73,3 +73,12 @@ cudaError_t sa_launch_hits(const uint32_t* sa, const uint32_t* start, const uint
                            cudaStream_t s);
 cudaError_t sa_launch_remap(const uint32_t* sa, uint32_t n, const uint32_t* map, const uint8_t* quoted_by_text,
                             uint32_t* sa_out, uint32_t* quoted_bits_by_rank, cudaStream_t s);
+
+// ---- csv_scan.cu (device copy of the file, zero padded to sa_csv_padded_bytes)
+uint32_t sa_csv_tiles(uint64_t size);
+uint64_t sa_csv_padded_bytes(uint64_t size);
+cudaError_t sa_launch_csv_quotes(const uint8_t* f, uint64_t size, uint32_t* tile_q, uint32_t* flags, cudaStream_t s);
+cudaError_t sa_launch_csv_delims(const uint8_t* f, uint64_t size, const uint32_t* tile_q, uint32_t* tile_d, cudaStream_t s);
+cudaError_t sa_launch_csv_emit(bool write, const uint8_t* f, uint64_t size, const uint32_t* tile_q, const uint32_t* tile_d,
+                               uint32_t* tile_e, uint32_t wanted, uint32_t num_columns, uint8_t* text, uint32_t* map,
+                               uint8_t* quoted, uint32_t* flags, cudaStream_t s);

@@ -1,11 +1,13 @@
 // sa_csv.cu -- CSV column feeder + device remap behind sa_build_csv.
 //
 // Replaces construct_truncated_suffix_array_from_csv_partitioned_mmap[_full]
-// (engine.c:1454-1482 -> :461-654).  The column scan stays on the host (a branchy byte state
-// machine, engine.c:522-605) but writes straight into PINNED buffers that are copied to the
-// device asynchronously; the build runs on the device; the two post-build loops of the
-// reference (quoted-bit permutation, serial, engine.c:632-645; SA[i] = map[SA[i]],
-// engine.c:647-651) are one gather kernel (remap_kernel, query.cu).
+// (engine.c:1454-1482 -> :461-654).  The file is read into a pinned ring and copied to the device
+// asynchronously; the column scan (engine.c:522-605) runs there as three tile-parallel passes
+// (csv_scan.cu).  Files outside RFC-4180 quoting, where that scan and the reference's byte state
+// machine could differ, take the reference-shaped host scan below instead (into pinned buffers,
+// async H2D).  The build runs on the device; the two post-build loops of the reference
+// (quoted-bit permutation, serial, engine.c:632-645; SA[i] = map[SA[i]], engine.c:647-651) are
+// one gather kernel (remap_kernel, query.cu).
 #include <fcntl.h>
 #include <string.h>
 #include <sys/mman.h>
@@ -130,6 +132,119 @@ uint64_t scan_column(FileView v, uint32_t column_idx, uint32_t num_columns, uint
 
 }  // namespace
 
+// File bytes -> device: pread into a two-slot pinned ring, one async H2D copy per slot; the read
+// of slot i+1 overlaps the copy of slot i.
+static int stream_file_to_device(sa_index* idx, int fd, size_t size, uint8_t* d_file)
+{
+    constexpr size_t SLOT = 32u << 20;
+    cudaStream_t s = idx->stream;
+    if (!idx->h_ring[0]) {
+        for (int i = 0; i < 2; ++i) {
+            SA_CU(cudaMallocHost(&idx->h_ring[i], SLOT));
+            SA_CU(cudaEventCreateWithFlags(&idx->ring_ev[i], cudaEventDisableTiming));
+        }
+        idx->ring_bytes = SLOT;
+    }
+    size_t off = 0;
+    for (int slot = 0; off < size; slot ^= 1) {
+        SA_CU(cudaEventSynchronize(idx->ring_ev[slot]));          // the slot's previous copy has drained
+        const size_t len = size - off < SLOT ? size - off : SLOT;
+        size_t got = 0;
+        while (got < len) {
+            const ssize_t r = pread(fd, static_cast<uint8_t*>(idx->h_ring[slot]) + got, len - got, (off_t)(off + got));
+            if (r <= 0) { sa_set_error("read failed at offset %zu", off + got); return SA_ERR_IO; }
+            got += (size_t)r;
+        }
+        SA_CU(cudaMemcpyAsync(d_file + off, idx->h_ring[slot], len, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaEventRecord(idx->ring_ev[slot], s));
+        off += len;
+    }
+    return SA_OK;
+}
+
+// Device column scan (csv_scan.cu).  *regular = false when the file needs the host state machine;
+// otherwise idx->text / map / quoted_text hold the column stream and idx->n its length.
+static int scan_column_device(sa_index* idx, int fd, size_t size, uint32_t col, uint32_t num_columns, bool* regular)
+{
+    cudaStream_t s = idx->stream;
+    uint32_t* sm = idx->small.as<uint32_t>();
+    const uint32_t tiles = sa_csv_tiles(size);
+    const uint64_t padded = sa_csv_padded_bytes(size);
+    SA_CU(idx->csv_file.ensure(padded));
+    SA_CU(idx->csv_tq.ensure((size_t)tiles * 4));
+    SA_CU(idx->csv_td.ensure((size_t)tiles * 4));
+    SA_CU(idx->csv_te.ensure((size_t)tiles * 4));
+    uint8_t* d_file = idx->csv_file.as<uint8_t>();
+    const size_t tail = size & ~(size_t)15;
+    SA_CU(cudaMemsetAsync(d_file + tail, 0, padded - tail, s));
+    SA_CU(cudaMemsetAsync(sm + SM_CSV, 0, 8 * sizeof(uint32_t), s));
+    {
+        ScopedPhase ph(idx, &idx->stats.ms_h2d);
+        int rc = stream_file_to_device(idx, fd, size, d_file);
+        if (rc != SA_OK) return rc;
+    }
+    uint32_t *tq = idx->csv_tq.as<uint32_t>(), *td = idx->csv_td.as<uint32_t>(), *te = idx->csv_te.as<uint32_t>();
+    {
+        ScopedPhase ph(idx, &idx->stats.ms_csv_scan);
+        SA_CU(sa_launch_csv_quotes(d_file, size, tq, sm + SM_CSV, s));
+        SA_CU(sa_launch_scan_u32(tq, tiles, sm + SM_CSV + 1, s));
+        SA_CU(sa_launch_csv_delims(d_file, size, tq, td, s));
+        SA_CU(sa_launch_scan_u32(td, tiles, sm + SM_CSV + 2, s));
+        SA_CU(sa_launch_csv_emit(false, d_file, size, tq, td, te, col, num_columns, nullptr, nullptr, nullptr, sm + SM_CSV, s));
+        SA_CU(sa_launch_scan_u32(te, tiles, sm + SM_CSV + 3, s));
+        idx->stats.kernel_launches += 6;
+    }
+    SA_CU(cudaMemcpyAsync(idx->h_small, sm + SM_CSV, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaStreamSynchronize(s));
+    const uint32_t irregular = idx->h_small[0];
+    const uint64_t n = idx->h_small[3];
+    *regular = irregular == 0;
+    if (irregular) return SA_OK;
+    if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
+    idx->n = n;
+    const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
+    SA_CU(idx->text.ensure(bytes));
+    SA_CU(idx->map.ensure((size_t)n * 4 + 4));
+    SA_CU(idx->quoted_text.ensure((size_t)n + 1));
+    SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + ((size_t)n & ~(size_t)15), 0, bytes - ((size_t)n & ~(size_t)15), s));
+    {
+        ScopedPhase ph(idx, &idx->stats.ms_csv_scan);
+        SA_CU(sa_launch_csv_emit(true, d_file, size, tq, td, te, col, num_columns, idx->text.as<uint8_t>(),
+                                 idx->map.as<uint32_t>(), idx->quoted_text.as<uint8_t>(), sm + SM_CSV, s));
+        idx->stats.kernel_launches += 1;
+    }
+    return SA_OK;
+}
+
+// The reference-shaped host scan into pinned buffers (irregular files, or sa_debug_set csv_scanner = 1)
+static int scan_column_host(sa_index* idx, const Mapped& m, uint32_t col, uint32_t num_columns)
+{
+    const size_t cap = m.size + 2;
+    Pinned h_text, h_map, h_q;
+    cudaError_t e = h_text.alloc(cap);
+    if (e == cudaSuccess) e = h_map.alloc(cap * 4);
+    if (e == cudaSuccess) e = h_q.alloc(cap);
+    if (e != cudaSuccess) return sa_cuda_fail(e, "pinned staging buffers");
+    const uint64_t n = scan_column(FileView{m.p, m.size}, col, num_columns, h_text.as<uint8_t>(), h_map.as<uint32_t>(),
+                                   h_q.as<uint8_t>());
+    if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
+    idx->n = n;
+    cudaStream_t s = idx->stream;
+    const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
+    SA_CU(idx->text.ensure(bytes));
+    SA_CU(idx->map.ensure((size_t)n * 4 + 4));
+    SA_CU(idx->quoted_text.ensure((size_t)n + 1));
+    SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + ((size_t)n & ~(size_t)15), 0, bytes - ((size_t)n & ~(size_t)15), s));
+    if (n) {
+        ScopedPhase ph(idx, &idx->stats.ms_h2d);
+        SA_CU(cudaMemcpyAsync(idx->text.p, h_text.p, n, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaMemcpyAsync(idx->map.p, h_map.p, n * 4, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaMemcpyAsync(idx->quoted_text.p, h_q.p, n, cudaMemcpyHostToDevice, s));
+    }
+    SA_CU(cudaStreamSynchronize(s));     // the pinned staging buffers are released on return
+    return SA_OK;
+}
+
 extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags)
 {
     if (!idx || !csv_path || !column) { sa_set_error("sa_build_csv: NULL argument"); return SA_ERR_INVALID; }
@@ -157,36 +272,31 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
         if (cells[i] == column) { col = (int)i; break; }     // strcmp match, engine.c:1424-1435
     if (col < 0) { sa_set_error("column '%s' not found in %s", column, csv_path); return SA_ERR_IO; }
 
-    const size_t cap = m.size + 2;
-    Pinned h_text, h_map, h_q;
-    cudaError_t e = h_text.alloc(cap);
-    if (e == cudaSuccess) e = h_map.alloc(cap * 4);
-    if (e == cudaSuccess) e = h_q.alloc(cap);
-    if (e != cudaSuccess) return sa_cuda_fail(e, "pinned staging buffers");
-
-    const uint64_t n = scan_column(FileView{m.p, m.size}, (uint32_t)col, (uint32_t)cells.size(), h_text.as<uint8_t>(),
-                                   h_map.as<uint32_t>(), h_q.as<uint8_t>());
-    if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
-
     idx->timing = (flags & SA_FLAG_TIMING) != 0;
-    idx->n = n;
-    cudaStream_t s = idx->stream;
-    const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
-    SA_CU(idx->text.ensure(bytes));
-    SA_CU(idx->map.ensure((size_t)n * 4));
-    SA_CU(idx->quoted_text.ensure((size_t)n));
-    SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + ((size_t)n & ~(size_t)15), 0, bytes - ((size_t)n & ~(size_t)15), s));
+    idx->built = false;
     idx->stats.ms_h2d = 0.f;
-    if (n) {
-        ScopedPhase ph(idx, &idx->stats.ms_h2d);
-        SA_CU(cudaMemcpyAsync(idx->text.p, h_text.p, n, cudaMemcpyHostToDevice, s));
-        SA_CU(cudaMemcpyAsync(idx->map.p, h_map.p, n * 4, cudaMemcpyHostToDevice, s));
-        SA_CU(cudaMemcpyAsync(idx->quoted_text.p, h_q.p, n, cudaMemcpyHostToDevice, s));
+    idx->stats.ms_csv_scan = 0.f;
+    idx->stats.csv_host_scan = 0;
+    bool regular = false;
+    if (idx->dbg_csv_scanner != 1) {
+        int rc = scan_column_device(idx, m.fd, m.size, (uint32_t)col, (uint32_t)cells.size(), &regular);
+        if (rc != SA_OK) return rc;
+        if (!regular && idx->dbg_csv_scanner == 2) {
+            sa_set_error("%s is not a regular CSV file for the device scanner (flags 0x%x)", csv_path, idx->h_small[0]);
+            return SA_ERR_IO;
+        }
     }
+    if (!regular) {
+        int rc = scan_column_host(idx, m, (uint32_t)col, (uint32_t)cells.size());
+        if (rc != SA_OK) return rc;
+    }
+    const uint64_t n = idx->n;
+    cudaStream_t s = idx->stream;
     // the scan already lower-cased the column (tolower, engine.c:559,581,593)
     int rc = sa_build_resident(idx, flags & ~SA_FLAG_LOWERCASE);
     if (rc != SA_OK) return rc;
     idx->built = false;
+    idx->stats.csv_host_scan = regular ? 0u : 1u;
     SA_CU(idx->sa_file.ensure((size_t)n * 4));
     SA_CU(idx->qbits.ensure((((size_t)n + 31) / 32) * 4 + 4));
     {
@@ -195,7 +305,7 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
                               idx->quoted_text.as<uint8_t>(), idx->sa_file.as<uint32_t>(), idx->qbits.as<uint32_t>(), s));
         idx->stats.kernel_launches += 1;
     }
-    SA_CU(cudaStreamSynchronize(s));     // pinned staging buffers are released on return
+    SA_CU(cudaStreamSynchronize(s));
     sa_time_collect(idx);
     idx->csv = true;
     idx->built = true;

@@ -43,7 +43,8 @@ enum SmallSlot : uint32_t {
     SM_NLTOTAL = 4110,      // 1
     SM_BYTEHIST = 4112,     // 256 presence flags
     SM_TABLE = 4368,        // 256 bytes = 64 words: byte -> code
-    SM_WORDS = 4432
+    SM_CSV = 4432,          // 8: irregularity flags, total quotes, total delimiters, total emitted bytes
+    SM_WORDS = 4440
 };
 
 constexpr uint64_t SA_MAX_INDEX_BYTES = 1ull << 31;   // records per index: look-back prefixes are 31-bit
@@ -73,6 +74,10 @@ struct sa_index {
     DevBuf sa_file;     // CSV: u32[n] file offsets (engine.c:647-651)
     DevBuf qbits;       // CSV: quoted bit per rank
     DevBuf map, quoted_text;   // CSV feeder outputs on the device
+    DevBuf csv_file, csv_tq, csv_td, csv_te;   // device copy of the file + per-tile counts (csv_scan.cu)
+    void* h_ring[2] = {nullptr, nullptr};      // pinned staging ring of the file reader
+    cudaEvent_t ring_ev[2] = {nullptr, nullptr};
+    size_t ring_bytes = 0;
 
     // build scratch (kept between builds so repeated builds do not re-allocate)
     DevBuf keys[2], vals[2], aux[2], lcp, tie, amask, hmask, counts, status, small, nl_counts;
@@ -110,6 +115,7 @@ struct sa_index {
     int64_t dbg_force_gbits = 0;    // use at least this many group-id bits (exercises small cb)
     int64_t dbg_query_kernel = 0;   // 0: by batch size; 1: one thread per query; 2: eight lanes per query
     int64_t dbg_same_process = 0;   // sharded build: peers live in this process (raw pointers instead of IPC)
+    int64_t dbg_csv_scanner = 0;    // 0: device scan, host scan for irregular files; 1: host scan; 2: device scan or fail
     int64_t dbg_sort0_chars = -1;   // -1: automatic; else at most this many characters in the first sort's keys
     int64_t dbg_code_bits = -1;     // -1: choose from the alphabet; 8: never compress; 1..7: at least this width
 };
