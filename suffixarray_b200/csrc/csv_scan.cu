@@ -9,7 +9,7 @@
 // (quote counts -> delimiter counts -> emitted bytes), each followed by a small prefix scan.
 // Emitted for the wanted column, in file order (= the reference's three append_* streams):
 //   lower-cased cell bytes, a '\n' per cell at the delimiter's offset, the file offset of every
-//   emitted byte, and the "cell was quoted" flag; `""` inside a quoted cell emits one '"'.
+//   emitted byte with the "cell was quoted" flag in bit 31; `""` inside a quoted cell emits one '"'.
 // Anything the equivalence does not cover sets an irregularity flag and sa_build_csv falls back to
 // the reference-shaped host scan (sa_csv.cu): a NUL byte, a quote opening in the middle of a cell,
 // a closing quote not followed by , \n " or the end of the file, an unterminated quote.
@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(CSV_THREADS)
 csv_emit_kernel(const uint8_t* __restrict__ f, uint64_t size, const uint32_t* __restrict__ tile_q,
                 const uint32_t* __restrict__ tile_d, uint32_t* __restrict__ tile_e, uint32_t wanted,
                 uint32_t num_columns, uint8_t* __restrict__ text, uint32_t* __restrict__ map,
-                uint8_t* __restrict__ quoted, uint32_t* __restrict__ flags)
+                uint32_t* __restrict__ flags)
 {
     __shared__ uint32_t ws[CSV_THREADS / 32];
     const uint64_t p = (uint64_t)blockIdx.x * CSV_TILE + threadIdx.x * 16;
@@ -205,16 +205,14 @@ csv_emit_kernel(const uint8_t* __restrict__ f, uint64_t size, const uint32_t* __
             if (c >= 'A' && c <= 'Z') c += 32;
         }
         text[o] = (uint8_t)c;
-        map[o] = (uint32_t)(p + j);
-        quoted[o] = (uint8_t)qf;
+        map[o] = (uint32_t)(p + j) | (qf << 31);     // offsets are < 2^31: the quoted flag rides in bit 31
         ++o;
     }
     if (eof_sentinel) {
         const uint32_t j = (uint32_t)(size - p);
         const uint32_t last = j ? b.at(j - 1) : prev;
         text[o] = '\n';
-        map[o] = (uint32_t)size;
-        quoted[o] = (uint8_t)(last == '"');
+        map[o] = (uint32_t)size | ((last == '"') ? 0x80000000u : 0u);
     }
 }
 
@@ -237,13 +235,13 @@ cudaError_t sa_launch_csv_delims(const uint8_t* f, uint64_t size, const uint32_t
 
 cudaError_t sa_launch_csv_emit(bool write, const uint8_t* f, uint64_t size, const uint32_t* tile_q, const uint32_t* tile_d,
                                uint32_t* tile_e, uint32_t wanted, uint32_t num_columns, uint8_t* text, uint32_t* map,
-                               uint8_t* quoted, uint32_t* flags, cudaStream_t s)
+                               uint32_t* flags, cudaStream_t s)
 {
     if (write)
         sa::csv_emit_kernel<true><<<sa_csv_tiles(size), sa::CSV_THREADS, 0, s>>>(f, size, tile_q, tile_d, tile_e, wanted,
-                                                                                num_columns, text, map, quoted, flags);
+                                                                                num_columns, text, map, flags);
     else
         sa::csv_emit_kernel<false><<<sa_csv_tiles(size), sa::CSV_THREADS, 0, s>>>(f, size, tile_q, tile_d, tile_e, wanted,
-                                                                                 num_columns, text, map, quoted, flags);
+                                                                                 num_columns, text, map, flags);
     return cudaGetLastError();
 }

@@ -81,4 +81,4 @@ cudaError_t sa_launch_csv_quotes(const uint8_t* f, uint64_t size, uint32_t* tile
 cudaError_t sa_launch_csv_delims(const uint8_t* f, uint64_t size, const uint32_t* tile_q, uint32_t* tile_d, cudaStream_t s);
 cudaError_t sa_launch_csv_emit(bool write, const uint8_t* f, uint64_t size, const uint32_t* tile_q, const uint32_t* tile_d,
                                uint32_t* tile_e, uint32_t wanted, uint32_t num_columns, uint8_t* text, uint32_t* map,
-                               uint8_t* quoted, uint32_t* flags, cudaStream_t s);
+                               uint32_t* flags, cudaStream_t s);

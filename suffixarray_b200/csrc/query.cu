@@ -368,8 +368,10 @@ __global__ void remap_kernel(const uint32_t* __restrict__ sa, uint32_t n, const 
         const uint32_t p = sa[i];
         // copy_buffer_bit (engine.c:256-261) copies only n / 8 whole bytes of the flags, so the
         // last n % 8 text bytes read as "not quoted" in the reference's permutation loop
-        qd = (p < (n & ~7u)) && quoted_by_text[p] != 0;
-        sa_out[i] = map[p];
+        // the device column scanner packs the flag into bit 31 of the offset (files are < 2 GiB)
+        const uint32_t m = map[p];
+        qd = (p < (n & ~7u)) && (quoted_by_text ? quoted_by_text[p] != 0 : (m >> 31) != 0);
+        sa_out[i] = quoted_by_text ? m : (m & 0x7FFFFFFFu);
     }
     const uint32_t b = __ballot_sync(0xffffffffu, qd);
     if ((threadIdx.x & 31) == 0 && (i >> 5) < ((n + 31) >> 5)) qbits[i >> 5] = b;

@@ -14,7 +14,10 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <algorithm>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "sa_index.h"
@@ -149,12 +152,25 @@ static int stream_file_to_device(sa_index* idx, int fd, size_t size, uint8_t* d_
     for (int slot = 0; off < size; slot ^= 1) {
         SA_CU(cudaEventSynchronize(idx->ring_ev[slot]));          // the slot's previous copy has drained
         const size_t len = size - off < SLOT ? size - off : SLOT;
-        size_t got = 0;
-        while (got < len) {
-            const ssize_t r = pread(fd, static_cast<uint8_t*>(idx->h_ring[slot]) + got, len - got, (off_t)(off + got));
-            if (r <= 0) { sa_set_error("read failed at offset %zu", off + got); return SA_ERR_IO; }
-            got += (size_t)r;
-        }
+        // the page-cache copy is the slow part of this loop: split the slot over a few reader threads
+        constexpr int READERS = 4;
+        uint8_t* dst = static_cast<uint8_t*>(idx->h_ring[slot]);
+        std::atomic<int> failed{0};
+        auto read_part = [&](size_t b, size_t e) {
+            while (b < e) {
+                const ssize_t r = pread(fd, dst + b, e - b, (off_t)(off + b));
+                if (r <= 0) { failed = 1; return; }
+                b += (size_t)r;
+            }
+        };
+        const size_t part = ((len + READERS - 1) / READERS + 4095) & ~(size_t)4095;
+        std::thread th[READERS - 1];
+        int started = 0;
+        for (int t = 1; t < READERS && (size_t)t * part < len; ++t, ++started)
+            th[t - 1] = std::thread(read_part, (size_t)t * part, std::min(len, (size_t)(t + 1) * part));
+        read_part(0, std::min(len, part));
+        for (int t = 0; t < started; ++t) th[t].join();
+        if (failed) { sa_set_error("read failed near offset %zu", off); return SA_ERR_IO; }
         SA_CU(cudaMemcpyAsync(d_file + off, idx->h_ring[slot], len, cudaMemcpyHostToDevice, s));
         SA_CU(cudaEventRecord(idx->ring_ev[slot], s));
         off += len;
@@ -190,7 +206,7 @@ static int scan_column_device(sa_index* idx, int fd, size_t size, uint32_t col, 
         SA_CU(sa_launch_scan_u32(tq, tiles, sm + SM_CSV + 1, s));
         SA_CU(sa_launch_csv_delims(d_file, size, tq, td, s));
         SA_CU(sa_launch_scan_u32(td, tiles, sm + SM_CSV + 2, s));
-        SA_CU(sa_launch_csv_emit(false, d_file, size, tq, td, te, col, num_columns, nullptr, nullptr, nullptr, sm + SM_CSV, s));
+        SA_CU(sa_launch_csv_emit(false, d_file, size, tq, td, te, col, num_columns, nullptr, nullptr, sm + SM_CSV, s));
         SA_CU(sa_launch_scan_u32(te, tiles, sm + SM_CSV + 3, s));
         idx->stats.kernel_launches += 6;
     }
@@ -205,12 +221,11 @@ static int scan_column_device(sa_index* idx, int fd, size_t size, uint32_t col, 
     const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
     SA_CU(idx->text.ensure(bytes));
     SA_CU(idx->map.ensure((size_t)n * 4 + 4));
-    SA_CU(idx->quoted_text.ensure((size_t)n + 1));
     SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + ((size_t)n & ~(size_t)15), 0, bytes - ((size_t)n & ~(size_t)15), s));
     {
         ScopedPhase ph(idx, &idx->stats.ms_csv_scan);
         SA_CU(sa_launch_csv_emit(true, d_file, size, tq, td, te, col, num_columns, idx->text.as<uint8_t>(),
-                                 idx->map.as<uint32_t>(), idx->quoted_text.as<uint8_t>(), sm + SM_CSV, s));
+                                 idx->map.as<uint32_t>(), sm + SM_CSV, s));
         idx->stats.kernel_launches += 1;
     }
     return SA_OK;
@@ -302,7 +317,8 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
     {
         ScopedPhase ph(idx, &idx->stats.ms_remap);
         SA_CU(sa_launch_remap(idx->sa_final.as<uint32_t>(), (uint32_t)n, idx->map.as<uint32_t>(),
-                              idx->quoted_text.as<uint8_t>(), idx->sa_file.as<uint32_t>(), idx->qbits.as<uint32_t>(), s));
+                              regular ? nullptr : idx->quoted_text.as<uint8_t>(), idx->sa_file.as<uint32_t>(),
+                              idx->qbits.as<uint32_t>(), s));
         idx->stats.kernel_launches += 1;
     }
     SA_CU(cudaStreamSynchronize(s));
