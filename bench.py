@@ -67,6 +67,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="global mode: fused split + peer stores through CUDA IPC (default) or split + NCCL all-to-all")
+    ap.add_argument("--replicate", default="fused", choices=["fused", "allgather"],
+                    help="N > 1: how every rank gets the complete array: the finish kernel stores into all ranks' arrays "
+                         "(peer stores over NVLink), or NCCL all-gather of the slices + copy")
     ap.add_argument("--mode", default="global", choices=["global", "partition"],
                     help="N > 1: one global index built as a sample sort (default) or one independent "
                          "partition per GPU (the reference's own partitioning, suffix_array.pyx:148-180)")
@@ -347,7 +350,7 @@ def run_ours_global(args, world, rank, local):
         t0 = time.perf_counter()
         b, phases = SH.build_distributed(h_text, L, local, lowercase=lower, timing=True,
                                          device_text=d_text if kind == "dev" else None, builder=builders[kind],
-                                         exchange=args.exchange)
+                                         exchange=args.exchange, replicate=args.replicate)
         builders[kind] = b
         torch.cuda.synchronize()
         return b, (time.perf_counter() - t0) * 1e3, phases
@@ -419,7 +422,9 @@ def run_ours_global(args, world, rank, local):
         xms = phases.get("exchange", 0.0)
         result["config"]["sharding"] = ("one global index over the N concatenated partitions: sample sort, splitters from "
                                         "the all-reduced 65536-bin key histogram, NCCL all-to-all of (key, pos) records, "
-                                        "128-record halos for the bucket finish, all-gather of the slices")
+                                        "128-record halos for the bucket finish, " +
+                                        ("finish kernel stores every placed position into all ranks' arrays (peer stores over NVLink)"
+                                         if args.replicate == "fused" else "NCCL all-gather of the slices"))
         result["config"]["exchange"] = ("split kernel stores records straight into the destination GPU's sort buffers "
                                         "(CUDA IPC peer stores over NVLink)" if args.exchange == "p2p"
                                         else "split into send buffers + NCCL all_to_all_single")

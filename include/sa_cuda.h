@@ -155,6 +155,18 @@ int sa_shard_scatter_p2p(sa_index* idx, const uint64_t* d_keys, const uint32_t* 
                          int my_rank, const uint8_t* handles, const uint64_t* dst_offset);
 int sa_shard_sort_recv(sa_index* idx, uint64_t m);
 
+/* Fused finish + replicate (no all-gather, no adopt copy): finish_kernel stores every placed
+ * position into all ranks' final arrays, the local one directly and the peers' through CUDA IPC
+ * mappings over NVLink.  sa_shard_final_prepare exports this rank's array (handle_final: 64 bytes);
+ * sa_shard_finish_bcast takes all ranks' handles (64 bytes each) and the global rank of this
+ * shard's first record; after a barrier over the ranks sa_shard_mark_built makes the index
+ * queryable.  Same halo arguments as sa_shard_finish. */
+int sa_shard_final_prepare(sa_index* idx, uint8_t* handle_final);
+int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
+                          uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp, uint32_t nright,
+                          int nranks, int my_rank, const uint8_t* handles, uint64_t global_offset);
+int sa_shard_mark_built(sa_index* idx);
+
 /* Debug / parity hooks (used by tests to localise a mismatch; not part of the drop-in). */
 int sa_debug_copy_lcp(sa_index* idx, uint16_t* out, uint64_t cap);
 int sa_debug_set(sa_index* idx, const char* key, int64_t value);

@@ -35,7 +35,9 @@ for name, text, L, lower in [c for c in cases for _ in (0, 1)]:
     if builder is not None and builder.L != L:
         builder.close()
         builder = None
-    builder, phases = SH.build_distributed(text, L, local, lowercase=lower, builder=builder, exchange=exchange)
+    replicate = "fused" if exchange == "p2p" else "allgather"
+    builder, phases = SH.build_distributed(text, L, local, lowercase=lower, builder=builder, exchange=exchange,
+                                           replicate=replicate)
     builder._last = (name, exchange)
     got = builder.idx.sa()
     want_text = O.oracle_lowercase(text) if lower else text
@@ -44,7 +46,7 @@ for name, text, L, lower in [c for c in cases for _ in (0, 1)]:
     flags = torch.tensor([int(same)], device="cuda")
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print(f"{name} [{exchange}]: n={text.size} world={world} shard m={builder.m} -> {'OK' if flags.item() else 'MISMATCH'}  "
+        print(f"{name} [{exchange}/{replicate}]: n={text.size} world={world} shard m={builder.m} -> {'OK' if flags.item() else 'MISMATCH'}  "
               + " ".join(f"{k}={v:.1f}ms" for k, v in phases.items()), flush=True)
     ok = ok and bool(flags.item())
 builder.close()

@@ -30,6 +30,7 @@ EXPORTS = [
     "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
     "sa_shard_begin", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
     "sa_adopt_sa", "sa_adopt_sa_parts", "sa_shard_count", "sa_shard_recv_prepare", "sa_shard_scatter_p2p", "sa_shard_sort_recv",
+    "sa_shard_final_prepare", "sa_shard_finish_bcast", "sa_shard_mark_built",
 ]
 
 
@@ -110,6 +111,10 @@ def lib():
     L.sa_shard_recv_prepare.argtypes = [_vp, C.c_uint64, _vp, _vp]
     L.sa_shard_scatter_p2p.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_int, C.c_int, _vp, _vp]
     L.sa_shard_sort_recv.argtypes = [_vp, C.c_uint64]
+    L.sa_shard_final_prepare.argtypes = [_vp, _vp]
+    L.sa_shard_finish_bcast.argtypes = [_vp, _vp, _vp, C.c_uint32, C.c_uint32, _vp, _vp, C.c_uint32, C.c_int, C.c_int,
+                                        _vp, C.c_uint64]
+    L.sa_shard_mark_built.argtypes = [_vp]
     _lib = L
     return L
 

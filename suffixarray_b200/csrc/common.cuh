@@ -176,6 +176,15 @@ __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p)
 }  // namespace sa
 
 // error flag bits written by device-side guards (sa_index::d_err)
+namespace sa {
+// where finish_kernel puts a placed position: out[g] + rank for every replica g, ranks [lo, hi) only
+struct FinishOut {
+    uint32_t* out[16];
+    int n;
+    uint32_t lo, hi;
+};
+}  // namespace sa
+
 #define SA_DEVERR_LOOKBACK_TIMEOUT 1u
 #define SA_DEVERR_RUN_TOO_LONG 2u
 // csv_scan.cu: the file is outside the cases where the tile-parallel scan equals the reference's state machine

@@ -83,10 +83,19 @@ __device__ __forceinline__ uint64_t ld_keep_u64(const uint64_t* p, uint64_t poli
     return v;
 }
 
+// One placed position goes to every replica of the output (1 locally; all ranks' arrays through
+// peer stores over NVLink in a sharded build, where only ranks [lo, hi) belong to this shard).
+__device__ __forceinline__ void put(const FinishOut& o, int64_t x, uint32_t pos)
+{
+    if (x < (int64_t)o.lo || x >= (int64_t)o.hi) return;
+#pragma unroll 1
+    for (int g = 0; g < o.n; ++g) __stcs(o.out[g] + x, pos);
+}
+
 __global__ void __launch_bounds__(FTHREADS)
 finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ lcp,
               const uint8_t* __restrict__ text, uint32_t n, uint32_t lprime, uint32_t r_begin, uint32_t r_end,
-              uint32_t* __restrict__ sa_out, unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err)
+              const FinishOut outs, unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err)
 {
     __shared__ int16_t s_l[FLCP];        // adjacent LCPs, -1 outside [1, n)
     __shared__ int16_t s_p[FLCP];        // block prefix min of l, later block prefix max of m
@@ -207,18 +216,18 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
         const int e = t + 32, q = e >> 5, i = e & 31;
         const uint64_t tp = s_tp[e];
         const uint32_t pos = (uint32_t)tp;
-        if (!((s_sort[q] >> i) & 1u)) { __stcs(sa_out + r, pos); continue; }
+        if (!((s_sort[q] >> i) & 1u)) { put(outs, r, pos); continue; }
         // bucket = [first, last]: last head at or before e, next head after e
         const uint64_t X = (((uint64_t)s_head[q] << 32) | s_head[q - 1]) & (~0ull >> (31 - i));
         const int first = (q - 1) * 32 + (63 - __clzll((long long)X));
         const uint64_t Y = ((((uint64_t)s_head[q + 1] << 32) | s_head[q]) >> i) >> 1;
         const int last = Y ? e + __ffsll((long long)Y) - 1 : e + 32;
-        if (X == 0 || last - first + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); __stcs(sa_out + r, pos); continue; }
+        if (X == 0 || last - first + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); put(outs, r, pos); continue; }
         const uint64_t hi = s_hi[e], lo = s_lo[e];
         uint32_t rank = 0;
         for (int x = first; x <= last; ++x)                 // branch-free (key, byte 16, position) compare
             rank -= less192(s_hi[x], s_lo[x], s_tp[x], hi, lo, tp);
-        __stcs(sa_out + (r - (e - first) + rank), pos);
+        put(outs, r - (e - first) + rank, pos);
         if (e == first) ++my_runs;
     }
     if (my_runs) atomicAdd(&s_runs, my_runs);
@@ -229,12 +238,11 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
 }  // namespace sa
 
 cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,
-                             uint32_t lprime, uint32_t r_begin, uint32_t r_end, uint32_t* sa_out,
+                             uint32_t lprime, uint32_t r_begin, uint32_t r_end, const sa::FinishOut& outs,
                              unsigned long long* run_counter, uint32_t* err, cudaStream_t s)
 {
     if (!n) return cudaSuccess;
     const uint32_t blocks = (n + sa::FT - 1) / sa::FT;
-    sa::finish_kernel<<<blocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, sa_out, run_counter,
-                                                      err);
+    sa::finish_kernel<<<blocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, outs, run_counter, err);
     return cudaGetLastError();
 }

@@ -50,7 +50,7 @@ cudaError_t sa_launch_writeback(const uint32_t* slots, const uint64_t* ckeys, co
 
 // ---- finish.cu
 cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,
-                             uint32_t lprime, uint32_t r_begin, uint32_t r_end, uint32_t* sa_out,
+                             uint32_t lprime, uint32_t r_begin, uint32_t r_end, const sa::FinishOut& outs,
                              unsigned long long* run_counter, uint32_t* err, cudaStream_t s);
 
 // ---- query.cu

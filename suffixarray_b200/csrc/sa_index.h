@@ -95,6 +95,9 @@ struct sa_index {
     void* peer_pos[16] = {};
     cudaIpcMemHandle_t peer_hk[16] = {}, peer_hp[16] = {};
     bool peer_mapped[16] = {};
+    void* peer_final[16] = {};                 // peers' sa_final arrays (fused finish + replicate)
+    cudaIpcMemHandle_t peer_hf[16] = {};
+    bool peer_final_mapped[16] = {};
 
     // query scratch / results of the last batch
     DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
@@ -160,4 +163,6 @@ int sa_ensure_scratch(sa_index* idx, uint32_t m);
 int sa_stage_sort_refine(sa_index* idx, uint32_t m, bool identity, uint32_t** sa_sorted);
 int sa_stage_finish(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
                     uint32_t r_end, uint32_t* out);
+int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
+                       uint32_t r_end, const sa::FinishOut& outs);
 int sa_check_device_error(sa_index* idx);

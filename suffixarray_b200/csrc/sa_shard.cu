@@ -393,22 +393,18 @@ extern "C" int sa_shard_edges(sa_index* idx, uint32_t edge, uint32_t* head_pos, 
 // global order (left_lcp[0] is ignored), lcp_first = LCP(last left record, first own record);
 // right_*: the nright records that follow (right_lcp[0] = LCP(last own record, first right record)).
 // The m placed positions go to d_sa_out (device).
-extern "C" int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
+// Shared body of the two finish entry points: halo records -> extended arrays -> finish_kernel.
+// outs == nullptr: results go to idx->ext_out (extended rank space).
+static int shard_finish_common(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
                                uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp,
-                               uint32_t nright, uint32_t* d_sa_out)
+                               uint32_t nright, const sa::FinishOut* outs)
 {
-    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_finish: no sorted shard");
-    SH_REQUIRE(nleft <= 4096 && nright <= 4096, SA_ERR_LIMIT, "sa_shard_finish: halo too large");
-    std::lock_guard<std::mutex> lock(idx->mu);
-    SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = idx->shard_m;
-    if (m == 0) return SA_OK;
-    SH_REQUIRE(d_sa_out, SA_ERR_INVALID, "sa_shard_finish: d_sa_out is NULL");
     const uint32_t total = nleft + m + nright;
     SA_CU(idx->ext_sa.ensure((size_t)total * 4));
     SA_CU(idx->ext_lcp.ensure((size_t)total * 2 + 64));
-    SA_CU(idx->ext_out.ensure((size_t)total * 4));
+    if (!outs) SA_CU(idx->ext_out.ensure((size_t)total * 4));
     // halo records: pinned staging is overkill for <= 8192 records; a pageable copy is synchronous
     const uint32_t nh = nleft + nright;
     SA_CU(idx->aux[0].ensure((size_t)(nh + 1) * 4));
@@ -429,13 +425,110 @@ extern "C" int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const ui
     idx->stats.kernel_launches += 1;
     const uint32_t r_begin = nleft - (nleft < 32 ? nleft : 32);
     const uint32_t r_end = nleft + m + (nright < 32 ? nright : 32);
-    int rc = sa_stage_finish(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end,
-                             idx->ext_out.as<uint32_t>());
+    if (outs)
+        return sa_stage_finish_to(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end, *outs);
+    return sa_stage_finish(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end,
+                           idx->ext_out.as<uint32_t>());
+}
+
+extern "C" int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
+                               uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp,
+                               uint32_t nright, uint32_t* d_sa_out)
+{
+    SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_finish: no sorted shard");
+    SH_REQUIRE(nleft <= 4096 && nright <= 4096, SA_ERR_LIMIT, "sa_shard_finish: halo too large");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    cudaStream_t s = idx->stream;
+    const uint32_t m = idx->shard_m;
+    if (m == 0) return SA_OK;
+    SH_REQUIRE(d_sa_out, SA_ERR_INVALID, "sa_shard_finish: d_sa_out is NULL");
+    int rc = shard_finish_common(idx, left_pos, left_lcp, nleft, lcp_first, right_pos, right_lcp, nright, nullptr);
     if (rc != SA_OK) return rc;
     SA_CU(cudaMemcpyAsync(d_sa_out, idx->ext_out.as<uint32_t>() + nleft, (size_t)m * 4, cudaMemcpyDeviceToDevice, s));
     rc = sa_check_device_error(idx);
     sa_time_collect(idx);
     return rc;
+}
+
+// ------------------------------------------------------------------------------ fused finish + replicate
+// Instead of "finish into a local slice, all-gather the slices, copy into place", finish_kernel can
+// store every placed position straight into ALL ranks' final arrays (local HBM + peer stores over
+// NVLink): the replication overlaps the finishing compute and the gather / adopt passes disappear.
+// 1. sa_shard_final_prepare: allocate this rank's final array (n entries) and export its IPC handle.
+extern "C" int sa_shard_final_prepare(sa_index* idx, uint8_t* handle_final)
+{
+    SH_REQUIRE(idx && idx->shard_prepared && handle_final, SA_ERR_INVALID, "sa_shard_final_prepare: bad argument");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    idx->built = false;
+    SA_CU(idx->sa_final.ensure((size_t)(idx->n ? idx->n : 1) * 4));
+    memset(handle_final, 0, 64);
+    if (idx->dbg_same_process) {
+        memcpy(handle_final, "SAMEPROC", 8);
+        memcpy(handle_final + 8, &idx->sa_final.p, sizeof(void*));
+        return SA_OK;
+    }
+    cudaIpcMemHandle_t h;
+    SA_CU(cudaIpcGetMemHandle(&h, idx->sa_final.p));
+    memcpy(handle_final, &h, 64);
+    return SA_OK;
+}
+
+// 2. sa_shard_finish_bcast: like sa_shard_finish, but the m placed positions of this shard are
+//    written to final[global_offset .. global_offset + m) of every rank (handles: 64 bytes per rank,
+//    from sa_shard_final_prepare).  After a barrier over all ranks call sa_shard_mark_built.
+extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
+                                     uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp,
+                                     uint32_t nright, int nranks, int my_rank, const uint8_t* handles,
+                                     uint64_t global_offset)
+{
+    SH_REQUIRE(idx && idx->shard_prepared && handles, SA_ERR_INVALID, "sa_shard_finish_bcast: bad argument");
+    SH_REQUIRE(nleft <= 4096 && nright <= 4096, SA_ERR_LIMIT, "sa_shard_finish_bcast: halo too large");
+    SH_REQUIRE(nranks >= 1 && nranks <= 16 && my_rank >= 0 && my_rank < nranks, SA_ERR_INVALID, "sa_shard_finish_bcast: bad rank");
+    SH_REQUIRE(global_offset + idx->shard_m <= idx->n, SA_ERR_INVALID, "sa_shard_finish_bcast: slice outside the array");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    const uint32_t m = idx->shard_m;
+    sa::FinishOut fo{};
+    fo.n = nranks;
+    fo.lo = nleft;
+    fo.hi = nleft + m;
+    for (int g = 0; g < nranks; ++g) {
+        void* base = nullptr;
+        const uint8_t* h = handles + (size_t)g * 64;
+        if (g == my_rank) {
+            base = idx->sa_final.p;
+        } else if (memcmp(h, "SAMEPROC", 8) == 0) {
+            memcpy(&base, h + 8, sizeof base);
+        } else {
+            if (!idx->peer_final_mapped[g] || memcmp(&idx->peer_hf[g], h, 64) != 0) {
+                if (idx->peer_final_mapped[g]) { cudaIpcCloseMemHandle(idx->peer_final[g]); idx->peer_final_mapped[g] = false; }
+                memcpy(&idx->peer_hf[g], h, 64);
+                SA_CU(cudaIpcOpenMemHandle(&idx->peer_final[g], idx->peer_hf[g], cudaIpcMemLazyEnablePeerAccess));
+                idx->peer_final_mapped[g] = true;
+            }
+            base = idx->peer_final[g];
+        }
+        SH_REQUIRE(base, SA_ERR_INVALID, "sa_shard_finish_bcast: rank %d has no final array", g);
+        // extended rank x (>= nleft) -> global rank global_offset + x - nleft
+        fo.out[g] = static_cast<uint32_t*>(base) + global_offset - nleft;
+    }
+    if (m == 0) return SA_OK;
+    int rc = shard_finish_common(idx, left_pos, left_lcp, nleft, lcp_first, right_pos, right_lcp, nright, &fo);
+    if (rc != SA_OK) return rc;
+    rc = sa_check_device_error(idx);          // synchronises the stream: all peer stores of this rank are issued and done
+    sa_time_collect(idx);
+    return rc;
+}
+
+// 3. every rank's finish has completed (barrier): the local final array is complete.
+extern "C" int sa_shard_mark_built(sa_index* idx)
+{
+    SH_REQUIRE(idx && idx->shard_prepared && idx->sa_final.p, SA_ERR_INVALID, "sa_shard_mark_built: nothing to adopt");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    idx->built = true;
+    return SA_OK;
 }
 
 // Install a complete suffix array (n entries, e.g. the all-gathered shard outputs) so that the

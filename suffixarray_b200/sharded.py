@@ -251,6 +251,29 @@ class ShardBuilder:
         self.slice = out[: self.m]
         return self.slice
 
+    # ---- fused finish + replicate (peer stores through CUDA IPC)
+    def final_prepare(self) -> np.ndarray:
+        """-> 64 bytes: the IPC handle of this rank's final array."""
+        h = np.zeros(64, dtype=np.uint8)
+        S.check(S.lib().sa_shard_final_prepare(self.idx._h, h.ctypes.data_as(S._vp)))
+        return h
+
+    def finish_bcast(self, all_edges: list[dict], all_handles: np.ndarray):
+        """finish this shard and store its slice into every rank's final array."""
+        goff = int(sum(int(e["m"]) for e in all_edges[: self.rank]))
+        handles = np.ascontiguousarray(all_handles, dtype=np.uint8).reshape(-1)
+        z32, z16 = np.zeros(0, np.uint32), np.zeros(0, np.uint16)
+        lp, ll, lf, rp, rl = (z32, z16, 0, z32, z16)
+        if self.m:
+            lp, ll, lf, rp, rl = assemble_halos(all_edges, self.rank, self.text, self.lprime, self.lowercase)
+        vp = lambda a: a.ctypes.data_as(S._vp) if a.size else None   # noqa: E731
+        self.torch.cuda.synchronize(self.dev)
+        S.check(S.lib().sa_shard_finish_bcast(self.idx._h, vp(lp), vp(ll), lp.size, lf, vp(rp), vp(rl), rp.size,
+                                              self.world, self.rank, handles.ctypes.data_as(S._vp), goff))
+
+    def mark_built(self):
+        S.check(S.lib().sa_shard_mark_built(self.idx._h))
+
     def adopt(self, full_sa):
         self.torch.cuda.synchronize(self.dev)
         S.check(S.lib().sa_adopt_sa(self.idx._h, self._p(full_sa), self.n))
@@ -285,7 +308,7 @@ def _array_to_edges(row: np.ndarray) -> dict:
 
 # ----------------------------------------------------------------------------- drivers
 def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lowercase: bool = False,
-                   adopt: bool = True, exchange: str = "p2p"):
+                   adopt: bool = True, exchange: str = "p2p", replicate: str = "allgather"):
     """G ranks in lock step inside one process on ONE GPU (collectives = tensor copies).
     -> (full SA as a torch int32 CUDA tensor, list of ShardBuilder).  Test tier only."""
     import torch
@@ -304,6 +327,14 @@ def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lo
         for r in ranks:                                                        # barrier
             r.sort_recv()
         edges = [_array_to_edges(_edges_to_array(r.edges())) for r in ranks]
+        if replicate == "fused":
+            fh = np.stack([r.final_prepare() for r in ranks])                   # all-gather of the handles
+            for r in ranks:
+                r.finish_bcast(edges, fh)
+            for r in ranks:                                                    # barrier
+                r.mark_built()
+            full = torch.from_numpy(ranks[0].idx.sa().astype(np.int32)).to(ranks[0].dev)
+            return full, ranks
         slices = [r.finish(edges) for r in ranks]
         full = torch.cat(slices)
         if adopt:
@@ -334,7 +365,8 @@ def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lo
 
 
 def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool = False, timing: bool = False,
-                      adopt: bool = True, group=None, device_text=None, builder=None, exchange: str = "p2p"):
+                      adopt: bool = True, group=None, device_text=None, builder=None, exchange: str = "p2p",
+                      replicate: str = "fused"):
     """This process's rank of the sample-sort build under torch.distributed (NCCL).
     -> (ShardBuilder with the complete SA adopted, dict of per-phase wall times in ms)."""
     import time
@@ -381,7 +413,7 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
         r.sort_recv()
         lap("sort+refine")
         r.exchange_bytes = int((send_counts.sum() - send_counts[rank]) * 12)
-        return _finish_distributed(r, t, lap, adopt, group)
+        return _finish_distributed(r, t, lap, adopt, group, replicate)
     send_counts = r.split(hist_np)
     sc = torch.from_numpy(send_counts.copy()).to(r.dev)
     rc = torch.empty_like(sc)
@@ -399,19 +431,31 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
     del recv_keys, recv_pos
     lap("sort+refine")
     r.exchange_bytes = int((send_counts.sum() - send_counts[rank]) * 12)
-    return _finish_distributed(r, t, lap, adopt, group)
+    return _finish_distributed(r, t, lap, adopt, group, replicate)
 
 
-def _finish_distributed(r, t, lap, adopt, group):
+def _finish_distributed(r, t, lap, adopt, group, replicate="fused"):
     import torch
     import torch.distributed as dist
     world = r.world
-    mine = torch.from_numpy(_edges_to_array(r.edges())).to(r.dev)
+    fused = adopt and replicate == "fused"
+    row = _edges_to_array(r.edges())
+    if fused:                                   # the final array's IPC handle rides along (8 int64 words)
+        row = np.concatenate([row, r.final_prepare().view(np.int64)])
+    mine = torch.from_numpy(row).to(r.dev)
     rows = torch.empty(world * mine.numel(), dtype=mine.dtype, device=r.dev)
     dist.all_gather_into_tensor(rows, mine, group=group)
     rows_np = rows.cpu().numpy().reshape(world, -1)
     edges = [_array_to_edges(rows_np[g]) for g in range(world)]
     lap("edges")
+    if fused:
+        handles = np.ascontiguousarray(rows_np[:, -8:]).view(np.uint8).reshape(world, 64)
+        r.finish_bcast(edges, handles)
+        dist.barrier(group=group)               # every rank's stores into every final array have completed
+        r.mark_built()
+        r.replicated_bytes = int(r.m) * 4 * (world - 1)
+        lap("finish+replicate")
+        return r, t
     sl = r.finish(edges)
     lap("finish")
     if adopt:

@@ -30,9 +30,9 @@ def test_boundary_lcp_rules():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("exchange", ["p2p", "nccl"])
+@pytest.mark.parametrize("exchange,replicate", [("p2p", "fused"), ("p2p", "allgather"), ("nccl", "allgather")])
 @pytest.mark.parametrize("world", [2, 3, 8])
-def test_emulated_ranks_match_oracle(world, exchange):
+def test_emulated_ranks_match_oracle(world, exchange, replicate):
     rng = np.random.default_rng(50 + world)
     cases = [
         (W.english_documents(300_000, seed=41), 32, False),
@@ -45,7 +45,7 @@ def test_emulated_ranks_match_oracle(world, exchange):
         (random_text(rng, 40, 2), 32, False),
     ]
     for text, L, lower in cases:
-        full, ranks = SH.build_emulated(text, L, world, lowercase=lower, exchange=exchange)
+        full, ranks = SH.build_emulated(text, L, world, lowercase=lower, exchange=exchange, replicate=replicate)
         want_text = O.oracle_lowercase(text) if lower else text
         want = O.oracle_build(want_text, L)
         got = full.cpu().numpy().astype(np.uint32)
