@@ -58,7 +58,7 @@ uint32_t sa_newline_tiles(uint32_t n);
 cudaError_t sa_launch_newline_count(const uint8_t* text, uint32_t n, uint32_t* counts, cudaStream_t s);
 cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, cudaStream_t s);
 cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint32_t* tile_offsets,
-                                    uint32_t* nlpos, cudaStream_t s);
+                                    uint32_t* nlpos, unsigned long long* nlbits, uint32_t* nlrank, cudaStream_t s);
 cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa, uint32_t n, uint32_t max_suffix_length,
                             const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
                             uint32_t* end, int mode /* 0 auto, 1 thread per query, 2 eight lanes per query */,
@@ -69,8 +69,8 @@ cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uin
 cudaError_t sa_launch_scan_u32_to_u64(const uint32_t* counts, uint32_t num, uint64_t* off, uint32_t* block_sums,
                                       cudaStream_t s);
 cudaError_t sa_launch_hits(const uint32_t* sa, const uint32_t* start, const uint64_t* hit_off, uint32_t nq,
-                           const uint32_t* nlpos, uint32_t num_nl, uint32_t* hit_pos, uint32_t* hit_doc,
-                           cudaStream_t s);
+                           const unsigned long long* nlbits, const uint32_t* nlrank, uint32_t* hit_pos,
+                           uint32_t* hit_doc, cudaStream_t s);
 cudaError_t sa_launch_remap(const uint32_t* sa, uint32_t n, const uint32_t* map, const uint8_t* quoted_by_text,
                             uint32_t* sa_out, uint32_t* quoted_bits_by_rank, cudaStream_t s);
 

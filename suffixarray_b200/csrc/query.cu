@@ -135,9 +135,21 @@ __global__ void __launch_bounds__(256) newline_count_kernel(const uint4* __restr
     }
 }
 
+// 8-bit mask of the bytes of w that equal '\n' (bit i = byte i)
+__device__ __forceinline__ uint32_t nl_mask8(uint64_t w)
+{
+    const uint64_t z = zero_bytes(w ^ 0x0A0A0A0A0A0A0A0Aull) >> 7;          // 0x01 per matching byte
+    return (uint32_t)((z * 0x0102040810204080ull) >> 56);
+}
+
+// positions of the '\n' bytes (nlpos, ascending) and a rank structure over them: one bit per text
+// byte (nlbits, 64 per word) + the number of '\n' in front of every 64-byte block (nlrank), so
+// "record index of text position p" is two independent loads instead of a bisection over nlpos.
 __global__ void __launch_bounds__(256) newline_write_kernel(const uint4* __restrict__ text16, uint32_t n,
                                                             const uint32_t* __restrict__ tile_offsets,
-                                                            uint32_t* __restrict__ nlpos)
+                                                            uint32_t* __restrict__ nlpos,
+                                                            unsigned long long* __restrict__ nlbits,
+                                                            uint32_t* __restrict__ nlrank)
 {
     __shared__ uint32_t ws[8];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -156,6 +168,17 @@ __global__ void __launch_bounds__(256) newline_write_kernel(const uint4* __restr
     uint32_t pre = tile_offsets[blockIdx.x];
     for (int w = 0; w < warp; ++w) pre += ws[w];
     uint32_t o = pre + inc - c;
+    {
+        const uint32_t m16 = nl_mask8(((uint64_t)v.y << 32) | v.x) | (nl_mask8(((uint64_t)v.w << 32) | v.z) << 8);
+        const uint32_t m1 = __shfl_down_sync(0xffffffffu, m16, 1), m2 = __shfl_down_sync(0xffffffffu, m16, 2),
+                       m3 = __shfl_down_sync(0xffffffffu, m16, 3);
+        const uint64_t blk = byte0 >> 6;
+        if ((lane & 3) == 0 && blk <= (uint64_t)(n >> 6)) {
+            nlbits[blk] = (unsigned long long)m16 | ((unsigned long long)m1 << 16) | ((unsigned long long)m2 << 32) |
+                          ((unsigned long long)m3 << 48);
+            nlrank[blk] = o;
+        }
+    }
     if (c) {
         const uint8_t* b = reinterpret_cast<const uint8_t*>(&v);
 #pragma unroll
@@ -337,8 +360,8 @@ __global__ void hit_counts_kernel(const uint32_t* __restrict__ start, const uint
 // one warp per query: rank -> text position -> record index (# of '\n' before the position)
 __global__ void __launch_bounds__(256)
 hits_kernel(const uint32_t* __restrict__ sa, const uint32_t* __restrict__ start,
-            const uint64_t* __restrict__ hit_off, uint32_t nq, const uint32_t* __restrict__ nlpos,
-            uint32_t num_nl, uint32_t* __restrict__ hit_pos, uint32_t* __restrict__ hit_doc)
+            const uint64_t* __restrict__ hit_off, uint32_t nq, const unsigned long long* __restrict__ nlbits,
+            const uint32_t* __restrict__ nlrank, uint32_t* __restrict__ hit_pos, uint32_t* __restrict__ hit_doc)
 {
     const uint32_t wq = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (wq >= nq) return;
@@ -347,13 +370,12 @@ hits_kernel(const uint32_t* __restrict__ sa, const uint32_t* __restrict__ start,
     const uint32_t s = start[wq];
     for (uint32_t j = threadIdx.x & 31; j < take; j += 32) {
         const uint32_t p = sa[(uint64_t)s + j];
-        uint32_t lo = 0, hi = num_nl;
-        while (lo < hi) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (__ldg(nlpos + mid) < p) lo = mid + 1; else hi = mid;
-        }
         if (hit_pos) hit_pos[o + j] = p;
-        if (hit_doc) hit_doc[o + j] = lo;
+        if (hit_doc) {
+            // record index = number of '\n' in front of p
+            const unsigned long long bits = __ldg(nlbits + (p >> 6));
+            hit_doc[o + j] = __ldg(nlrank + (p >> 6)) + (uint32_t)__popcll(bits & ((1ull << (p & 63u)) - 1ull));
+        }
     }
 }
 
@@ -397,11 +419,12 @@ cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, 
 }
 
 cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint32_t* tile_offsets, uint32_t* nlpos,
-                                    cudaStream_t s)
+                                    unsigned long long* nlbits, uint32_t* nlrank, cudaStream_t s)
 {
     const uint32_t tiles = (n + sa::NL_TILE - 1) / sa::NL_TILE;
     if (!tiles) return cudaSuccess;
-    sa::newline_write_kernel<<<tiles, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), n, tile_offsets, nlpos);
+    sa::newline_write_kernel<<<tiles, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), n, tile_offsets, nlpos, nlbits,
+                                                   nlrank);
     return cudaGetLastError();
 }
 
@@ -443,12 +466,12 @@ cudaError_t sa_launch_scan_u32_to_u64(const uint32_t* counts, uint32_t num, uint
 }
 
 cudaError_t sa_launch_hits(const uint32_t* sa_, const uint32_t* start, const uint64_t* hit_off, uint32_t nq,
-                           const uint32_t* nlpos, uint32_t num_nl, uint32_t* hit_pos, uint32_t* hit_doc,
-                           cudaStream_t s)
+                           const unsigned long long* nlbits, const uint32_t* nlrank, uint32_t* hit_pos,
+                           uint32_t* hit_doc, cudaStream_t s)
 {
     if (!nq) return cudaSuccess;
     const uint64_t threads = (uint64_t)nq * 32;
-    sa::hits_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(sa_, start, hit_off, nq, nlpos, num_nl, hit_pos,
+    sa::hits_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(sa_, start, hit_off, nq, nlbits, nlrank, hit_pos,
                                                                      hit_doc);
     return cudaGetLastError();
 }

@@ -250,13 +250,14 @@ extern "C" int sa_query_hits(sa_index* idx, uint32_t* hit_pos, uint32_t* hit_doc
     SA_REQUIRE(cap >= total, SA_ERR_INVALID, "cap %llu < %llu hits", (unsigned long long)cap, (unsigned long long)total);
     if (total == 0 || idx->last_nq == 0) return SA_OK;
     cudaStream_t s = idx->stream;
-    SA_CU(idx->hitpos.ensure((size_t)total * 4));
-    SA_CU(idx->hitdoc.ensure((size_t)total * 4));
+    if (hit_pos) SA_CU(idx->hitpos.ensure((size_t)total * 4));
+    if (hit_doc) SA_CU(idx->hitdoc.ensure((size_t)total * 4));
     {
         ScopedPhase ph(idx, &idx->stats.ms_hits);
         SA_CU(sa_launch_hits(idx->sa_final.as<uint32_t>(), idx->qstart.as<uint32_t>(), idx->hitoff.as<uint64_t>(),
-                             (uint32_t)idx->last_nq, idx->nlpos.as<uint32_t>(), idx->num_nl,
-                             idx->hitpos.as<uint32_t>(), idx->hitdoc.as<uint32_t>(), s));
+                             (uint32_t)idx->last_nq, idx->nlbits.as<unsigned long long>(), idx->nlrank.as<uint32_t>(),
+                             hit_pos ? idx->hitpos.as<uint32_t>() : nullptr, hit_doc ? idx->hitdoc.as<uint32_t>() : nullptr,
+                             s));
         idx->stats.kernel_launches += 1;
     }
     if (hit_pos) SA_CU(cudaMemcpyAsync(hit_pos, idx->hitpos.p, total * 4, cudaMemcpyDeviceToHost, s));

@@ -69,6 +69,7 @@ struct sa_index {
     // persistent after a build
     DevBuf text;        // n + SA_TEXT_PAD bytes, zero padded
     DevBuf sa_final;    // u32[n] text positions in ORDER-E
+    DevBuf nlbits, nlrank;   // rank structure over the '\n' bytes: u64 bit mask + u32 count in front, per 64 text bytes
     DevBuf nlpos;       // u32[num_nl] positions of '\n'
     uint32_t num_nl = 0;
     DevBuf sa_file;     // CSV: u32[n] file offsets (engine.c:647-651)
