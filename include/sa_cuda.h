@@ -167,6 +167,16 @@ int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, const uint16_
                           int nranks, int my_rank, const uint8_t* handles, uint64_t global_offset);
 int sa_shard_mark_built(sa_index* idx);
 
+/* Persistence (the reference only sketches it: write_suffix_array / read_into_suffix_array_file,
+ * engine.c:1098-1165, TODO.md).  sa_save writes one container file (text, ORDER-E positions, and for
+ * CSV indexes the file offsets + quoted bits); sa_load restores it into a handle created with the
+ * same max_suffix_length -- the index then answers queries without sorting anything.
+ * sa_export_reference_files writes the reference's own two-file layout (u64 start, u64 end, u32 L,
+ * u32 n, u32 SA[n]; u32 capacity + quoted bits); quoted_path may be NULL. */
+int sa_save(sa_index* idx, const char* path);
+int sa_load(sa_index* idx, const char* path);
+int sa_export_reference_files(sa_index* idx, const char* sa_path, const char* quoted_path);
+
 /* Debug / parity hooks (used by tests to localise a mismatch; not part of the drop-in). */
 int sa_debug_copy_lcp(sa_index* idx, uint16_t* out, uint64_t cap);
 int sa_debug_set(sa_index* idx, const char* key, int64_t value);

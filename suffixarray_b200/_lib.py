@@ -31,6 +31,7 @@ EXPORTS = [
     "sa_shard_begin", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
     "sa_adopt_sa", "sa_adopt_sa_parts", "sa_shard_count", "sa_shard_recv_prepare", "sa_shard_scatter_p2p", "sa_shard_sort_recv",
     "sa_shard_final_prepare", "sa_shard_finish_bcast", "sa_shard_mark_built",
+    "sa_save", "sa_load", "sa_export_reference_files",
 ]
 
 
@@ -115,6 +116,9 @@ def lib():
     L.sa_shard_finish_bcast.argtypes = [_vp, _vp, _vp, C.c_uint32, C.c_uint32, _vp, _vp, C.c_uint32, C.c_int, C.c_int,
                                         _vp, C.c_uint64]
     L.sa_shard_mark_built.argtypes = [_vp]
+    L.sa_save.argtypes = [_vp, C.c_char_p]
+    L.sa_load.argtypes = [_vp, C.c_char_p]
+    L.sa_export_reference_files.argtypes = [_vp, C.c_char_p, C.c_char_p]
     _lib = L
     return L
 
@@ -158,6 +162,15 @@ class Index:
 
     def build_csv(self, path: str, column: str, timing: bool = False):
         check(lib().sa_build_csv(self._h, path.encode(), column.encode(), SA_FLAG_TIMING if timing else 0))
+
+    def save(self, path: str):
+        check(lib().sa_save(self._h, path.encode()))
+
+    def load(self, path: str):
+        check(lib().sa_load(self._h, path.encode()))
+
+    def export_reference_files(self, sa_path: str, quoted_path: str | None = None):
+        check(lib().sa_export_reference_files(self._h, sa_path.encode(), quoted_path.encode() if quoted_path else None))
 
     def debug_set(self, key: str, value: int):
         check(lib().sa_debug_set(self._h, key.encode(), value))

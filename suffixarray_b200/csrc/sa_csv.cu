@@ -324,6 +324,7 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
     SA_CU(cudaStreamSynchronize(s));
     sa_time_collect(idx);
     idx->csv = true;
+    idx->csv_file_bytes = m.size;
     idx->built = true;
     return SA_OK;
 }

@@ -79,6 +79,7 @@ struct sa_index {
     void* h_ring[2] = {nullptr, nullptr};      // pinned staging ring of the file reader
     cudaEvent_t ring_ev[2] = {nullptr, nullptr};
     size_t ring_bytes = 0;
+    uint64_t csv_file_bytes = 0;               // size of the CSV file of the last sa_build_csv
 
     // build scratch (kept between builds so repeated builds do not re-allocate)
     DevBuf keys[2], vals[2], aux[2], lcp, tie, amask, hmask, counts, status, small, nl_counts;

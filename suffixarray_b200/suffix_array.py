@@ -174,6 +174,44 @@ class SuffixArray:
             rows.append(line.rstrip("\r"))
         return [dict(zip(self.columns, row)) for row in csv.reader(rows)]   # pyx:258-260
 
+    # ------------------------------------------------------------------ persistence
+    def save(self, path: str) -> None:
+        """Write the built index to `path` (+ `path.partNNN` for further partitions, + `path.json`
+        with what the host side needs).  The reference only sketches this (engine.c:1098-1165)."""
+        if self._mode is None:
+            raise RuntimeError("no suffix array has been constructed")
+        import json
+        for i, idx in enumerate(self._parts):
+            idx.save(path if i == 0 else f"{path}.part{i:03d}")
+        meta = {"mode": self._mode, "max_suffix_length": self.max_suffix_length, "partitions": len(self._parts),
+                "partition_bytes": int(self.PARTITION_BYTES), "columns": self.columns, "csv_path": self._csv_path}
+        with open(path + ".json", "w") as f:
+            json.dump(meta, f)
+
+    @classmethod
+    def load(cls, path: str, device: int = 0) -> "SuffixArray":
+        """Restore an index written by save(): no sorting, the arrays go straight to the device."""
+        import json
+        with open(path + ".json") as f:
+            meta = json.load(f)
+        self = cls(max_suffix_length=int(meta["max_suffix_length"]), device=device)
+        self.PARTITION_BYTES = int(meta["partition_bytes"])
+        self._parts = [self._idx] + [S.Index(self.max_suffix_length, device=device)
+                                     for _ in range(int(meta["partitions"]) - 1)]
+        for i, idx in enumerate(self._parts):
+            idx.load(path if i == 0 else f"{path}.part{i:03d}")
+        self._mode = meta["mode"]
+        if self._mode == "documents":
+            low = np.concatenate([idx.text() for idx in self._parts]) if self._parts else np.zeros(0, np.uint8)
+            self._text = low.tobytes()
+            nl = np.flatnonzero(low == 10).astype(np.int64)
+            self._doc_starts = np.concatenate([[0], nl + 1]).astype(np.int64)
+        else:
+            self.columns = meta["columns"]
+            self._csv_path = meta["csv_path"]
+            self._open_csv(self._csv_path)          # rows are materialised from the CSV file itself
+        return self
+
     # ------------------------------------------------------------------ misc
     @property
     def suffix_array(self) -> np.ndarray:

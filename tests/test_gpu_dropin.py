@@ -105,3 +105,41 @@ def test_partitioned_documents_walk(monkeypatch):
                 break
         assert sa.query_records(q, k=k) == want
     sa.close()
+
+
+def test_save_load_round_trip(tmp_path):
+    """a saved index answers queries after load without being rebuilt; the
+    reference-layout export holds (u64 start, u64 end, u32 L, u32 n, u32 SA[n])."""
+    from suffixarray_b200 import _lib as S
+    names = W.company_names(3000, seed=17, upper=True)
+    docs = [b.decode() for b in names]
+    sa = SuffixArray(documents=docs, max_suffix_length=32)
+    p = str(tmp_path / "docs.sa")
+    sa.save(p)
+    sb = SuffixArray.load(p)
+    assert np.array_equal(sa.suffix_array, sb.suffix_array)
+    for q in ("inc", "group", docs[5].lower(), "zzzz"):
+        assert sa.query_records(q, k=50) == sb.query_records(q, k=50)
+    sa._idx.export_reference_files(p + ".ref", p + ".refq")
+    raw = np.fromfile(p + ".ref", dtype=np.uint8)
+    start, end = np.frombuffer(raw[:16].tobytes(), np.uint64)
+    L, n = np.frombuffer(raw[16:24].tobytes(), np.uint32)
+    assert (start, L, n) == (0, 32, sa._idx.n) and end == n
+    assert np.array_equal(np.frombuffer(raw[24:].tobytes(), np.uint32), sa.suffix_array)
+    sa.close()
+    sb.close()
+    # CSV index: file offsets and quoted bits survive the round trip
+    data = W.csv_file_bytes(400, seed=5, quoted_fraction=0.3)
+    path = str(tmp_path / "t.csv")
+    with open(path, "wb") as f:
+        f.write(data)
+    a = SuffixArray(csv_file=path, search_column="name", max_suffix_length=32)
+    a.save(str(tmp_path / "csv.sa"))
+    b = SuffixArray.load(str(tmp_path / "csv.sa"))
+    assert np.array_equal(a.suffix_array, b.suffix_array)
+    assert np.array_equal(a._idx.quoted_bits(), b._idx.quoted_bits())
+    assert a.query_records("inc", k=20) == b.query_records("inc", k=20)
+    with pytest.raises(Exception):
+        S.Index(16).load(str(tmp_path / "csv.sa"))        # max_suffix_length mismatch
+    a.close()
+    b.close()
