@@ -155,9 +155,10 @@ int sa_shard_scatter_p2p(sa_index* idx, const uint64_t* d_keys, const uint32_t* 
                          int my_rank, const uint8_t* handles, const uint64_t* dst_offset);
 int sa_shard_sort_recv(sa_index* idx, uint64_t m);
 
-/* Fused finish + replicate (no all-gather, no adopt copy): finish_kernel stores every placed
- * position into all ranks' final arrays, the local one directly and the peers' through CUDA IPC
- * mappings over NVLink.  sa_shard_final_prepare exports this rank's array (handle_final: 64 bytes);
+/* Finish + replicate, overlapped (no all-gather, no adopt copy): the shard is finished in chunks
+ * straight into this rank's final array while the previous chunk is pushed into every peer's final
+ * array over NVLink (device-to-device copies into CUDA IPC mappings on a second stream).
+ * sa_shard_final_prepare exports this rank's array (handle_final: 64 bytes);
  * sa_shard_finish_bcast takes all ranks' handles (64 bytes each) and the global rank of this
  * shard's first record; after a barrier over the ranks sa_shard_mark_built makes the index
  * queryable.  Same halo arguments as sa_shard_finish. */

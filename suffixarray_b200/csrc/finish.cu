@@ -95,7 +95,8 @@ __device__ __forceinline__ void put(const FinishOut& o, int64_t x, uint32_t pos)
 __global__ void __launch_bounds__(FTHREADS)
 finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ lcp,
               const uint8_t* __restrict__ text, uint32_t n, uint32_t lprime, uint32_t r_begin, uint32_t r_end,
-              const FinishOut outs, unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err)
+              const FinishOut outs, unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err,
+              uint32_t block0)
 {
     __shared__ int16_t s_l[FLCP];        // adjacent LCPs, -1 outside [1, n)
     __shared__ int16_t s_p[FLCP];        // block prefix min of l, later block prefix max of m
@@ -105,7 +106,7 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
     __shared__ uint32_t s_runs;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t b0 = (int64_t)blockIdx.x * FT;
+    const int64_t b0 = (int64_t)(blockIdx.x + block0) * FT;
     uint64_t keep;
     asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
     if (tid == 0) s_runs = 0;
@@ -239,10 +240,17 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
 
 cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,
                              uint32_t lprime, uint32_t r_begin, uint32_t r_end, const sa::FinishOut& outs,
-                             unsigned long long* run_counter, uint32_t* err, cudaStream_t s)
+                             unsigned long long* run_counter, uint32_t* err, cudaStream_t s, uint32_t block0,
+                             uint32_t nblocks)
 {
     if (!n) return cudaSuccess;
-    const uint32_t blocks = (n + sa::FT - 1) / sa::FT;
-    sa::finish_kernel<<<blocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, outs, run_counter, err);
+    const uint32_t blocks = sa_finish_blocks(n);
+    if (block0 >= blocks) return cudaSuccess;
+    if (nblocks > blocks - block0) nblocks = blocks - block0;
+    sa::finish_kernel<<<nblocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, outs, run_counter, err,
+                                                       block0);
     return cudaGetLastError();
 }
+
+uint32_t sa_finish_blocks(uint32_t n) { return (n + sa::FT - 1) / sa::FT; }
+uint32_t sa_finish_block_ranks() { return sa::FT; }

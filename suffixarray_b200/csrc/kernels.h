@@ -51,7 +51,10 @@ cudaError_t sa_launch_writeback(const uint32_t* slots, const uint64_t* ckeys, co
 // ---- finish.cu
 cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const uint8_t* text, uint32_t n,
                              uint32_t lprime, uint32_t r_begin, uint32_t r_end, const sa::FinishOut& outs,
-                             unsigned long long* run_counter, uint32_t* err, cudaStream_t s);
+                             unsigned long long* run_counter, uint32_t* err, cudaStream_t s, uint32_t block0 = 0,
+                             uint32_t nblocks = 0xFFFFFFFFu);
+uint32_t sa_finish_blocks(uint32_t n);       // blocks of sa_finish_block_ranks() consecutive ranks
+uint32_t sa_finish_block_ranks();
 
 // ---- query.cu
 uint32_t sa_newline_tiles(uint32_t n);

@@ -91,6 +91,10 @@ extern "C" void sa_destroy(sa_index* idx)
                      &idx->ext_sa, &idx->ext_lcp, &idx->ext_out, &idx->split_table, &idx->split_offsets,
                      &idx->csv_file, &idx->csv_tq, &idx->csv_td, &idx->csv_te, &idx->nlbits, &idx->nlrank};
     for (DevBuf* b : all) b->release();
+    for (int i = 0; i < 16; ++i) {
+        if (idx->copy_streams[i]) cudaStreamDestroy(idx->copy_streams[i]);
+        if (idx->chunk_ev[i]) cudaEventDestroy(idx->chunk_ev[i]);
+    }
     for (int i = 0; i < 2; ++i) {
         if (idx->h_ring[i]) cudaFreeHost(idx->h_ring[i]);
         if (idx->ring_ev[i]) cudaEventDestroy(idx->ring_ev[i]);
@@ -352,7 +356,7 @@ int sa_stage_finish(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint
 }
 
 int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
-                       uint32_t r_end, const sa::FinishOut& outs)
+                       uint32_t r_end, const sa::FinishOut& outs, uint32_t block0, uint32_t nblocks)
 {
     uint32_t* out = outs.out[0];
     cudaStream_t s = idx->stream;
@@ -363,7 +367,7 @@ int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, u
         SA_CU(cudaMemcpyAsync(out, sa, (size_t)m * 4, cudaMemcpyDeviceToDevice, s));
     } else {
         SA_CU(sa_launch_finish(sa, lcp, idx->text.as<uint8_t>(), m, idx->lprime, r_begin, r_end, outs,
-                               reinterpret_cast<unsigned long long*>(sm + SM_RUNCTR), sm + SM_ERR, s));
+                               reinterpret_cast<unsigned long long*>(sm + SM_RUNCTR), sm + SM_ERR, s, block0, nblocks));
         st.kernel_launches += 1;
     }
     return SA_OK;

@@ -100,6 +100,8 @@ struct sa_index {
     void* peer_final[16] = {};                 // peers' sa_final arrays (fused finish + replicate)
     cudaIpcMemHandle_t peer_hf[16] = {};
     bool peer_final_mapped[16] = {};
+    cudaStream_t copy_streams[16] = {};        // replication copies (one stream per peer) run beside the finishing kernels
+    cudaEvent_t chunk_ev[16] = {};
 
     // query scratch / results of the last batch
     DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
@@ -166,5 +168,5 @@ int sa_stage_sort_refine(sa_index* idx, uint32_t m, bool identity, uint32_t** sa
 int sa_stage_finish(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
                     uint32_t r_end, uint32_t* out);
 int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
-                       uint32_t r_end, const sa::FinishOut& outs);
+                       uint32_t r_end, const sa::FinishOut& outs, uint32_t block0 = 0, uint32_t nblocks = 0xFFFFFFFFu);
 int sa_check_device_error(sa_index* idx);

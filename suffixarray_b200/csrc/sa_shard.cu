@@ -425,8 +425,7 @@ static int shard_finish_common(sa_index* idx, const uint32_t* left_pos, const ui
     idx->stats.kernel_launches += 1;
     const uint32_t r_begin = nleft - (nleft < 32 ? nleft : 32);
     const uint32_t r_end = nleft + m + (nright < 32 ? nright : 32);
-    if (outs)
-        return sa_stage_finish_to(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end, *outs);
+    if (outs) return SA_OK;                   // the caller launches the finishing kernels itself (chunked)
     return sa_stage_finish(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end,
                            idx->ext_out.as<uint32_t>());
 }
@@ -451,10 +450,13 @@ extern "C" int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const ui
     return rc;
 }
 
-// ------------------------------------------------------------------------------ fused finish + replicate
-// Instead of "finish into a local slice, all-gather the slices, copy into place", finish_kernel can
-// store every placed position straight into ALL ranks' final arrays (local HBM + peer stores over
-// NVLink): the replication overlaps the finishing compute and the gather / adopt passes disappear.
+// ------------------------------------------------------------------------------ finish + replicate, overlapped
+// Instead of "finish into a local slice, all-gather the slices, copy into place", the shard is
+// finished in chunks straight into this rank's final array, and while chunk c+1 is being finished
+// chunk c is pushed into every peer's final array (device-to-device copies over NVLink into CUDA IPC
+// mappings, on a second stream): replication hides behind the finishing kernels and the gather /
+// adopt passes disappear.  (Letting finish_kernel itself store to all peers works too -- FinishOut
+// carries up to 16 replicas -- but 4-byte peer stores reach only ~260 GB/s at 8 GPUs.)
 // 1. sa_shard_final_prepare: allocate this rank's final array (n entries) and export its IPC handle.
 extern "C" int sa_shard_final_prepare(sa_index* idx, uint8_t* handle_final)
 {
@@ -475,9 +477,9 @@ extern "C" int sa_shard_final_prepare(sa_index* idx, uint8_t* handle_final)
     return SA_OK;
 }
 
-// 2. sa_shard_finish_bcast: like sa_shard_finish, but the m placed positions of this shard are
-//    written to final[global_offset .. global_offset + m) of every rank (handles: 64 bytes per rank,
-//    from sa_shard_final_prepare).  After a barrier over all ranks call sa_shard_mark_built.
+// 2. sa_shard_finish_bcast: like sa_shard_finish, but the m placed positions of this shard end up in
+//    final[global_offset .. global_offset + m) of every rank (handles: 64 bytes per rank, from
+//    sa_shard_final_prepare).  After a barrier over all ranks call sa_shard_mark_built.
 extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
                                      uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp,
                                      uint32_t nright, int nranks, int my_rank, const uint8_t* handles,
@@ -487,13 +489,11 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     SH_REQUIRE(nleft <= 4096 && nright <= 4096, SA_ERR_LIMIT, "sa_shard_finish_bcast: halo too large");
     SH_REQUIRE(nranks >= 1 && nranks <= 16 && my_rank >= 0 && my_rank < nranks, SA_ERR_INVALID, "sa_shard_finish_bcast: bad rank");
     SH_REQUIRE(global_offset + idx->shard_m <= idx->n, SA_ERR_INVALID, "sa_shard_finish_bcast: slice outside the array");
+    SH_REQUIRE(idx->sa_final.p, SA_ERR_INVALID, "sa_shard_finish_bcast: call sa_shard_final_prepare first");
     std::lock_guard<std::mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     const uint32_t m = idx->shard_m;
-    sa::FinishOut fo{};
-    fo.n = nranks;
-    fo.lo = nleft;
-    fo.hi = nleft + m;
+    uint32_t* peer_base[16] = {};
     for (int g = 0; g < nranks; ++g) {
         void* base = nullptr;
         const uint8_t* h = handles + (size_t)g * 64;
@@ -511,13 +511,53 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
             base = idx->peer_final[g];
         }
         SH_REQUIRE(base, SA_ERR_INVALID, "sa_shard_finish_bcast: rank %d has no final array", g);
-        // extended rank x (>= nleft) -> global rank global_offset + x - nleft
-        fo.out[g] = static_cast<uint32_t*>(base) + global_offset - nleft;
+        peer_base[g] = static_cast<uint32_t*>(base);
     }
     if (m == 0) return SA_OK;
+    cudaStream_t s = idx->stream;
+    for (int g = 0; g < nranks; ++g)
+        if (g != my_rank && !idx->copy_streams[g]) SA_CU(cudaStreamCreateWithFlags(&idx->copy_streams[g], cudaStreamNonBlocking));
+    constexpr int CHUNKS = 8;
+    for (int c = 0; c < CHUNKS; ++c)
+        if (!idx->chunk_ev[c]) SA_CU(cudaEventCreateWithFlags(&idx->chunk_ev[c], cudaEventDisableTiming));
+
+    // extended rank x (>= nleft) lives at global rank global_offset + x - nleft of the final arrays
+    sa::FinishOut fo{};
+    fo.n = 1;
+    fo.lo = nleft;
+    fo.hi = nleft + m;
+    fo.out[0] = peer_base[my_rank] + global_offset - nleft;
     int rc = shard_finish_common(idx, left_pos, left_lcp, nleft, lcp_first, right_pos, right_lcp, nright, &fo);
     if (rc != SA_OK) return rc;
-    rc = sa_check_device_error(idx);          // synchronises the stream: all peer stores of this rank are issued and done
+    const uint32_t total = nleft + m + nright;
+    const uint32_t r_begin = nleft - (nleft < 32 ? nleft : 32);
+    const uint32_t r_end = nleft + m + (nright < 32 ? nright : 32);
+    const uint32_t blocks = sa_finish_blocks(total), FTR = sa_finish_block_ranks();
+    const uint32_t per = (blocks + CHUNKS - 1) / CHUNKS;
+    uint32_t copied_to = nleft;               // extended rank up to which the peers are up to date
+    for (int c = 0; c < CHUNKS && (uint64_t)c * per < blocks; ++c) {
+        const uint32_t b0 = (uint32_t)c * per;
+        rc = sa_stage_finish_to(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end, fo, b0, per);
+        if (rc != SA_OK) return rc;
+        SA_CU(cudaEventRecord(idx->chunk_ev[c], s));
+        // a bucket may reach 32 ranks back into the previous chunk: ranks below hi_c - 32 are final now
+        const bool last = (uint64_t)(c + 1) * per >= blocks;
+        uint64_t upto = last ? (uint64_t)nleft + m : (uint64_t)(b0 + per) * FTR;
+        if (!last) upto = upto > 32 ? upto - 32 : 0;
+        if (upto > (uint64_t)nleft + m) upto = (uint64_t)nleft + m;
+        if (upto <= copied_to) continue;
+        const size_t off = (size_t)global_offset + copied_to - nleft, cnt = (size_t)(upto - copied_to);
+        for (int k = 1; k < nranks; ++k) {    // one stream per peer: the copies to different peers run side by side
+            const int g = (my_rank + k) % nranks;
+            SA_CU(cudaStreamWaitEvent(idx->copy_streams[g], idx->chunk_ev[c], 0));
+            SA_CU(cudaMemcpyAsync(peer_base[g] + off, peer_base[my_rank] + off, cnt * 4, cudaMemcpyDeviceToDevice,
+                                  idx->copy_streams[g]));
+        }
+        copied_to = (uint32_t)upto;
+    }
+    for (int g = 0; g < nranks; ++g)
+        if (g != my_rank) SA_CU(cudaStreamSynchronize(idx->copy_streams[g]));
+    rc = sa_check_device_error(idx);          // synchronises the build stream
     sa_time_collect(idx);
     return rc;
 }
