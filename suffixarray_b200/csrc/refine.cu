@@ -305,20 +305,36 @@ compact_gather_kernel(const uint32_t* __restrict__ amask, const uint32_t* __rest
     }
     __syncthreads();
     const uint32_t out0 = tile_offsets[2 * blockIdx.x];
-    for (uint32_t j = t; j < tot; j += T) {
-        const uint32_t r = s_rank[j];
-        const uint32_t p = sa[r];
-        uint64_t wd;
-        if (ci.bits == 8) {
-            wd = mask_word(load_be64(text, (uint64_t)p + depth), cb);
-        } else {
-            uint64_t w0, w1;
-            load_be128(text, (uint64_t)p + depth, w0, w1);
-            wd = pack_chars(w0, w1, cb, ci);
+    // two dependent random reads per record (sa[r], then the text at sa[r] + depth): four records
+    // per thread are kept in flight so the gather is not one DRAM latency per record
+    constexpr int B = 4;
+    for (uint32_t j0 = t; j0 < tot; j0 += T * B) {
+        uint32_t r[B], p[B];
+        uint64_t w0[B], w1[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u) {
+            const uint32_t j = j0 + u * T;
+            r[u] = j < tot ? s_rank[j] : 0u;
         }
-        slots[out0 + j] = r;
-        cvals[out0 + j] = p;
-        ckeys[out0 + j] = ((uint64_t)s_gid[j] << (64 - gbits)) | (wd >> gbits);
+#pragma unroll
+        for (int u = 0; u < B; ++u) p[u] = (j0 + u * T < tot) ? __ldg(sa + r[u]) : 0u;
+#pragma unroll
+        for (int u = 0; u < B; ++u) {
+            w0[u] = w1[u] = 0;
+            if (j0 + u * T < tot) {
+                if (ci.bits == 8) w0[u] = load_be64(text, (uint64_t)p[u] + depth);
+                else load_be128(text, (uint64_t)p[u] + depth, w0[u], w1[u]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < B; ++u) {
+            const uint32_t j = j0 + u * T;
+            if (j >= tot) continue;
+            const uint64_t wd = ci.bits == 8 ? mask_word(w0[u], cb) : pack_chars(w0[u], w1[u], cb, ci);
+            slots[out0 + j] = r[u];
+            cvals[out0 + j] = p[u];
+            ckeys[out0 + j] = ((uint64_t)s_gid[j] << (64 - gbits)) | (wd >> gbits);
+        }
     }
 }
 
