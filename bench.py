@@ -558,7 +558,7 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
                 "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "api": "sa_build_text + sa_query_ranges + sa_query_hits (pinned host buffers)"},
         "gpu_launches": int(sum(r["build_launches"] + r["query_launches"] for r in recs)),
-        "roofline": {"kernel": "onesweep_kernel (radix scatter pass)", "bound": "hbm",
+        "roofline": {"kernel": "onesweep4_kernel (radix scatter pass)", "bound": "hbm",
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "peak_source": peak_src,
                      "bytes_per_launch": int(os_bytes_per_launch), "avg_launch_ms": round(os_avg_ms, 4),
@@ -586,6 +586,16 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
                                          "get_substring_positions under an omp parallel-for; records: first "
                                          f"{cb['record_sample']} queries through get_matching_records, k = {K_HITS} "
                                          f"({cb['records']} records, {cb['record_s']:.2f} s)"}
+        if cb["kind"] == "reference":
+            # BASELINE.json's other CPU arm: the vendored libsais (a FULL suffix array, not ORDER-E: timing only)
+            from oracle import pyoracle as O
+            low = (O.oracle_lowercase(text) if lower else text)[:50_000_000]      # bounded sample
+            t0 = time.perf_counter()
+            O.ref_libsais(low, threads=0)
+            tl = time.perf_counter() - t0
+            out["cpu_baseline"]["libsais_omp"] = {"value": round(low.size / tl / 1e6, 2), "unit": "Mchars/s (full SA, untruncated)",
+                                                  "cores": cb["cores"], "seconds": round(tl, 2), "sample_chars": int(low.size),
+                                                  "note": "libsais_omp from the reference tree (SURVEY 8(d) baseline B); not a parity oracle"}
     return out
 
 
