@@ -611,6 +611,7 @@ onesweep4_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
     uint32_t val[IPT];
     uint32_t rank2[IPT / 2];                                 // two 16-bit ranks per register
     if (tid == 0) s_tile[0] = atomicAdd(tile_counter, 1u);
+    for (int i = tid; i < WARPS * 256; i += MAIN) whist[i] = 0;
     named_sync(1, MAIN);
     {
         const uint32_t t0 = s_tile[0];
@@ -628,8 +629,8 @@ onesweep4_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
     OS_CLK_INIT;
     for (uint32_t it = 0;; ++it) {
         const int b = it & 1;
-        for (int i = tid; i < WARPS * 256; i += MAIN) whist[i] = 0;
-        named_sync(1, MAIN);                                  // zeroed counters + s_tile[it & 3] visible
+        // s_tile[it & 3] was written one iteration ago (barriers in between); the per-warp counters
+        // were re-zeroed by their own warp after the previous re-order
         OS_CLK(0);
         const uint32_t tile = s_tile[it & 3];
         const bool valid = tile < num_tiles;
@@ -706,6 +707,9 @@ onesweep4_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
                     vb[lp] = IDENTITY_VALS ? idx : val[i];
                 }
             }
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) myhist[i * 32 + lane] = 0;     // own counters, ready for the next tile
             OS_CLK(4);
             // the registers are free again: start the loads of the next tile
             const uint32_t nt = s_tile[(it + 1) & 3];
@@ -749,8 +753,6 @@ onesweep4_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
                 }
             }
             OS_CLK(7);
-        } else {
-            named_sync(1, MAIN);                              // the per-warp counters are re-zeroed next
         }
         if (!valid) return;
         prev_n = tile_n;
