@@ -70,10 +70,18 @@ def parse_args():
     ap.add_argument("--replicate", default="fused", choices=["fused", "allgather"],
                     help="N > 1: how every rank gets the complete array: the finish kernel stores into all ranks' arrays "
                          "(peer stores over NVLink), or NCCL all-gather of the slices + copy")
+    ap.add_argument("--chars-per-gpu", type=int, default=0, help="override the c2 text size per GPU (scale runs)")
+    ap.add_argument("--queries-per-gpu", type=int, default=0, help="override the query batch size per GPU")
+    ap.add_argument("--verify-single", action="store_true",
+                    help="N > 1: after the timed steps rank 0 also builds the same text on ONE GPU and the arrays are "
+                         "compared bit for bit; every rank's replica is compared through a digest")
     ap.add_argument("--mode", default="global", choices=["global", "partition"],
                     help="N > 1: one global index built as a sample sort (default) or one independent "
                          "partition per GPU (the reference's own partitioning, suffix_array.pyx:148-180)")
     return ap.parse_args()
+
+
+OVERRIDE = {}
 
 
 def make_workload(name: str, rank: int):
@@ -81,6 +89,8 @@ def make_workload(name: str, rank: int):
     multi-GPU run gets its own partition (seed + r)."""
     from suffixarray_b200 import workloads as W
     n_chars, nq, _ = WORKLOADS[name]
+    n_chars = OVERRIDE.get("chars") or n_chars
+    nq = OVERRIDE.get("queries") or nq
     if name == "c1":
         text, starts = W.company_names_joined(1_000_000, seed=1001 + rank, upper=True)
         qs = W.whole_name_queries(text, starts, nq, seed=1002 + rank)
@@ -398,6 +408,30 @@ def run_ours_global(args, world, rank, local):
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t_wall0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
+    verify = None
+    if args.verify_single:
+        import hashlib
+        mine = builders["dev"].idx.sa()
+        digest = hashlib.blake2b(mine.tobytes(), digest_size=8).digest()
+        dg = torch.tensor(list(digest), dtype=torch.int32, device=dev)
+        all_dg = [torch.zeros_like(dg) for _ in range(world)]
+        dist.all_gather(all_dg, dg)
+        replicas_equal = all(bool(torch.equal(all_dg[0], x)) for x in all_dg)
+        if rank == 0:
+            for b in (builders["e2e"],):
+                if b is not None:
+                    b.close()
+            builders["e2e"] = None
+            single = S.Index(L, device=local)
+            single.build_text_device(d_text.data_ptr(), n, (S.SA_FLAG_LOWERCASE if lower else 0) | S.SA_FLAG_TIMING)
+            st1 = single.stats()
+            same = bool(np.array_equal(single.sa(), mine))
+            verify = {"single_gpu_equal": same, "replicas_equal": replicas_equal, "n": int(n),
+                      "single_gpu_build_ms": round(st1["ms_total"], 2),
+                      "single_gpu_mchars_per_s": round(n / st1["ms_total"] / 1e3, 1)}
+            single.close()
+        del mine
+        dist.barrier()
     K = args.steps
     phase_names = list(recs[-1]["phases"].keys())
     sums = torch.tensor([sum(r["build_dev_ms"] for r in recs), sum(r["query_dev_ms"] for r in recs),
@@ -421,15 +455,18 @@ def run_ours_global(args, world, rank, local):
         xbytes = [int(x[1].item()) for x in ms_all]
         xms = phases.get("exchange", 0.0)
         result["config"]["sharding"] = ("one global index over the N concatenated partitions: sample sort, splitters from "
-                                        "the all-reduced 65536-bin key histogram, NCCL all-to-all of (key, pos) records, "
+                                        "the all-reduced 65536-bin key histogram, one exchange of (key, pos) records, "
                                         "128-record halos for the bucket finish, " +
-                                        ("finish kernel stores every placed position into all ranks' arrays (peer stores over NVLink)"
+                                        ("each shard finished in chunks straight into the final array while the previous chunk is copied "
+                                         "into every peer's array over NVLink (CUDA IPC, one stream per peer)"
                                          if args.replicate == "fused" else "NCCL all-gather of the slices"))
         result["config"]["exchange"] = ("split kernel stores records straight into the destination GPU's sort buffers "
                                         "(CUDA IPC peer stores over NVLink)" if args.exchange == "p2p"
                                         else "split into send buffers + NCCL all_to_all_single")
         result["config"]["n_chars_total"] = n
         result["timing"] = "wall clock between barrier + cudaDeviceSynchronize pairs, max over ranks (the build is host-driven across collectives)"
+        if verify is not None:
+            result["verify"] = verify
         result["multi_gpu"] = {"phases_ms_max_over_ranks": phases, "shard_records": shard_sizes,
                                "imbalance": round(max(shard_sizes) * world / max(sum(shard_sizes), 1), 4),
                                "exchange_bytes_sent_per_rank": xbytes,
@@ -637,8 +674,14 @@ def run_reference(args):
 
 def main():
     args = parse_args()
+    if args.chars_per_gpu:
+        OVERRIDE["chars"] = args.chars_per_gpu
+    if args.queries_per_gpu:
+        OVERRIDE["queries"] = args.queries_per_gpu
     res = run_reference(args) if args.impl == "reference" else run_ours(args)
     if res is not None:
+        if OVERRIDE and "config" in res:
+            res["config"]["workload"] += f" -- SCALED RUN: {OVERRIDE} per GPU instead of the named sizes"
         print(json.dumps(res), flush=True)
 
 
