@@ -361,6 +361,10 @@ def run_ours_global(args, world, rank, local):
         b, phases = SH.build_distributed(h_text, L, local, lowercase=lower, timing=True,
                                          device_text=d_text if kind == "dev" else None, builder=builders[kind],
                                          exchange=args.exchange, replicate=args.replicate)
+        if builders[kind] is None:                                    # tuning experiments: key=value,... (from the 2nd build on)
+            for kv in (os.environ.get("SA_BENCH_DEBUG") or "").split(","):
+                if "=" in kv:
+                    b.idx.debug_set(kv.split("=")[0], int(kv.split("=")[1]))
         builders[kind] = b
         torch.cuda.synchronize()
         return b, (time.perf_counter() - t0) * 1e3, phases

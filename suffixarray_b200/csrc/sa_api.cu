@@ -161,6 +161,7 @@ extern "C" int sa_debug_set(sa_index* idx, const char* key, int64_t value)
     else if (!strcmp(key, "code_bits")) idx->dbg_code_bits = value;
     else if (!strcmp(key, "sort0_chars")) idx->dbg_sort0_chars = value;
     else if (!strcmp(key, "csv_scanner")) idx->dbg_csv_scanner = value;
+    else if (!strcmp(key, "replicate_memcpy")) idx->dbg_replicate_memcpy = value;
     else if (!strcmp(key, "same_process")) idx->dbg_same_process = value;
     else if (!strcmp(key, "query_kernel")) idx->dbg_query_kernel = value;
     else if (!strcmp(key, "onesweep_variant")) sa_onesweep_variant = (int)value;

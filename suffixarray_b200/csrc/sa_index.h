@@ -122,6 +122,7 @@ struct sa_index {
     int64_t dbg_force_gbits = 0;    // use at least this many group-id bits (exercises small cb)
     int64_t dbg_query_kernel = 0;   // 0: by batch size; 1: one thread per query; 2: eight lanes per query
     int64_t dbg_same_process = 0;   // sharded build: peers live in this process (raw pointers instead of IPC)
+    int64_t dbg_replicate_memcpy = 0;   // sharded finish: replicate with cudaMemcpyAsync instead of replicate_kernel
     int64_t dbg_csv_scanner = 0;    // 0: device scan, host scan for irregular files; 1: host scan; 2: device scan or fail
     int64_t dbg_sort0_chars = -1;   // -1: automatic; else at most this many characters in the first sort's keys
     int64_t dbg_code_bits = -1;     // -1: choose from the alphabet; 8: never compress; 1..7: at least this width

@@ -450,6 +450,35 @@ extern "C" int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const ui
     return rc;
 }
 
+// Push `count` u32 entries of the local final array to the same offset of every peer's array: one
+// read of local HBM, one 16-byte store per peer over NVLink (head / tail to 16-byte alignment with
+// 4-byte stores; all arrays share the alignment of the offset).
+namespace sa {
+struct ReplicaTable {
+    uint32_t* dst[15];
+    int n;
+};
+
+__global__ void __launch_bounds__(512) replicate_kernel(const uint32_t* __restrict__ src, uint64_t count, ReplicaTable t)
+{
+    const uint64_t head = min(count, (uint64_t)((16u - ((uintptr_t)src & 15u)) & 15u) / 4u);
+    const uint64_t nvec = (count - head) / 4u;
+    const uint64_t tail0 = head + nvec * 4u;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (uint64_t)gridDim.x * blockDim.x;
+    const uint4* sv = reinterpret_cast<const uint4*>(src + head);
+    for (uint64_t i = tid; i < nvec; i += nthreads) {
+        const uint4 v = __ldcs(sv + i);
+#pragma unroll 1
+        for (int g = 0; g < t.n; ++g) reinterpret_cast<uint4*>(t.dst[g] + head)[i] = v;
+    }
+    for (uint64_t i = tid; i < head + (count - tail0); i += nthreads) {
+        const uint64_t j = i < head ? i : tail0 + (i - head);
+        const uint32_t v = src[j];
+        for (int g = 0; g < t.n; ++g) t.dst[g][j] = v;
+    }
+}
+}  // namespace sa
+
 // ------------------------------------------------------------------------------ finish + replicate, overlapped
 // Instead of "finish into a local slice, all-gather the slices, copy into place", the shard is
 // finished in chunks straight into this rank's final array, and while chunk c+1 is being finished
@@ -547,11 +576,21 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
         if (upto > (uint64_t)nleft + m) upto = (uint64_t)nleft + m;
         if (upto <= copied_to) continue;
         const size_t off = (size_t)global_offset + copied_to - nleft, cnt = (size_t)(upto - copied_to);
-        for (int k = 1; k < nranks; ++k) {    // one stream per peer: the copies to different peers run side by side
-            const int g = (my_rank + k) % nranks;
-            SA_CU(cudaStreamWaitEvent(idx->copy_streams[g], idx->chunk_ev[c], 0));
-            SA_CU(cudaMemcpyAsync(peer_base[g] + off, peer_base[my_rank] + off, cnt * 4, cudaMemcpyDeviceToDevice,
-                                  idx->copy_streams[g]));
+        if (idx->dbg_replicate_memcpy) {      // copy engines instead of the store kernel (slower at 8 GPUs)
+            for (int k = 1; k < nranks; ++k) {
+                const int g = (my_rank + k) % nranks;
+                SA_CU(cudaStreamWaitEvent(idx->copy_streams[g], idx->chunk_ev[c], 0));
+                SA_CU(cudaMemcpyAsync(peer_base[g] + off, peer_base[my_rank] + off, cnt * 4, cudaMemcpyDeviceToDevice,
+                                      idx->copy_streams[g]));
+            }
+        } else if (nranks > 1) {
+            sa::ReplicaTable rt{};
+            for (int k = 1; k < nranks; ++k) rt.dst[rt.n++] = peer_base[(my_rank + k) % nranks] + off;
+            cudaStream_t cs = idx->copy_streams[(my_rank + 1) % nranks];
+            SA_CU(cudaStreamWaitEvent(cs, idx->chunk_ev[c], 0));
+            sa::replicate_kernel<<<64, 512, 0, cs>>>(peer_base[my_rank] + off, (uint64_t)cnt, rt);
+            SA_CU(cudaGetLastError());
+            idx->stats.kernel_launches += 1;
         }
         copied_to = (uint32_t)upto;
     }
