@@ -157,7 +157,7 @@ int sa_shard_sort_recv(sa_index* idx, uint64_t m);
 
 /* Finish + replicate, overlapped (no all-gather, no adopt copy): the shard is finished in chunks
  * straight into this rank's final array while the previous chunk is pushed into every peer's final
- * array over NVLink (device-to-device copies into CUDA IPC mappings on a second stream).
+ * array over NVLink (a copy kernel on a second stream storing into CUDA IPC mappings).
  * sa_shard_final_prepare exports this rank's array (handle_final: 64 bytes);
  * sa_shard_finish_bcast takes all ranks' handles (64 bytes each) and the global rank of this
  * shard's first record; after a barrier over the ranks sa_shard_mark_built makes the index
