@@ -1,0 +1,173 @@
+#!/usr/bin/env python
+"""check_wide.py -- bit-exact check of ONE global index with more than 2^31 entries (SURVEY 8 C4:
+u32 positions above 2^31, the widened bisection) on a single GPU.
+
+The reference cannot build such an index (u32 `mid = (first + last) / 2`, `int` loop indices,
+engine.c:738,796-797,884) -- it cuts the text every 2 GiB -- so there is no CPU answer to compare
+with at this size.  The expected array is derived instead from a text whose suffix array is known in
+closed form from a SMALL single-GPU build (itself parity-checked against the reference by the test
+suite):
+
+    T = '\\n' * j  +  R          j a little below 2^31, R a synthetic English text
+
+ORDER-E never refines the '\\n' bucket (engine.c:771-773): it stays in ascending position order, and
+'\\n' is the smallest byte of T, so
+
+    SA(T) = [0, 1, ..., j-1]  ++  (SA(R) + j)        (SA(R) itself starts with R's '\\n' bucket)
+
+Half of R's suffixes sit at positions >= 2^31.  The index is built by the sharded pipeline (the only
+path that takes n > 2^31: two emulated ranks in one process, fused split + scatter, fused finish +
+replicate), queried, and compared entry by entry; ranges must equal the ranges of the small index
+shifted by j, record ids are shifted by j as well (every '\\n' of the prefix is an empty record).
+
+    python scripts/check_wide.py [--r-chars 64000000] [--queries 20000] [--out gpurun_out/wide.json]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def run(r_chars: int, prefix: int = 0, n_queries: int = 20_000, world: int = 2, L: int = 32) -> dict:
+    import torch
+    from suffixarray_b200 import _lib as S
+    from suffixarray_b200 import sharded as SH
+    from suffixarray_b200 import workloads as W
+
+    K = 1000
+    dev = 0
+    R = W.english_documents(r_chars, seed=4001)
+    r = int(R.size)
+    j = prefix or (((1 << 31) - r // 2) & ~15)
+    n = j + r
+    assert n < (1 << 32) - 2048
+    qbytes, qoff = W.substring_queries(R, n_queries, seed=4002)
+    queries = W.unpack_queries(qbytes, qoff)
+    report = {"n": n, "prefix_newlines": j, "r_chars": r, "positions_above_2^31": int(max(0, n - (1 << 31))),
+              "world": world, "max_suffix_length": L}
+
+    # ---- the small index: SA(R), ranges and record ids of the query batch
+    small = S.Index(L, device=dev)
+    small.build_text(R)
+    sa_r = small.sa().astype(np.int64)
+    s_r, e_r, off_r = small.query_ranges(queries, k=K)
+    small.close()
+    assert R[sa_r[0]] == 10, "R's smallest byte must be '\\n'"
+
+    # ---- the wide index, through the sharded pipeline (emulated ranks, one process)
+    T = np.empty(n, dtype=np.uint8)
+    T[:j] = 10
+    T[j:] = R
+    t0 = time.perf_counter()
+    ranks = [SH.ShardBuilder(T, L, g, world, dev) for g in range(world)]
+    hist = sum(b.pack().to(torch.int64) for b in ranks)
+    hist_np = hist.cpu().numpy()
+    for b in ranks:
+        b.idx.debug_set("same_process", 1)
+    counts = np.stack([b.count(hist_np) for b in ranks])
+    handles = np.stack([b.recv_prepare(int(counts[:, d].sum())) for d, b in enumerate(ranks)])
+    for b in ranks:
+        b.scatter_p2p(handles, counts)
+    torch.cuda.synchronize()
+    del hist
+    torch.cuda.empty_cache()                       # the packed records have been delivered
+    for b in ranks:
+        b.sort_recv()
+    edges = [SH._array_to_edges(SH._edges_to_array(b.edges())) for b in ranks]
+    fh = np.stack([b.final_prepare() for b in ranks])
+    for b in ranks:
+        b.finish_bcast(edges, fh)
+    for b in ranks:
+        b.mark_built()
+    torch.cuda.synchronize()
+    report["build_wall_s"] = round(time.perf_counter() - t0, 2)
+    report["shard_records"] = [int(b.m) for b in ranks]
+
+    # ---- entry by entry, every replica
+    ok_all = True
+    for g, b in enumerate(ranks):
+        got = b.idx.sa()
+        assert got.size == n
+        head_ok = True
+        CH = 1 << 26
+        for a in range(0, j, CH):
+            z = min(j, a + CH)
+            if not np.array_equal(got[a:z], np.arange(a, z, dtype=np.uint32)):
+                head_ok = False
+                break
+        tail_ok = bool(np.array_equal(got[j:].astype(np.int64), sa_r + j))
+        report[f"replica{g}_prefix_bucket_equal"] = head_ok
+        report[f"replica{g}_text_part_equal"] = tail_ok
+        if g == 0:
+            report["max_position"] = int(got[j:].max())
+        ok_all = ok_all and head_ok and tail_ok
+        del got
+
+    # ---- queries against the wide index (bisection over 2^31 < n < 2^32 ranks)
+    wide = ranks[-1].idx
+    s_w, e_w, off_w = wide.query_ranges(queries, k=K)
+    pos_w, doc_w = wide.query_hits(int(off_w[-1]))
+    # The probe sequence depends on n, and ORDER-E is only sorted as far as the 17-byte windows of its
+    # <= 32 buckets reach: for queries of at most 17 bytes the compare is monotone over the ranks, so
+    # both indexes MUST return the same range (shifted by j); longer queries may legitimately land on
+    # a different boundary inside a run of suffixes that agree in their first 17+ bytes -- counted,
+    # and every returned hit is checked against the text instead.
+    shift = lambda a: np.where(a == S.UINT32_MAX, np.int64(-1), a.astype(np.int64) + j)   # noqa: E731
+    same = (shift(s_r) == np.where(s_w == S.UINT32_MAX, np.int64(-1), s_w.astype(np.int64))) & \
+           (shift(e_r) == np.where(e_w == S.UINT32_MAX, np.int64(-1), e_w.astype(np.int64)))
+    lens = (qoff[1:] - qoff[:-1]).astype(np.int64)
+    short = lens <= 17
+    short_equal = bool(same[short].all())
+    long_diff = int((~same[~short]).sum())
+    # hits: position must carry the query's first min(len, L) bytes; record id = '\n' bytes in front
+    nl_r = np.flatnonzero(R == 10).astype(np.int64)
+    doc_want = j + np.searchsorted(nl_r, pos_w.astype(np.int64) - j, side="left")
+    docs_ok = bool(np.array_equal(doc_w.astype(np.int64), doc_want))
+    hits_valid = True
+    for i in range(0, len(queries), max(1, len(queries) // 2000)):
+        q = queries[i][:L]
+        for p in pos_w[int(off_w[i]):int(off_w[i + 1])][:50].tolist():
+            if T[p:p + len(q)].tobytes() != q:
+                hits_valid = False
+    identical = same
+    cnt_same = bool(np.array_equal((off_w[1:] - off_w[:-1])[identical], (off_r[1:] - off_r[:-1])[identical]))
+    report.update({"queries": len(queries), "queries_found": int((s_w != S.UINT32_MAX).sum()),
+                   "short_queries": int(short.sum()), "short_query_ranges_equal_shifted": short_equal,
+                   "long_query_ranges_differing": long_diff, "hits": int(off_w[-1]), "hits_carry_the_query": hits_valid,
+                   "record_ids_equal_newlines_in_front": docs_ok, "hit_counts_equal_where_ranges_equal": cnt_same})
+    ok_all = ok_all and short_equal and docs_ok and hits_valid and cnt_same and long_diff <= len(queries) // 100
+    report["ok"] = bool(ok_all)
+    for b in ranks:
+        b.close()
+    return report
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--r-chars", type=int, default=64_000_000)
+    ap.add_argument("--prefix", type=int, default=0, help="'\\n' bytes in front (default: 2^31 - r_chars / 2)")
+    ap.add_argument("--queries", type=int, default=20_000)
+    ap.add_argument("--world", type=int, default=2)
+    ap.add_argument("--max-suffix-length", type=int, default=32)
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    report = run(args.r_chars, args.prefix, args.queries, args.world, args.max_suffix_length)
+    line = json.dumps(report)
+    print(line, flush=True)
+    if args.out:
+        with open(args.out, "w") as f:
+            f.write(line + "\n")
+    return 0 if report["ok"] else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -62,3 +62,20 @@ def test_emulated_ranks_match_oracle(world, exchange, replicate):
             assert np.array_equal(s, ws) and np.array_equal(e, we)
         for r in ranks:
             r.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3])
+def test_wide_check_at_small_scale(world):
+    """scripts/check_wide.py (the n > 2^31 check: '\\n' prefix + text, closed-form expected array,
+    shifted ranges and record ids) run with a short prefix, so the script itself is covered by the
+    ordinary GPU tier; the full-size run is `python scripts/check_wide.py` (about 135 GB of HBM)."""
+    import importlib.util
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts", "check_wide.py")
+    spec = importlib.util.spec_from_file_location("check_wide", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    rep = mod.run(250_000, prefix=70_001, n_queries=3000, world=world)
+    assert rep["ok"], rep
+    assert rep["replica0_prefix_bucket_equal"] and rep["replica0_text_part_equal"]

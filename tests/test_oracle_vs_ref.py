@@ -99,3 +99,18 @@ def test_known_answer_banana():
     assert sa.tolist() == [6, 13, 5, 11, 3, 1, 8, 0, 7, 10, 12, 4, 2, 9]
     s, e = O.oracle_query(t, sa, 32, [b"ana", b"ban"])
     assert (s.tolist(), e.tolist()) == ([3, 7], [5, 8])
+
+
+def test_newline_prefix_closed_form():
+    """scripts/check_wide.py derives the expected array of an index with more than 2^31 entries from
+    SA('\\n' * j + R) = [0 .. j-1] ++ (SA(R) + j): the '\\n' bucket is never refined (engine.c:771-773).
+    Checked here at small sizes against the oracle and, when built, the unmodified reference."""
+    R = W.english_documents(60_000, seed=4001)
+    sa_r = O.oracle_build(R, 32).astype(np.int64)
+    assert R[sa_r[0]] == 10
+    for j in (1, 16, 33, 5000):
+        T = np.concatenate([np.full(j, 10, np.uint8), R])
+        want = np.concatenate([np.arange(j, dtype=np.int64), sa_r + j])
+        assert np.array_equal(O.oracle_build(T, 32).astype(np.int64), want), j
+        if O.have_ref():
+            assert np.array_equal(O.ref_build(T, 32).astype(np.int64), want), j
