@@ -88,6 +88,15 @@ int sa_build_text_device(sa_index* idx, const uint8_t* d_text, uint64_t n, uint3
  * Single partition (file < 2 GiB), as the reference handles one partition per 2 GiB. */
 int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags);
 
+/* Several columns of one file, one index per column (idxs[c] indexes columns[c]; distinct handles on
+ * one device).  The reference's entry already takes `char** search_cols, uint32_t num_search_cols`
+ * (engine.h:209-215) but indexes search_cols[0] only (engine.c:1476; suffix_array.pyx:197 "TODO:
+ * Allow multiple columns").  The file is read, uploaded and analysed once (quote parity, delimiter
+ * counts, row table); each column then costs its emit pass, its build and its remap.
+ * sa_build_csv(idx, path, column, flags) == sa_build_csv_columns(&idx, &column, 1, path, flags). */
+int sa_build_csv_columns(sa_index* const* idxs, const char* const* columns, uint32_t ncols, const char* csv_path,
+                         uint32_t flags);
+
 /* Accessors.  sa_copy_sa_u32 returns what SuffixArray_struct.suffix_array holds after the
  * build (text positions; FILE OFFSETS after sa_build_csv, engine.c:647-651). */
 uint64_t sa_size(const sa_index* idx);
@@ -108,10 +117,14 @@ int sa_get_stats(const sa_index* idx, sa_stats* out);
 int sa_query_ranges(sa_index* idx, const uint8_t* qbytes, const uint64_t* qoff, uint64_t nq,
                     uint32_t k, uint32_t* start, uint32_t* end, uint64_t* hit_off);
 
-/* Hits of the last sa_query_ranges call, in rank order, duplicates kept (engine.c:1187):
- * hit_pos = SA[rank] (text position), hit_doc = record index = number of '\n' before it
- * (the record engine.c:1189-1191 scans back to).  Replaces the hit loop of
- * get_matching_records / get_matching_records_file (engine.c:1185-1211, :1356-1388). */
+/* Hits of the last sa_query_ranges call, in rank order, duplicates kept (engine.c:1187).
+ * Text index: hit_pos = SA[rank] (text position), hit_doc = record index = number of '\n' before it
+ * (the record engine.c:1189-1191 scans back to).  CSV index: hit_pos = SA[rank] = offset in the FILE
+ * (engine.c:647-651), hit_doc = row of the file that holds that offset, counting record ends ('\n'
+ * outside quotes) in front of it -- header line = row 0 -- i.e. the record the reference seeks from
+ * the offset (engine.c:1217-1323); cells with raw newlines inside quotes and ragged rows keep their
+ * file row.  Replaces the hit loop of get_matching_records / get_matching_records_file
+ * (engine.c:1185-1211, :1356-1388). */
 int sa_query_hits(sa_index* idx, uint32_t* hit_pos, uint32_t* hit_doc, uint64_t cap);
 
 /* Device-resident variants for callers that keep batches in HBM (bench `value` path). */

@@ -25,7 +25,7 @@ UINT32_MAX = 0xFFFFFFFF
 # every symbol include/sa_cuda.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "sa_last_error", "sa_abi_version", "sa_create", "sa_destroy", "sa_build_text", "sa_build_text_device",
-    "sa_build_csv", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
+    "sa_build_csv", "sa_build_csv_columns", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
     "sa_copy_quoted_bits", "sa_copy_text", "sa_device_sa", "sa_get_stats", "sa_query_ranges", "sa_query_hits",
     "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
     "sa_shard_begin", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
@@ -86,6 +86,7 @@ def lib():
     L.sa_build_text.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
     L.sa_build_text_device.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
     L.sa_build_csv.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint32]
+    L.sa_build_csv_columns.argtypes = [C.POINTER(_vp), C.POINTER(C.c_char_p), C.c_uint32, C.c_char_p, C.c_uint32]
     L.sa_size.argtypes = [_vp]
     L.sa_size.restype = C.c_uint64
     L.sa_num_docs.argtypes = [_vp]
@@ -162,6 +163,15 @@ class Index:
 
     def build_csv(self, path: str, column: str, timing: bool = False):
         check(lib().sa_build_csv(self._h, path.encode(), column.encode(), SA_FLAG_TIMING if timing else 0))
+
+    @staticmethod
+    def build_csv_columns(indexes, path: str, columns, timing: bool = False):
+        """indexes[c] <- column columns[c] of the file: one read / upload / quote analysis for all."""
+        n = len(indexes)
+        assert n == len(columns) and n > 0
+        hs = (_vp * n)(*[ix._h for ix in indexes])
+        cs = (C.c_char_p * n)(*[c.encode() for c in columns])
+        check(lib().sa_build_csv_columns(hs, cs, n, path.encode(), SA_FLAG_TIMING if timing else 0))
 
     def save(self, path: str):
         check(lib().sa_save(self._h, path.encode()))

@@ -216,6 +216,43 @@ csv_emit_kernel(const uint8_t* __restrict__ f, uint64_t size, const uint32_t* __
     }
 }
 
+// Row table of the FILE: bit p of the mask = file byte p is a '\n' outside quotes (a record end), one
+// u16 per 16-byte group = one u64 per 64 file bytes, the layout of the text's rank structure
+// (newline_write_kernel, query.cu), so hits_kernel turns the file offset of a hit into its row index
+// -- header line = row 0 -- with two loads.  Counting rows in the FILE, not '\n' bytes in the column
+// text, keeps row ids right for cells that hold a raw newline inside quotes and for ragged rows
+// (the reference seeks the record of a hit from its file offset too, engine.c:1217-1323).
+// pass A: masks + per-tile counts
+__global__ void __launch_bounds__(CSV_THREADS)
+csv_rows_kernel(const uint8_t* __restrict__ f, uint64_t size, const uint32_t* __restrict__ tile_q,
+                uint16_t* __restrict__ rowbits16, uint32_t* __restrict__ tile_r)
+{
+    __shared__ uint32_t ws[CSV_THREADS / 32];
+    const uint64_t p = (uint64_t)blockIdx.x * CSV_TILE + threadIdx.x * 16;
+    const Bytes16 b = load16(f, p);
+    const uint32_t vm = valid_mask(p, size);
+    const uint32_t q = eq_mask(b, '"') & vm;
+    uint32_t tot;
+    const uint32_t qpre = block_excl_scan(__popc(q), ws, &tot) + tile_q[blockIdx.x];
+    const uint32_t inq_before = ((prefix_xor16(q) << 1) & 0xFFFFu) ^ ((qpre & 1u) ? 0xFFFFu : 0u);
+    const uint32_t nl = eq_mask(b, '\n') & vm & ~inq_before;
+    rowbits16[p >> 4] = (uint16_t)nl;
+    block_excl_scan(__popc(nl), ws, &tot);
+    if (threadIdx.x == 0) tile_r[blockIdx.x] = tot;
+}
+
+// pass B: rows in front of every 64-byte block (tile_r holds the exclusive per-tile counts now)
+__global__ void __launch_bounds__(CSV_THREADS)
+csv_rowrank_kernel(const uint16_t* __restrict__ rowbits16, const uint32_t* __restrict__ tile_r,
+                   uint32_t* __restrict__ rowrank)
+{
+    __shared__ uint32_t ws[CSV_THREADS / 32];
+    const uint64_t g = (uint64_t)blockIdx.x * CSV_THREADS + threadIdx.x;      // 16-byte group of the file
+    uint32_t tot;
+    const uint32_t pre = block_excl_scan(__popc((uint32_t)rowbits16[g]), ws, &tot) + tile_r[blockIdx.x];
+    if ((threadIdx.x & 3) == 0) rowrank[g >> 2] = pre;
+}
+
 }  // namespace sa
 
 uint32_t sa_csv_tiles(uint64_t size) { return (uint32_t)((size + 1 + sa::CSV_TILE - 1) / sa::CSV_TILE); }
@@ -243,5 +280,25 @@ cudaError_t sa_launch_csv_emit(bool write, const uint8_t* f, uint64_t size, cons
     else
         sa::csv_emit_kernel<false><<<sa_csv_tiles(size), sa::CSV_THREADS, 0, s>>>(f, size, tile_q, tile_d, tile_e, wanted,
                                                                                  num_columns, text, map, flags);
+    return cudaGetLastError();
+}
+
+// rowbits: sa_csv_rowbits_bytes(size) bytes, rowrank: sa_csv_rowrank_bytes(size) bytes
+uint64_t sa_csv_rowbits_bytes(uint64_t size) { return (uint64_t)sa_csv_tiles(size) * sa::CSV_THREADS * sizeof(uint16_t); }
+uint64_t sa_csv_rowrank_bytes(uint64_t size) { return (uint64_t)sa_csv_tiles(size) * (sa::CSV_THREADS / 4) * sizeof(uint32_t); }
+
+cudaError_t sa_launch_csv_rows(const uint8_t* f, uint64_t size, const uint32_t* tile_q, unsigned long long* rowbits,
+                               uint32_t* tile_r, cudaStream_t s)
+{
+    sa::csv_rows_kernel<<<sa_csv_tiles(size), sa::CSV_THREADS, 0, s>>>(f, size, tile_q, reinterpret_cast<uint16_t*>(rowbits),
+                                                                       tile_r);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_csv_rowrank(const unsigned long long* rowbits, uint64_t size, const uint32_t* tile_r, uint32_t* rowrank,
+                                  cudaStream_t s)
+{
+    sa::csv_rowrank_kernel<<<sa_csv_tiles(size), sa::CSV_THREADS, 0, s>>>(reinterpret_cast<const uint16_t*>(rowbits), tile_r,
+                                                                          rowrank);
     return cudaGetLastError();
 }

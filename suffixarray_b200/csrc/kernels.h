@@ -85,3 +85,10 @@ cudaError_t sa_launch_csv_delims(const uint8_t* f, uint64_t size, const uint32_t
 cudaError_t sa_launch_csv_emit(bool write, const uint8_t* f, uint64_t size, const uint32_t* tile_q, const uint32_t* tile_d,
                                uint32_t* tile_e, uint32_t wanted, uint32_t num_columns, uint8_t* text, uint32_t* map,
                                uint32_t* flags, cudaStream_t s);
+// row table of the file (record ends = '\n' outside quotes): bit mask + rows in front of every 64-byte block
+uint64_t sa_csv_rowbits_bytes(uint64_t size);
+uint64_t sa_csv_rowrank_bytes(uint64_t size);
+cudaError_t sa_launch_csv_rows(const uint8_t* f, uint64_t size, const uint32_t* tile_q, unsigned long long* rowbits,
+                               uint32_t* tile_r, cudaStream_t s);
+cudaError_t sa_launch_csv_rowrank(const unsigned long long* rowbits, uint64_t size, const uint32_t* tile_r, uint32_t* rowrank,
+                                  cudaStream_t s);

@@ -255,8 +255,13 @@ extern "C" int sa_query_hits(sa_index* idx, uint32_t* hit_pos, uint32_t* hit_doc
     if (hit_doc) SA_CU(idx->hitdoc.ensure((size_t)total * 4));
     {
         ScopedPhase ph(idx, &idx->stats.ms_hits);
-        SA_CU(sa_launch_hits(idx->sa_final.as<uint32_t>(), idx->qstart.as<uint32_t>(), idx->hitoff.as<uint64_t>(),
-                             (uint32_t)idx->last_nq, idx->nlbits.as<unsigned long long>(), idx->nlrank.as<uint32_t>(),
+        // text index: position in the text, record = '\n' bytes in front of it; CSV index: offset in the
+        // FILE (what the remapped array holds, engine.c:647-651), record = row of the file (header = 0)
+        const bool rows = idx->csv && idx->rowbits.p && idx->rowrank.p;
+        SA_CU(sa_launch_hits(rows ? idx->sa_file.as<uint32_t>() : idx->sa_final.as<uint32_t>(), idx->qstart.as<uint32_t>(),
+                             idx->hitoff.as<uint64_t>(), (uint32_t)idx->last_nq,
+                             rows ? idx->rowbits.as<unsigned long long>() : idx->nlbits.as<unsigned long long>(),
+                             rows ? idx->rowrank.as<uint32_t>() : idx->nlrank.as<uint32_t>(),
                              hit_pos ? idx->hitpos.as<uint32_t>() : nullptr, hit_doc ? idx->hitdoc.as<uint32_t>() : nullptr,
                              s));
         idx->stats.kernel_launches += 1;

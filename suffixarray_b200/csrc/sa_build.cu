@@ -89,7 +89,8 @@ extern "C" void sa_destroy(sa_index* idx)
                      &idx->status, &idx->small, &idx->nl_counts, &idx->codes, &idx->qbytes, &idx->qoff, &idx->qstart,
                      &idx->qend, &idx->qcounts, &idx->hitoff, &idx->blocksums, &idx->hitpos, &idx->hitdoc,
                      &idx->ext_sa, &idx->ext_lcp, &idx->ext_out, &idx->split_table, &idx->split_offsets,
-                     &idx->csv_file, &idx->csv_tq, &idx->csv_td, &idx->csv_te, &idx->nlbits, &idx->nlrank};
+                     &idx->csv_file, &idx->csv_tq, &idx->csv_td, &idx->csv_te, &idx->csv_tr, &idx->rowbits, &idx->rowrank,
+                     &idx->nlbits, &idx->nlrank};
     for (DevBuf* b : all) b->release();
     for (int i = 0; i < 16; ++i) {
         if (idx->copy_streams[i]) cudaStreamDestroy(idx->copy_streams[i]);

@@ -178,56 +178,81 @@ static int stream_file_to_device(sa_index* idx, int fd, size_t size, uint8_t* d_
     return SA_OK;
 }
 
-// Device column scan (csv_scan.cu).  *regular = false when the file needs the host state machine;
-// otherwise idx->text / map / quoted_text hold the column stream and idx->n its length.
-static int scan_column_device(sa_index* idx, int fd, size_t size, uint32_t col, uint32_t num_columns, bool* regular)
+// The file on the device (on src): upload, quote parity per tile, the row table of the file, and --
+// unless the host scanner is forced -- the delimiter counts per tile.  Shared by every column of a
+// multi-column build.
+static int csv_load_device(sa_index* src, int fd, size_t size, bool want_delims)
 {
-    cudaStream_t s = idx->stream;
-    uint32_t* sm = idx->small.as<uint32_t>();
+    cudaStream_t s = src->stream;
+    uint32_t* sm = src->small.as<uint32_t>();
     const uint32_t tiles = sa_csv_tiles(size);
     const uint64_t padded = sa_csv_padded_bytes(size);
-    SA_CU(idx->csv_file.ensure(padded));
-    SA_CU(idx->csv_tq.ensure((size_t)tiles * 4));
-    SA_CU(idx->csv_td.ensure((size_t)tiles * 4));
-    SA_CU(idx->csv_te.ensure((size_t)tiles * 4));
-    uint8_t* d_file = idx->csv_file.as<uint8_t>();
+    SA_CU(src->csv_file.ensure(padded));
+    SA_CU(src->csv_tq.ensure((size_t)tiles * 4));
+    SA_CU(src->csv_td.ensure((size_t)tiles * 4));
+    SA_CU(src->csv_te.ensure((size_t)tiles * 4));
+    SA_CU(src->csv_tr.ensure((size_t)tiles * 4));
+    SA_CU(src->rowbits.ensure(sa_csv_rowbits_bytes(size)));
+    SA_CU(src->rowrank.ensure(sa_csv_rowrank_bytes(size)));
+    uint8_t* d_file = src->csv_file.as<uint8_t>();
     const size_t tail = size & ~(size_t)15;
     SA_CU(cudaMemsetAsync(d_file + tail, 0, padded - tail, s));
     SA_CU(cudaMemsetAsync(sm + SM_CSV, 0, 8 * sizeof(uint32_t), s));
     {
-        ScopedPhase ph(idx, &idx->stats.ms_h2d);
-        int rc = stream_file_to_device(idx, fd, size, d_file);
+        ScopedPhase ph(src, &src->stats.ms_h2d);
+        int rc = stream_file_to_device(src, fd, size, d_file);
         if (rc != SA_OK) return rc;
     }
-    uint32_t *tq = idx->csv_tq.as<uint32_t>(), *td = idx->csv_td.as<uint32_t>(), *te = idx->csv_te.as<uint32_t>();
-    {
-        ScopedPhase ph(idx, &idx->stats.ms_csv_scan);
-        SA_CU(sa_launch_csv_quotes(d_file, size, tq, sm + SM_CSV, s));
-        SA_CU(sa_launch_scan_u32(tq, tiles, sm + SM_CSV + 1, s));
+    uint32_t *tq = src->csv_tq.as<uint32_t>(), *td = src->csv_td.as<uint32_t>(), *tr = src->csv_tr.as<uint32_t>();
+    ScopedPhase ph(src, &src->stats.ms_csv_scan);
+    SA_CU(sa_launch_csv_quotes(d_file, size, tq, sm + SM_CSV, s));
+    SA_CU(sa_launch_scan_u32(tq, tiles, sm + SM_CSV + 1, s));
+    SA_CU(sa_launch_csv_rows(d_file, size, tq, src->rowbits.as<unsigned long long>(), tr, s));
+    SA_CU(sa_launch_scan_u32(tr, tiles, sm + SM_CSV + 4, s));
+    SA_CU(sa_launch_csv_rowrank(src->rowbits.as<unsigned long long>(), size, tr, src->rowrank.as<uint32_t>(), s));
+    src->stats.kernel_launches += 5;
+    if (want_delims) {
         SA_CU(sa_launch_csv_delims(d_file, size, tq, td, s));
         SA_CU(sa_launch_scan_u32(td, tiles, sm + SM_CSV + 2, s));
+        src->stats.kernel_launches += 2;
+    }
+    return SA_OK;
+}
+
+// Device column scan (csv_scan.cu) of column `col` of the file held by src into dst's text / map.
+// *regular = false when the file needs the host state machine; otherwise dst->n is the stream length.
+static int scan_column_device(sa_index* src, sa_index* dst, size_t size, uint32_t col, uint32_t num_columns, bool* regular)
+{
+    cudaStream_t s = src->stream;
+    uint32_t* sm = src->small.as<uint32_t>();
+    const uint32_t tiles = sa_csv_tiles(size);
+    const uint8_t* d_file = src->csv_file.as<uint8_t>();
+    uint32_t *tq = src->csv_tq.as<uint32_t>(), *td = src->csv_td.as<uint32_t>(), *te = src->csv_te.as<uint32_t>();
+    {
+        ScopedPhase ph(src, &dst->stats.ms_csv_scan);
         SA_CU(sa_launch_csv_emit(false, d_file, size, tq, td, te, col, num_columns, nullptr, nullptr, sm + SM_CSV, s));
         SA_CU(sa_launch_scan_u32(te, tiles, sm + SM_CSV + 3, s));
-        idx->stats.kernel_launches += 6;
+        dst->stats.kernel_launches += 2;
     }
-    SA_CU(cudaMemcpyAsync(idx->h_small, sm + SM_CSV, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    SA_CU(cudaMemcpyAsync(src->h_small, sm + SM_CSV, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     SA_CU(cudaStreamSynchronize(s));
-    const uint32_t irregular = idx->h_small[0];
-    const uint64_t n = idx->h_small[3];
+    const uint32_t irregular = src->h_small[0];
+    const uint64_t n = src->h_small[3];
     *regular = irregular == 0;
     if (irregular) return SA_OK;
     if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
-    idx->n = n;
+    dst->n = n;
     const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
-    SA_CU(idx->text.ensure(bytes));
-    SA_CU(idx->map.ensure((size_t)n * 4 + 4));
-    SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + ((size_t)n & ~(size_t)15), 0, bytes - ((size_t)n & ~(size_t)15), s));
+    SA_CU(dst->text.ensure(bytes));
+    SA_CU(dst->map.ensure((size_t)n * 4 + 4));
+    SA_CU(cudaMemsetAsync(dst->text.as<uint8_t>() + ((size_t)n & ~(size_t)15), 0, bytes - ((size_t)n & ~(size_t)15), s));
     {
-        ScopedPhase ph(idx, &idx->stats.ms_csv_scan);
-        SA_CU(sa_launch_csv_emit(true, d_file, size, tq, td, te, col, num_columns, idx->text.as<uint8_t>(),
-                                 idx->map.as<uint32_t>(), sm + SM_CSV, s));
-        idx->stats.kernel_launches += 1;
+        ScopedPhase ph(src, &dst->stats.ms_csv_scan);
+        SA_CU(sa_launch_csv_emit(true, d_file, size, tq, td, te, col, num_columns, dst->text.as<uint8_t>(),
+                                 dst->map.as<uint32_t>(), sm + SM_CSV, s));
+        dst->stats.kernel_launches += 1;
     }
+    SA_CU(cudaStreamSynchronize(s));          // dst builds on its own stream
     return SA_OK;
 }
 
@@ -260,11 +285,30 @@ static int scan_column_host(sa_index* idx, const Mapped& m, uint32_t col, uint32
     return SA_OK;
 }
 
-extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags)
+// Several columns of ONE file, one index per column (the reference's entry takes
+// `char** search_cols, uint32_t num_search_cols` but only ever indexes search_cols[0], engine.c:1476,
+// suffix_array.pyx:197 "TODO: Allow multiple columns").  The file is read, uploaded and analysed once
+// (quote parity, delimiter counts, row table) on idxs[0]; every column then costs one emit pass, its
+// build and its remap.
+extern "C" int sa_build_csv_columns(sa_index* const* idxs, const char* const* columns, uint32_t ncols, const char* csv_path,
+                                    uint32_t flags)
 {
-    if (!idx || !csv_path || !column) { sa_set_error("sa_build_csv: NULL argument"); return SA_ERR_INVALID; }
-    std::lock_guard<std::mutex> lock(idx->mu);
-    SA_CU(cudaSetDevice(idx->device));
+    if (!idxs || !columns || !csv_path || ncols == 0) { sa_set_error("sa_build_csv_columns: NULL argument"); return SA_ERR_INVALID; }
+    if (ncols > 64) { sa_set_error("sa_build_csv_columns: at most 64 columns per call"); return SA_ERR_LIMIT; }
+    std::vector<sa_index*> order(idxs, idxs + ncols);
+    for (uint32_t c = 0; c < ncols; ++c) {
+        if (!idxs[c] || !columns[c]) { sa_set_error("sa_build_csv_columns: NULL entry %u", c); return SA_ERR_INVALID; }
+        if (idxs[c]->device != idxs[0]->device) { sa_set_error("sa_build_csv_columns: all indexes must live on one device"); return SA_ERR_INVALID; }
+    }
+    std::sort(order.begin(), order.end());
+    if (std::adjacent_find(order.begin(), order.end()) != order.end()) {
+        sa_set_error("sa_build_csv_columns: one index per column (a handle was passed twice)");
+        return SA_ERR_INVALID;
+    }
+    std::vector<std::unique_lock<std::mutex>> locks;      // address order: concurrent callers cannot deadlock
+    for (sa_index* p : order) locks.emplace_back(p->mu);
+    sa_index* src = idxs[0];
+    SA_CU(cudaSetDevice(src->device));
     Mapped m;
     m.fd = open(csv_path, O_RDONLY);
     if (m.fd < 0) { sa_set_error("cannot open %s", csv_path); return SA_ERR_IO; }
@@ -282,49 +326,80 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
     madvise(mp, m.size, MADV_SEQUENTIAL);
 
     const std::vector<std::string> cells = header_cells(m.p, m.size);
-    int col = -1;
-    for (size_t i = 0; i < cells.size(); ++i)
-        if (cells[i] == column) { col = (int)i; break; }     // strcmp match, engine.c:1424-1435
-    if (col < 0) { sa_set_error("column '%s' not found in %s", column, csv_path); return SA_ERR_IO; }
-
-    idx->timing = (flags & SA_FLAG_TIMING) != 0;
-    idx->built = false;
-    idx->stats.ms_h2d = 0.f;
-    idx->stats.ms_csv_scan = 0.f;
-    idx->stats.csv_host_scan = 0;
-    bool regular = false;
-    if (idx->dbg_csv_scanner != 1) {
-        int rc = scan_column_device(idx, m.fd, m.size, (uint32_t)col, (uint32_t)cells.size(), &regular);
-        if (rc != SA_OK) return rc;
-        if (!regular && idx->dbg_csv_scanner == 2) {
-            sa_set_error("%s is not a regular CSV file for the device scanner (flags 0x%x)", csv_path, idx->h_small[0]);
-            return SA_ERR_IO;
-        }
+    std::vector<uint32_t> col_of(ncols);
+    for (uint32_t c = 0; c < ncols; ++c) {
+        int col = -1;
+        for (size_t i = 0; i < cells.size(); ++i)
+            if (cells[i] == columns[c]) { col = (int)i; break; }     // strcmp match, engine.c:1424-1435
+        if (col < 0) { sa_set_error("column '%s' not found in %s", columns[c], csv_path); return SA_ERR_IO; }
+        col_of[c] = (uint32_t)col;
     }
-    if (!regular) {
-        int rc = scan_column_host(idx, m, (uint32_t)col, (uint32_t)cells.size());
-        if (rc != SA_OK) return rc;
+    for (uint32_t c = 0; c < ncols; ++c) {
+        sa_index* idx = idxs[c];
+        idx->timing = (flags & SA_FLAG_TIMING) != 0;
+        idx->built = false;
+        idx->have_ranges = false;
+        idx->stats.ms_h2d = 0.f;
+        idx->stats.ms_csv_scan = 0.f;
+        idx->stats.csv_host_scan = 0;
+        idx->stats.kernel_launches = 0;
     }
-    const uint64_t n = idx->n;
-    cudaStream_t s = idx->stream;
-    // the scan already lower-cased the column (tolower, engine.c:559,581,593)
-    int rc = sa_build_resident(idx, flags & ~SA_FLAG_LOWERCASE);
+    const int64_t scanner = src->dbg_csv_scanner;
+    int rc = csv_load_device(src, m.fd, m.size, scanner != 1);
     if (rc != SA_OK) return rc;
-    idx->built = false;
-    idx->stats.csv_host_scan = regular ? 0u : 1u;
-    SA_CU(idx->sa_file.ensure((size_t)n * 4));
-    SA_CU(idx->qbits.ensure((((size_t)n + 31) / 32) * 4 + 4));
-    {
-        ScopedPhase ph(idx, &idx->stats.ms_remap);
-        SA_CU(sa_launch_remap(idx->sa_final.as<uint32_t>(), (uint32_t)n, idx->map.as<uint32_t>(),
-                              regular ? nullptr : idx->quoted_text.as<uint8_t>(), idx->sa_file.as<uint32_t>(),
-                              idx->qbits.as<uint32_t>(), s));
-        idx->stats.kernel_launches += 1;
+    bool file_regular = scanner != 1;
+    for (uint32_t c = 0; c < ncols; ++c) {
+        sa_index* idx = idxs[c];
+        bool regular = false;
+        if (file_regular) {
+            rc = scan_column_device(src, idx, m.size, col_of[c], (uint32_t)cells.size(), &regular);
+            if (rc != SA_OK) return rc;
+            if (!regular && scanner == 2) {
+                sa_set_error("%s is not a regular CSV file for the device scanner (flags 0x%x)", csv_path, src->h_small[0]);
+                return SA_ERR_IO;
+            }
+            file_regular = regular;               // irregular quoting is a property of the file, not of the column
+        }
+        if (!regular) {
+            rc = scan_column_host(idx, m, col_of[c], (uint32_t)cells.size());
+            if (rc != SA_OK) return rc;
+        }
+        const uint64_t n = idx->n;
+        cudaStream_t s = idx->stream;
+        const uint64_t scan_launches = idx->stats.kernel_launches;   // sa_build_resident clears the stats
+        // the scan already lower-cased the column (tolower, engine.c:559,581,593)
+        rc = sa_build_resident(idx, flags & ~SA_FLAG_LOWERCASE);
+        if (rc != SA_OK) return rc;
+        idx->stats.kernel_launches += scan_launches;
+        idx->built = false;
+        idx->stats.csv_host_scan = regular ? 0u : 1u;
+        SA_CU(idx->sa_file.ensure((size_t)n * 4));
+        SA_CU(idx->qbits.ensure((((size_t)n + 31) / 32) * 4 + 4));
+        {
+            ScopedPhase ph(idx, &idx->stats.ms_remap);
+            SA_CU(sa_launch_remap(idx->sa_final.as<uint32_t>(), (uint32_t)n, idx->map.as<uint32_t>(),
+                                  regular ? nullptr : idx->quoted_text.as<uint8_t>(), idx->sa_file.as<uint32_t>(),
+                                  idx->qbits.as<uint32_t>(), s));
+            idx->stats.kernel_launches += 1;
+        }
+        if (idx != src) {                          // every index answers hits with row ids: its own copy of the row table
+            SA_CU(idx->rowbits.ensure(sa_csv_rowbits_bytes(m.size)));
+            SA_CU(idx->rowrank.ensure(sa_csv_rowrank_bytes(m.size)));
+            SA_CU(cudaMemcpyAsync(idx->rowbits.p, src->rowbits.p, sa_csv_rowbits_bytes(m.size), cudaMemcpyDeviceToDevice, s));
+            SA_CU(cudaMemcpyAsync(idx->rowrank.p, src->rowrank.p, sa_csv_rowrank_bytes(m.size), cudaMemcpyDeviceToDevice, s));
+        }
+        SA_CU(cudaStreamSynchronize(s));
+        sa_time_collect(idx);
+        if (idx != src) sa_time_collect(src);      // scan phases of this column were recorded on src's stream
+        idx->csv = true;
+        idx->csv_file_bytes = m.size;
+        idx->built = true;
     }
-    SA_CU(cudaStreamSynchronize(s));
-    sa_time_collect(idx);
-    idx->csv = true;
-    idx->csv_file_bytes = m.size;
-    idx->built = true;
     return SA_OK;
+}
+
+extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags)
+{
+    if (!idx || !csv_path || !column) { sa_set_error("sa_build_csv: NULL argument"); return SA_ERR_INVALID; }
+    return sa_build_csv_columns(&idx, &column, 1, csv_path, flags);
 }

@@ -75,7 +75,8 @@ struct sa_index {
     DevBuf sa_file;     // CSV: u32[n] file offsets (engine.c:647-651)
     DevBuf qbits;       // CSV: quoted bit per rank
     DevBuf map, quoted_text;   // CSV feeder outputs on the device
-    DevBuf csv_file, csv_tq, csv_td, csv_te;   // device copy of the file + per-tile counts (csv_scan.cu)
+    DevBuf csv_file, csv_tq, csv_td, csv_te, csv_tr;   // device copy of the file + per-tile counts (csv_scan.cu)
+    DevBuf rowbits, rowrank;   // CSV: rank structure over the record ends of the FILE (hits -> row index)
     void* h_ring[2] = {nullptr, nullptr};      // pinned staging ring of the file reader
     cudaEvent_t ring_ev[2] = {nullptr, nullptr};
     size_t ring_bytes = 0;

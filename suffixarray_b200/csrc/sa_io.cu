@@ -3,7 +3,7 @@
 // The reference only sketches persistence (write_suffix_array / read_into_suffix_array_file,
 // engine.c:1098-1165, unreachable from Python; TODO.md:1,4).  Two things are provided here:
 //   * sa_save / sa_load: one self-describing container with everything a query needs (text,
-//     ORDER-E positions, and for CSV indexes the file offsets + quoted bits), so a loaded index
+//     ORDER-E positions, and for CSV indexes the file offsets, quoted bits and the file's row table), so a loaded index
 //     answers queries without re-sorting; the record table is rebuilt on the device at load time.
 //   * sa_export_reference_files: the reference's own layout, for tools written against it:
 //       <sa file>      u64 global_byte_start_idx, u64 global_byte_end_idx, u32 max_suffix_length,
@@ -73,7 +73,7 @@ extern "C" int sa_save(sa_index* idx, const char* path)
     if (!out.f) { sa_set_error("cannot create %s", path); return SA_ERR_IO; }
     FileHeader h{};
     memcpy(h.magic, MAGIC, 8);
-    h.version = 1;
+    h.version = 2;
     h.max_suffix_length = idx->L;
     h.n = idx->n;
     h.flags = idx->csv ? 1u : 0u;
@@ -85,6 +85,9 @@ extern "C" int sa_save(sa_index* idx, const char* path)
     if (rc == SA_OK) rc = write_device(idx, out.f, idx->sa_final.p, n * 4, buf);
     if (rc == SA_OK && idx->csv) rc = write_device(idx, out.f, idx->sa_file.p, n * 4, buf);
     if (rc == SA_OK && idx->csv) rc = write_device(idx, out.f, idx->qbits.p, ((n + 31) / 32) * 4, buf);
+    // the row table of the CSV file (hits -> row index): restored as is, the file itself is not needed to load
+    if (rc == SA_OK && idx->csv) rc = write_device(idx, out.f, idx->rowbits.p, sa_csv_rowbits_bytes(idx->csv_file_bytes), buf);
+    if (rc == SA_OK && idx->csv) rc = write_device(idx, out.f, idx->rowrank.p, sa_csv_rowrank_bytes(idx->csv_file_bytes), buf);
     return rc;
 }
 
@@ -97,7 +100,7 @@ extern "C" int sa_load(sa_index* idx, const char* path)
     in.f = fopen(path, "rb");
     if (!in.f) { sa_set_error("cannot open %s", path); return SA_ERR_IO; }
     FileHeader h{};
-    if (fread(&h, sizeof h, 1, in.f) != 1 || memcmp(h.magic, MAGIC, 8) != 0 || h.version != 1) {
+    if (fread(&h, sizeof h, 1, in.f) != 1 || memcmp(h.magic, MAGIC, 8) != 0 || h.version != 2) {
         sa_set_error("%s is not a libsa_cuda index file", path);
         return SA_ERR_IO;
     }
@@ -131,6 +134,11 @@ extern "C" int sa_load(sa_index* idx, const char* path)
         if (rc == SA_OK) rc = read_device(idx, in.f, idx->qbits.p, ((n + 31) / 32) * 4, buf);
         if (rc != SA_OK) return rc;
         idx->csv_file_bytes = h.csv_file_bytes;
+        SA_CU(idx->rowbits.ensure(sa_csv_rowbits_bytes(h.csv_file_bytes)));
+        SA_CU(idx->rowrank.ensure(sa_csv_rowrank_bytes(h.csv_file_bytes)));
+        rc = read_device(idx, in.f, idx->rowbits.p, sa_csv_rowbits_bytes(h.csv_file_bytes), buf);
+        if (rc == SA_OK) rc = read_device(idx, in.f, idx->rowrank.p, sa_csv_rowrank_bytes(h.csv_file_bytes), buf);
+        if (rc != SA_OK) return rc;
     }
     if (n) {
         rc = sa_stage_prepare(idx, 0);          // record table (+ alphabet codes, unused by queries)

@@ -10,6 +10,10 @@ arithmetic of its own, so the mirror is plain Python over the C ABI -- INTEGRATI
 * ``SuffixArray(csv_file=f, search_column=c, max_suffix_length=32)``     README.md:40-44
 * ``construct_truncated_suffix_array_documents(documents)``              pyx:129-180
 * ``construct_truncated_suffix_array_from_csv(filename, search_column)`` pyx:183-207
+  (``search_column`` may also be a list of column names -- the reference's C entry takes
+  ``char** search_cols`` but indexes the first only, engine.c:1476, pyx:197 "TODO: Allow multiple
+  columns": one index per column, built from ONE read of the file; queries walk the columns in
+  the order given until k rows are found, or search one with ``column=``)
 * ``query_records(substring, k=1000)``                                   pyx:209-267
 * ``query_records_batch(substrings, k=1000)``  (new: the batched entry the GPU path wants)
 
@@ -35,7 +39,7 @@ class SuffixArray:
     PARTITION_BYTES = 1 << 31
 
     def __init__(self, max_suffix_length: int = 64, documents=None, csv_file: str | None = None,
-                 search_column: str | None = None, device: int = 0):
+                 search_column: str | list | None = None, device: int = 0):
         self.max_suffix_length = int(max_suffix_length)
         self._device = device
         self._idx = S.Index(self.max_suffix_length, device=device)
@@ -44,6 +48,8 @@ class SuffixArray:
         self._text = None            # documents: the joined, lower-cased utf-8 bytes (host copy)
         self._doc_starts = None
         self.columns = None          # csv: header cells (pyx:189-194)
+        self.search_columns = None   # csv: the indexed columns, in query order
+        self._col_idx = {}           # csv: column name -> its Index
         self._csv_path = None
         self._csv_mm = None
         self._row_starts = None
@@ -82,13 +88,25 @@ class SuffixArray:
         self._doc_starts = np.concatenate([[0], nl + 1]).astype(np.int64)
         self._mode = "documents"
 
-    def construct_truncated_suffix_array_from_csv(self, filename: str, search_column: str) -> None:
-        """pyx:183-207 -> engine.c:1454: mmap scan of one column, build, remap to file offsets."""
+    def construct_truncated_suffix_array_from_csv(self, filename: str, search_column) -> None:
+        """pyx:183-207 -> engine.c:1454: scan of the search column(s), build, remap to file offsets.
+        search_column: one name, or a list of names (one index per column, one read of the file)."""
         if not os.path.exists(filename):
             raise FileNotFoundError(filename)
         with open(filename, "r", newline="") as f:              # pyx:189-194
             self.columns = f.readline().strip().split(",")
-        self._idx.build_csv(filename, search_column)
+        cols = [search_column] if isinstance(search_column, str) else list(search_column)
+        if not cols or len(set(cols)) != len(cols):
+            raise ValueError("search_column must name one or more distinct columns")
+        for old in self._parts[1:]:
+            old.close()
+        self._parts = [self._idx] + [S.Index(self.max_suffix_length, device=self._device) for _ in cols[1:]]
+        if len(cols) == 1:
+            self._idx.build_csv(filename, cols[0])
+        else:
+            S.Index.build_csv_columns(self._parts, filename, cols)
+        self.search_columns = cols
+        self._col_idx = dict(zip(cols, self._parts))
         self._csv_path = filename
         self._open_csv(filename)
         self._mode = "csv"
@@ -109,14 +127,16 @@ class SuffixArray:
         self._row_ends = np.concatenate([nl, [data.size]]).astype(np.int64)[: starts.size]
 
     # ------------------------------------------------------------------ queries
-    def query_records(self, substring: str, k: int = 1000):
+    def query_records(self, substring: str, k: int = 1000, column: str | None = None):
         if substring == "":                                      # pyx:210-211
             return []
-        return self.query_records_batch([substring], k)[0]
+        return self.query_records_batch([substring], k, column=column)[0]
 
-    def query_records_batch(self, substrings, k: int = 1000):
+    def query_records_batch(self, substrings, k: int = 1000, column: str | None = None):
         """One list of records per query: the first min(k, matches) hits in suffix-array order,
-        duplicates kept (engine.c:1185-1211 / :1356-1388)."""
+        duplicates kept (engine.c:1185-1211 / :1356-1388).  CSV index over several columns: the
+        columns are searched in the order they were given until k rows are found (`column=` limits
+        the search to one of them)."""
         if self._mode is None:
             raise RuntimeError("no suffix array has been constructed")
         qs = [s.lower().encode("utf-8") for s in substrings]    # pyx:228
@@ -125,6 +145,24 @@ class SuffixArray:
         if not nonempty:
             return out
         sub = [qs[i] for i in nonempty]
+        if self._mode == "csv":
+            if column is not None and column not in self._col_idx:
+                raise ValueError(f"column {column!r} is not indexed (indexed: {self.search_columns})")
+            walk = [self._col_idx[column]] if column is not None else list(self._parts)
+            rows = [np.zeros(0, np.int64) for _ in sub]
+            for idx in walk:                                     # same walk as over partitions, pyx:221-247
+                need = [j for j in range(len(sub)) if rows[j].size < k]
+                if not need:
+                    break
+                kk = max(int(k) - rows[j].size for j in need)
+                _, _, off = idx.query_ranges([sub[j] for j in need], k=kk)
+                _, row = idx.query_hits(int(off[-1]))            # row of the FILE per hit (header = row 0)
+                for t, j in enumerate(need):
+                    take = row[int(off[t]):int(off[t + 1])][: int(k) - rows[j].size].astype(np.int64)
+                    rows[j] = np.concatenate([rows[j], take])
+            for j, i in enumerate(nonempty):
+                out[i] = self._materialise(rows[j])
+            return out
         start, end, off = self._idx.query_ranges(sub, k=int(k))
         pos, doc = self._idx.query_hits(int(off[-1]))
         if len(self._parts) == 1:
@@ -184,7 +222,8 @@ class SuffixArray:
         for i, idx in enumerate(self._parts):
             idx.save(path if i == 0 else f"{path}.part{i:03d}")
         meta = {"mode": self._mode, "max_suffix_length": self.max_suffix_length, "partitions": len(self._parts),
-                "partition_bytes": int(self.PARTITION_BYTES), "columns": self.columns, "csv_path": self._csv_path}
+                "partition_bytes": int(self.PARTITION_BYTES), "columns": self.columns, "csv_path": self._csv_path,
+                "search_columns": self.search_columns}
         with open(path + ".json", "w") as f:
             json.dump(meta, f)
 
@@ -208,6 +247,8 @@ class SuffixArray:
             self._doc_starts = np.concatenate([[0], nl + 1]).astype(np.int64)
         else:
             self.columns = meta["columns"]
+            self.search_columns = meta["search_columns"]
+            self._col_idx = dict(zip(self.search_columns, self._parts))
             self._csv_path = meta["csv_path"]
             self._open_csv(self._csv_path)          # rows are materialised from the CSV file itself
         return self
@@ -215,7 +256,8 @@ class SuffixArray:
     # ------------------------------------------------------------------ misc
     @property
     def suffix_array(self) -> np.ndarray:
-        """uint32 array as SuffixArray_struct.suffix_array holds it (file offsets on the CSV path)."""
+        """uint32 array as SuffixArray_struct.suffix_array holds it (file offsets on the CSV path);
+        a list of arrays when the index has several partitions / search columns."""
         return self._idx.sa() if len(self._parts) == 1 else [idx.sa() for idx in self._parts]
 
     def stats(self) -> dict:
