@@ -285,6 +285,68 @@ static int scan_column_host(sa_index* idx, const Mapped& m, uint32_t col, uint32
     return SA_OK;
 }
 
+static int open_csv(const char* csv_path, Mapped& m, std::vector<std::string>& cells)
+{
+    m.fd = open(csv_path, O_RDONLY);
+    if (m.fd < 0) { sa_set_error("cannot open %s", csv_path); return SA_ERR_IO; }
+    struct stat sb;
+    if (fstat(m.fd, &sb) != 0) { sa_set_error("fstat failed on %s", csv_path); return SA_ERR_IO; }
+    m.size = (size_t)sb.st_size;
+    if (m.size == 0) { sa_set_error("%s is empty", csv_path); return SA_ERR_IO; }
+    if (m.size >= (1ull << 31)) {
+        sa_set_error("%s: files >= 2 GiB span several reference partitions (engine.c:1437); not supported yet", csv_path);
+        return SA_ERR_LIMIT;
+    }
+    void* mp = mmap(nullptr, m.size, PROT_READ, MAP_PRIVATE, m.fd, 0);
+    if (mp == MAP_FAILED) { sa_set_error("mmap failed on %s", csv_path); return SA_ERR_IO; }
+    m.p = static_cast<const uint8_t*>(mp);
+    madvise(mp, m.size, MADV_SEQUENTIAL);
+    cells = header_cells(m.p, m.size);
+    return SA_OK;
+}
+
+static int find_column(const std::vector<std::string>& cells, const char* column, const char* csv_path, uint32_t* out)
+{
+    for (size_t i = 0; i < cells.size(); ++i)
+        if (cells[i] == column) { *out = (uint32_t)i; return SA_OK; }     // strcmp match, engine.c:1424-1435
+    sa_set_error("column '%s' not found in %s", column, csv_path);
+    return SA_ERR_IO;
+}
+
+// Column `col` of the file loaded on src -> dst's text / map (/ quoted_text on the host route).
+// *file_regular: in/out, false once the file has been found irregular (or the host scanner is forced).
+static int scan_one_column(sa_index* src, sa_index* dst, const Mapped& m, uint32_t col, uint32_t num_columns,
+                           const char* csv_path, bool* file_regular, bool* regular)
+{
+    *regular = false;
+    if (*file_regular) {
+        int rc = scan_column_device(src, dst, m.size, col, num_columns, regular);
+        if (rc != SA_OK) return rc;
+        if (!*regular && src->dbg_csv_scanner == 2) {
+            sa_set_error("%s is not a regular CSV file for the device scanner (flags 0x%x)", csv_path, src->h_small[0]);
+            return SA_ERR_IO;
+        }
+        *file_regular = *regular;                 // irregular quoting is a property of the file, not of the column
+    }
+    if (!*regular) return scan_column_host(dst, m, col, num_columns);
+    return SA_OK;
+}
+
+// The two post-build loops of the reference (engine.c:632-651) on the complete ORDER-E array of idx.
+static int csv_remap(sa_index* idx, bool regular)
+{
+    const uint64_t n = idx->n;
+    cudaStream_t s = idx->stream;
+    SA_CU(idx->sa_file.ensure((size_t)(n ? n : 1) * 4));
+    SA_CU(idx->qbits.ensure((((size_t)n + 31) / 32) * 4 + 4));
+    ScopedPhase ph(idx, &idx->stats.ms_remap);
+    SA_CU(sa_launch_remap(idx->sa_final.as<uint32_t>(), (uint32_t)n, idx->map.as<uint32_t>(),
+                          regular ? nullptr : idx->quoted_text.as<uint8_t>(), idx->sa_file.as<uint32_t>(),
+                          idx->qbits.as<uint32_t>(), s));
+    idx->stats.kernel_launches += 1;
+    return SA_OK;
+}
+
 // Several columns of ONE file, one index per column (the reference's entry takes
 // `char** search_cols, uint32_t num_search_cols` but only ever indexes search_cols[0], engine.c:1476,
 // suffix_array.pyx:197 "TODO: Allow multiple columns").  The file is read, uploaded and analysed once
@@ -310,61 +372,34 @@ extern "C" int sa_build_csv_columns(sa_index* const* idxs, const char* const* co
     sa_index* src = idxs[0];
     SA_CU(cudaSetDevice(src->device));
     Mapped m;
-    m.fd = open(csv_path, O_RDONLY);
-    if (m.fd < 0) { sa_set_error("cannot open %s", csv_path); return SA_ERR_IO; }
-    struct stat sb;
-    if (fstat(m.fd, &sb) != 0) { sa_set_error("fstat failed on %s", csv_path); return SA_ERR_IO; }
-    m.size = (size_t)sb.st_size;
-    if (m.size == 0) { sa_set_error("%s is empty", csv_path); return SA_ERR_IO; }
-    if (m.size >= (1ull << 31)) {
-        sa_set_error("%s: files >= 2 GiB span several reference partitions (engine.c:1437); not supported yet", csv_path);
-        return SA_ERR_LIMIT;
-    }
-    void* mp = mmap(nullptr, m.size, PROT_READ, MAP_PRIVATE, m.fd, 0);
-    if (mp == MAP_FAILED) { sa_set_error("mmap failed on %s", csv_path); return SA_ERR_IO; }
-    m.p = static_cast<const uint8_t*>(mp);
-    madvise(mp, m.size, MADV_SEQUENTIAL);
-
-    const std::vector<std::string> cells = header_cells(m.p, m.size);
+    std::vector<std::string> cells;
+    int rc = open_csv(csv_path, m, cells);
+    if (rc != SA_OK) return rc;
     std::vector<uint32_t> col_of(ncols);
     for (uint32_t c = 0; c < ncols; ++c) {
-        int col = -1;
-        for (size_t i = 0; i < cells.size(); ++i)
-            if (cells[i] == columns[c]) { col = (int)i; break; }     // strcmp match, engine.c:1424-1435
-        if (col < 0) { sa_set_error("column '%s' not found in %s", columns[c], csv_path); return SA_ERR_IO; }
-        col_of[c] = (uint32_t)col;
+        rc = find_column(cells, columns[c], csv_path, &col_of[c]);
+        if (rc != SA_OK) return rc;
     }
     for (uint32_t c = 0; c < ncols; ++c) {
         sa_index* idx = idxs[c];
         idx->timing = (flags & SA_FLAG_TIMING) != 0;
         idx->built = false;
         idx->have_ranges = false;
+        idx->shard_prepared = false;
+        idx->shard_csv = false;
         idx->stats.ms_h2d = 0.f;
         idx->stats.ms_csv_scan = 0.f;
         idx->stats.csv_host_scan = 0;
         idx->stats.kernel_launches = 0;
     }
-    const int64_t scanner = src->dbg_csv_scanner;
-    int rc = csv_load_device(src, m.fd, m.size, scanner != 1);
+    rc = csv_load_device(src, m.fd, m.size, src->dbg_csv_scanner != 1);
     if (rc != SA_OK) return rc;
-    bool file_regular = scanner != 1;
+    bool file_regular = src->dbg_csv_scanner != 1;
     for (uint32_t c = 0; c < ncols; ++c) {
         sa_index* idx = idxs[c];
         bool regular = false;
-        if (file_regular) {
-            rc = scan_column_device(src, idx, m.size, col_of[c], (uint32_t)cells.size(), &regular);
-            if (rc != SA_OK) return rc;
-            if (!regular && scanner == 2) {
-                sa_set_error("%s is not a regular CSV file for the device scanner (flags 0x%x)", csv_path, src->h_small[0]);
-                return SA_ERR_IO;
-            }
-            file_regular = regular;               // irregular quoting is a property of the file, not of the column
-        }
-        if (!regular) {
-            rc = scan_column_host(idx, m, col_of[c], (uint32_t)cells.size());
-            if (rc != SA_OK) return rc;
-        }
-        const uint64_t n = idx->n;
+        rc = scan_one_column(src, idx, m, col_of[c], (uint32_t)cells.size(), csv_path, &file_regular, &regular);
+        if (rc != SA_OK) return rc;
         cudaStream_t s = idx->stream;
         const uint64_t scan_launches = idx->stats.kernel_launches;   // sa_build_resident clears the stats
         // the scan already lower-cased the column (tolower, engine.c:559,581,593)
@@ -373,15 +408,8 @@ extern "C" int sa_build_csv_columns(sa_index* const* idxs, const char* const* co
         idx->stats.kernel_launches += scan_launches;
         idx->built = false;
         idx->stats.csv_host_scan = regular ? 0u : 1u;
-        SA_CU(idx->sa_file.ensure((size_t)n * 4));
-        SA_CU(idx->qbits.ensure((((size_t)n + 31) / 32) * 4 + 4));
-        {
-            ScopedPhase ph(idx, &idx->stats.ms_remap);
-            SA_CU(sa_launch_remap(idx->sa_final.as<uint32_t>(), (uint32_t)n, idx->map.as<uint32_t>(),
-                                  regular ? nullptr : idx->quoted_text.as<uint8_t>(), idx->sa_file.as<uint32_t>(),
-                                  idx->qbits.as<uint32_t>(), s));
-            idx->stats.kernel_launches += 1;
-        }
+        rc = csv_remap(idx, regular);
+        if (rc != SA_OK) return rc;
         if (idx != src) {                          // every index answers hits with row ids: its own copy of the row table
             SA_CU(idx->rowbits.ensure(sa_csv_rowbits_bytes(m.size)));
             SA_CU(idx->rowrank.ensure(sa_csv_rowrank_bytes(m.size)));
@@ -402,4 +430,58 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
 {
     if (!idx || !csv_path || !column) { sa_set_error("sa_build_csv: NULL argument"); return SA_ERR_INVALID; }
     return sa_build_csv_columns(&idx, &column, 1, csv_path, flags);
+}
+
+// ------------------------------------------------------------------------------ CSV column over several GPUs
+// The sharded build (sa_shard.cu) takes its text from a CSV column: every rank reads and scans the
+// file itself (the scan is ~1 % of the build; nothing has to be exchanged), sa_shard_begin_csv leaves
+// the rank where sa_shard_begin would, and once the complete ORDER-E array is installed
+// (sa_shard_mark_built / sa_adopt_sa[_parts]) sa_csv_finalize_shard runs the remap on it.
+extern "C" int sa_shard_begin_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags)
+{
+    if (!idx || !csv_path || !column) { sa_set_error("sa_shard_begin_csv: NULL argument"); return SA_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    Mapped m;
+    std::vector<std::string> cells;
+    int rc = open_csv(csv_path, m, cells);
+    if (rc != SA_OK) return rc;
+    uint32_t col = 0;
+    rc = find_column(cells, column, csv_path, &col);
+    if (rc != SA_OK) return rc;
+    idx->timing = (flags & SA_FLAG_TIMING) != 0;
+    idx->built = false;
+    idx->have_ranges = false;
+    idx->csv = false;
+    idx->shard_prepared = false;
+    idx->shard_csv = false;
+    memset(&idx->stats, 0, sizeof idx->stats);
+    rc = csv_load_device(idx, m.fd, m.size, idx->dbg_csv_scanner != 1);
+    if (rc != SA_OK) return rc;
+    bool file_regular = idx->dbg_csv_scanner != 1, regular = false;
+    rc = scan_one_column(idx, idx, m, col, (uint32_t)cells.size(), csv_path, &file_regular, &regular);
+    if (rc != SA_OK) return rc;
+    const uint64_t n = idx->n;
+    if (n == 0) { sa_set_error("sa_shard_begin_csv: the column is empty"); return SA_ERR_INVALID; }
+    idx->lprime = idx->L < n ? idx->L : (uint32_t)n;
+    idx->stats.n = n; idx->stats.max_suffix_length = idx->L; idx->stats.lprime = idx->lprime;
+    idx->stats.csv_host_scan = regular ? 0u : 1u;
+    rc = sa_stage_prepare(idx, flags & ~SA_FLAG_LOWERCASE);
+    if (rc != SA_OK) return rc;
+    if (idx->lprime == 0) { sa_set_error("sa_shard_begin_csv: max_suffix_length 0 needs no sharded build"); return SA_ERR_INVALID; }
+    idx->csv_file_bytes = m.size;
+    idx->shard_csv = true;
+    idx->shard_csv_regular = regular;
+    idx->shard_prepared = true;
+    return SA_OK;
+}
+
+int sa_csv_finalize_shard(sa_index* idx)
+{
+    int rc = csv_remap(idx, idx->shard_csv_regular);
+    if (rc != SA_OK) return rc;
+    SA_CU(cudaStreamSynchronize(idx->stream));
+    sa_time_collect(idx);
+    idx->csv = true;
+    return SA_OK;
 }

@@ -90,6 +90,8 @@ struct sa_index {
 
     // sharded (multi-GPU) build state, see sa_shard.cu
     bool shard_prepared = false;
+    bool shard_csv = false;          // the sharded build's text is a CSV column (sa_shard_begin_csv): remap when the array is complete
+    bool shard_csv_regular = false;  // ... scanned on the device (quoted flags ride in the offset map)
     uint32_t shard_m = 0;          // records this rank sorts
     uint32_t* shard_sa = nullptr;  // their positions in prefix order (points into vals[])
     DevBuf ext_sa, ext_lcp, ext_out, split_table, split_offsets;
@@ -172,3 +174,4 @@ int sa_stage_finish(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint
 int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
                        uint32_t r_end, const sa::FinishOut& outs, uint32_t block0 = 0, uint32_t nblocks = 0xFFFFFFFFu);
 int sa_check_device_error(sa_index* idx);
+int sa_csv_finalize_shard(sa_index* idx);   // sa_csv.cu: SA[i] = map[SA[i]] + quoted bits on the complete array of a sharded CSV build

@@ -260,6 +260,7 @@ extern "C" int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, ui
     idx->have_ranges = false;
     idx->csv = false;
     idx->shard_prepared = false;
+    idx->shard_csv = false;
     memset(&idx->stats, 0, sizeof idx->stats);
     idx->lprime = idx->L < n ? idx->L : (uint32_t)n;
     idx->stats.n = n; idx->stats.max_suffix_length = idx->L; idx->stats.lprime = idx->lprime;
@@ -606,7 +607,27 @@ extern "C" int sa_shard_mark_built(sa_index* idx)
 {
     SH_REQUIRE(idx && idx->shard_prepared && idx->sa_final.p, SA_ERR_INVALID, "sa_shard_mark_built: nothing to adopt");
     std::lock_guard<std::mutex> lock(idx->mu);
+    if (idx->shard_csv) {
+        SA_CU(cudaSetDevice(idx->device));
+        int rc = sa_csv_finalize_shard(idx);
+        if (rc != SA_OK) return rc;
+    }
     idx->built = true;
+    return SA_OK;
+}
+
+// Text the shard build works on (after sa_shard_begin / sa_shard_begin_csv): its size, and a copy for the
+// host side of the driver (a few boundary LCPs are computed there).
+extern "C" uint64_t sa_shard_text_size(const sa_index* idx) { return idx && idx->shard_prepared ? idx->n : 0; }
+
+extern "C" int sa_shard_copy_text(sa_index* idx, uint8_t* out, uint64_t cap)
+{
+    SH_REQUIRE(idx && idx->shard_prepared && out, SA_ERR_INVALID, "sa_shard_copy_text: bad argument");
+    SH_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "sa_shard_copy_text: cap too small");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    SA_CU(cudaMemcpyAsync(out, idx->text.p, (size_t)idx->n, cudaMemcpyDeviceToHost, idx->stream));
+    SA_CU(cudaStreamSynchronize(idx->stream));
     return SA_OK;
 }
 
@@ -622,6 +643,10 @@ extern "C" int sa_adopt_sa(sa_index* idx, const uint32_t* d_sa_full, uint64_t n)
     SA_CU(idx->sa_final.ensure((size_t)n * 4));
     SA_CU(cudaMemcpyAsync(idx->sa_final.p, d_sa_full, (size_t)n * 4, cudaMemcpyDeviceToDevice, idx->stream));
     SA_CU(cudaStreamSynchronize(idx->stream));
+    if (idx->shard_csv) {
+        int rc = sa_csv_finalize_shard(idx);
+        if (rc != SA_OK) return rc;
+    }
     idx->built = true;
     return SA_OK;
 }
@@ -787,6 +812,10 @@ extern "C" int sa_adopt_sa_parts(sa_index* idx, const uint32_t* d_parts, uint64_
         off += counts[g];
     }
     SA_CU(cudaStreamSynchronize(idx->stream));
+    if (idx->shard_csv) {
+        int rc = sa_csv_finalize_shard(idx);
+        if (rc != SA_OK) return rc;
+    }
     idx->built = true;
     return SA_OK;
 }
