@@ -143,6 +143,15 @@ int sa_copy_doc_starts(sa_index* idx, uint32_t* out, uint64_t cap);
  *   sa_shard_sort -> sa_shard_edges (+ all-gather of the edges) -> sa_shard_finish ->
  *   all-gather of the slices -> sa_adopt_sa (queries).  suffixarray_b200/sharded.py drives it. */
 int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, uint32_t flags);
+/* Same starting point with the text taken from a CSV column (BASELINE config 3 at 2/4/8 GPUs): every
+ * rank reads and scans the file itself (sa_build_csv's feeder), the stages that follow are unchanged,
+ * and when the complete array is installed (sa_shard_mark_built / sa_adopt_sa[_parts]) the rank runs
+ * the reference's two post-build loops on it (SA[i] = map[SA[i]], quoted bits; engine.c:632-651).
+ * sa_shard_text_size / sa_shard_copy_text give the host driver the column text it needs for the
+ * few boundary LCPs. */
+int sa_shard_begin_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags);
+uint64_t sa_shard_text_size(const sa_index* idx);
+int sa_shard_copy_text(sa_index* idx, uint8_t* out, uint64_t cap);
 int sa_shard_pack(sa_index* idx, uint64_t pos_begin, uint64_t pos_end, uint64_t* d_keys, uint32_t* d_pos,
                   uint32_t* d_hist16);
 int sa_shard_split(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m,

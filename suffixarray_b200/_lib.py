@@ -28,7 +28,7 @@ EXPORTS = [
     "sa_build_csv", "sa_build_csv_columns", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
     "sa_copy_quoted_bits", "sa_copy_text", "sa_device_sa", "sa_get_stats", "sa_query_ranges", "sa_query_hits",
     "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
-    "sa_shard_begin", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
+    "sa_shard_begin", "sa_shard_begin_csv", "sa_shard_text_size", "sa_shard_copy_text", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
     "sa_adopt_sa", "sa_adopt_sa_parts", "sa_shard_count", "sa_shard_recv_prepare", "sa_shard_scatter_p2p", "sa_shard_sort_recv",
     "sa_shard_final_prepare", "sa_shard_finish_bcast", "sa_shard_mark_built",
     "sa_save", "sa_load", "sa_export_reference_files",
@@ -102,6 +102,10 @@ def lib():
     L.sa_query_ranges_device.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint64, C.c_uint32, _vp, _vp]
     L.sa_debug_set.argtypes = [_vp, C.c_char_p, C.c_int64]
     L.sa_shard_begin.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
+    L.sa_shard_begin_csv.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint32]
+    L.sa_shard_text_size.argtypes = [_vp]
+    L.sa_shard_text_size.restype = C.c_uint64
+    L.sa_shard_copy_text.argtypes = [_vp, _vp, C.c_uint64]
     L.sa_shard_pack.argtypes = [_vp, C.c_uint64, C.c_uint64, _vp, _vp, _vp]
     L.sa_shard_split.argtypes = [_vp, _vp, _vp, C.c_uint64, _vp, C.c_int, _vp, _vp, _vp]
     L.sa_shard_sort.argtypes = [_vp, _vp, _vp, C.c_uint64]

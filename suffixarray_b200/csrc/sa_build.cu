@@ -415,6 +415,8 @@ int sa_build_resident(sa_index* idx, uint32_t flags)
     idx->built = false;
     idx->have_ranges = false;
     idx->csv = false;
+    idx->shard_prepared = false;
+    idx->shard_csv = false;
     if (n == 0) { idx->num_nl = 0; st.num_docs = 1; idx->built = true; return SA_OK; }
     int rc;
     {

@@ -138,17 +138,22 @@ def assemble_halos(edges: list[dict], rank: int, text: np.ndarray, lprime: int, 
 class ShardBuilder:
     """The per-rank phases.  Buffers that cross a collective are torch CUDA tensors."""
 
-    def __init__(self, text: np.ndarray, max_suffix_length: int, rank: int, world: int, device: int,
-                 lowercase: bool = False, timing: bool = False, device_text=None):
+    def __init__(self, text, max_suffix_length: int, rank: int, world: int, device: int,
+                 lowercase: bool = False, timing: bool = False, device_text=None, csv=None):
         """text: the whole text on the host (also used for the few boundary LCPs); device_text: an
-        optional torch CUDA uint8 tensor holding the same bytes, to skip the host-to-device copy."""
+        optional torch CUDA uint8 tensor holding the same bytes, to skip the host-to-device copy.
+        csv = (path, column): the text is that column of a CSV file instead (every rank scans the
+        file itself; the finished array holds file offsets, as after sa_build_csv)."""
         import torch
         self.torch = torch
         self.rank, self.world, self.device = rank, world, device
         self.L = int(max_suffix_length)
         self.dev = torch.device("cuda", device)
         self.idx = S.Index(self.L, device=device)
-        self.begin(text, lowercase, timing, device_text)
+        if csv is not None:
+            self.begin_csv(csv[0], csv[1], timing)
+        else:
+            self.begin(text, lowercase, timing, device_text)
 
     def begin(self, text: np.ndarray, lowercase: bool = False, timing: bool = False, device_text=None):
         """(Re)start a build on this rank's index; scratch from an earlier build is reused."""
@@ -163,6 +168,18 @@ class ShardBuilder:
                                            flags | S.SA_FLAG_DEVICE_TEXT))
         else:
             S.check(S.lib().sa_shard_begin(self.idx._h, self.text.ctypes.data_as(S._vp), self.n, flags))
+        b = slice_bounds(self.n, self.world)
+        self.pos_begin, self.pos_end = b[self.rank], b[self.rank + 1]
+        self.m_local = self.pos_end - self.pos_begin
+
+    def begin_csv(self, path: str, column: str, timing: bool = False):
+        """(Re)start a build whose text is a CSV column (sa_shard_begin_csv)."""
+        S.check(S.lib().sa_shard_begin_csv(self.idx._h, path.encode(), column.encode(), S.SA_FLAG_TIMING if timing else 0))
+        self.n = int(S.lib().sa_shard_text_size(self.idx._h))
+        self.text = np.empty(self.n, dtype=np.uint8)          # host copy for the boundary LCPs
+        S.check(S.lib().sa_shard_copy_text(self.idx._h, self.text.ctypes.data_as(S._vp), self.n))
+        self.lowercase = False                                 # the column scan lower-cases (engine.c:559,581,593)
+        self.lprime = min(self.L, self.n)
         b = slice_bounds(self.n, self.world)
         self.pos_begin, self.pos_end = b[self.rank], b[self.rank + 1]
         self.m_local = self.pos_end - self.pos_begin
@@ -308,13 +325,14 @@ def _array_to_edges(row: np.ndarray) -> dict:
 
 # ----------------------------------------------------------------------------- drivers
 def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lowercase: bool = False,
-                   adopt: bool = True, exchange: str = "p2p", replicate: str = "allgather"):
+                   adopt: bool = True, exchange: str = "p2p", replicate: str = "allgather", csv=None):
     """G ranks in lock step inside one process on ONE GPU (collectives = tensor copies).
-    -> (full SA as a torch int32 CUDA tensor, list of ShardBuilder).  Test tier only."""
+    -> (full array of text positions as a torch int32 CUDA tensor, list of ShardBuilder).  Test tier only."""
     import torch
-    text = np.ascontiguousarray(np.frombuffer(text, np.uint8) if isinstance(text, (bytes, bytearray)) else text,
-                                dtype=np.uint8)
-    ranks = [ShardBuilder(text, max_suffix_length, g, world, device, lowercase) for g in range(world)]
+    if csv is None:
+        text = np.ascontiguousarray(np.frombuffer(text, np.uint8) if isinstance(text, (bytes, bytearray)) else text,
+                                    dtype=np.uint8)
+    ranks = [ShardBuilder(text, max_suffix_length, g, world, device, lowercase, csv=csv) for g in range(world)]
     hist = sum(r.pack().to(torch.int64) for r in ranks)                       # all-reduce
     hist_np = hist.cpu().numpy()
     if exchange == "p2p":
@@ -333,7 +351,7 @@ def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lo
                 r.finish_bcast(edges, fh)
             for r in ranks:                                                    # barrier
                 r.mark_built()
-            full = torch.from_numpy(ranks[0].idx.sa().astype(np.int32)).to(ranks[0].dev)
+            full = torch.from_numpy(ranks[0].idx.text_positions().astype(np.int32)).to(ranks[0].dev)
             return full, ranks
         slices = [r.finish(edges) for r in ranks]
         full = torch.cat(slices)
@@ -366,15 +384,17 @@ def build_emulated(text, max_suffix_length: int, world: int, device: int = 0, lo
 
 def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool = False, timing: bool = False,
                       adopt: bool = True, group=None, device_text=None, builder=None, exchange: str = "p2p",
-                      replicate: str = "fused"):
+                      replicate: str = "fused", csv=None):
     """This process's rank of the sample-sort build under torch.distributed (NCCL).
+    csv = (path, column): index that column of a CSV file instead of `text`.
     -> (ShardBuilder with the complete SA adopted, dict of per-phase wall times in ms)."""
     import time
     import torch
     import torch.distributed as dist
     rank, world = dist.get_rank(group), dist.get_world_size(group)
-    text = np.ascontiguousarray(np.frombuffer(text, np.uint8) if isinstance(text, (bytes, bytearray)) else text,
-                                dtype=np.uint8)
+    if csv is None:
+        text = np.ascontiguousarray(np.frombuffer(text, np.uint8) if isinstance(text, (bytes, bytearray)) else text,
+                                    dtype=np.uint8)
     t = {}
     t0 = time.perf_counter()
 
@@ -386,7 +406,10 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
         t0 = now
 
     if builder is None:
-        r = ShardBuilder(text, max_suffix_length, rank, world, device, lowercase, timing, device_text)
+        r = ShardBuilder(text, max_suffix_length, rank, world, device, lowercase, timing, device_text, csv=csv)
+    elif csv is not None:
+        r = builder
+        r.begin_csv(csv[0], csv[1], timing)
     else:
         r = builder
         r.begin(text, lowercase, timing, device_text)

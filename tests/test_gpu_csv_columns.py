@@ -167,3 +167,42 @@ def test_suffix_array_class_multi_column_and_multiline_rows(tmp_path):
         assert sa.query_records(q, k=300) == sb.query_records(q, k=300)
     sa.close()
     sb.close()
+
+
+@pytest.mark.parametrize("world,exchange,replicate", [(2, "p2p", "fused"), (3, "p2p", "allgather"), (4, "nccl", "allgather")])
+def test_sharded_csv_column_matches_single_gpu(world, exchange, replicate):
+    """BASELINE config 3 over several GPUs: the sample-sort build fed by the CSV column scan
+    (sa_shard_begin_csv), ranks emulated on one GPU; array of file offsets, quoted bits and hits must
+    equal the single-GPU sa_build_csv result (itself checked against the oracle above)."""
+    from suffixarray_b200 import _lib as S
+    from suffixarray_b200 import sharded as SH
+    cases = [(W.csv_file_bytes(3000, seed=61, quoted_fraction=0.3), "name", 0),
+             (FILES["multiline_cells"][0], "a", 0),
+             (FILES["irregular_quote"][0], "b", 0),
+             (W.csv_file_bytes(800, seed=62, quoted_fraction=0.2), "city", 1)]
+    for data, column, scanner in cases:
+        path = write_tmp(data)
+        single = S.Index(L)
+        ranks = []
+        try:
+            single.debug_set("csv_scanner", scanner)
+            single.build_csv(path, column)
+            _, ranks = SH.build_emulated(None, L, world, exchange=exchange, replicate=replicate, csv=(path, column))
+            text = single.text()
+            qs = sorted({bytes(text[p:p + 4]).split(b"\n")[0] for p in range(0, text.size, 7)} - {b""})[:300]
+            ws, we, woff = single.query_ranges(qs, k=20)
+            wpos, wrow = single.query_hits(int(woff[-1]))
+            for r in ranks:
+                assert r.idx.n == single.n
+                assert np.array_equal(r.idx.sa(), single.sa())
+                assert np.array_equal(r.idx.text_positions(), single.text_positions())
+                assert np.array_equal(r.idx.quoted_bits(), single.quoted_bits())
+                s, e, off = r.idx.query_ranges(qs, k=20)
+                pos, row = r.idx.query_hits(int(off[-1]))
+                assert np.array_equal(s, ws) and np.array_equal(e, we) and np.array_equal(off, woff)
+                assert np.array_equal(pos, wpos) and np.array_equal(row, wrow)
+        finally:
+            single.close()
+            for r in ranks:
+                r.close()
+            os.unlink(path)
