@@ -196,7 +196,36 @@ def section_c3(args, out):
                  "phases_ms": {k: round(v, 2) for k, v in st.items() if k.startswith("ms_")},
                  "range_queries_per_s_device": round(args.queries / stq["ms_query"] * 1e3, 0),
                  "range_queries_per_s_host_buffers": round(args.queries / qms * 1e3, 0)}
+    # record queries: hits come back as (file offset, row of the file) from the device row table
+    total = int(res["r"][2][-1])
+
+    def qh():
+        res["h"] = idx.query_hits(total)
+    hms = timed(qh, reps=3, warm=1)
+    sth = idx.stats()
+    pos, row = res["h"]
+    out["c3"].update({"hits_per_batch": total, "hits_ms_device": round(sth["ms_hits"], 3), "hits_ms_host_buffers": round(hms, 3),
+                      "record_queries_per_s_device": round(args.queries / (stq["ms_query"] + sth["ms_hits"]) * 1e3, 0),
+                      "rows_in_range": bool(total == 0 or int(row.max()) <= rows)})
     idx.close()
+    # three search columns from one read of the file (sa_build_csv_columns)
+    cols = ["name", "city", "score"]
+    idxs = [S.Index(32, device=0) for _ in cols]
+    walls3 = []
+    for rep in range(2):
+        sync()
+        t0 = time.perf_counter()
+        S.Index.build_csv_columns(idxs, path, cols, timing=True)
+        sync()
+        walls3.append((time.perf_counter() - t0) * 1e3)
+    out["c3"]["three_columns_one_call"] = {
+        "columns": cols, "chars": [ix.n for ix in idxs], "e2e_ms_runs": [round(w, 1) for w in walls3],
+        "device_build_ms": [round(ix.stats()["ms_total"], 2) for ix in idxs],
+        "csv_scan_ms": [round(ix.stats()["ms_csv_scan"], 2) for ix in idxs],
+        "h2d_ms": [round(ix.stats()["ms_h2d"], 2) for ix in idxs],
+        "mchars_per_s_e2e": round(sum(ix.n for ix in idxs) / min(walls3) / 1e3, 1)}
+    for ix in idxs:
+        ix.close()
     os.remove(path)
     os.rmdir(d)
 
