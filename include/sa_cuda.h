@@ -147,11 +147,11 @@ int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, uint32_t flag
  * rank reads and scans the file itself (sa_build_csv's feeder), the stages that follow are unchanged,
  * and when the complete array is installed (sa_shard_mark_built / sa_adopt_sa[_parts]) the rank runs
  * the reference's two post-build loops on it (SA[i] = map[SA[i]], quoted bits; engine.c:632-651).
- * sa_shard_text_size / sa_shard_copy_text give the host driver the column text it needs for the
- * few boundary LCPs. */
+ * sa_shard_text_size / sa_shard_copy_text (any byte range) give the host driver the few windows of
+ * the column text it needs for the boundary LCPs. */
 int sa_shard_begin_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags);
 uint64_t sa_shard_text_size(const sa_index* idx);
-int sa_shard_copy_text(sa_index* idx, uint8_t* out, uint64_t cap);
+int sa_shard_copy_text(sa_index* idx, uint64_t offset, uint64_t len, uint8_t* out);
 int sa_shard_pack(sa_index* idx, uint64_t pos_begin, uint64_t pos_end, uint64_t* d_keys, uint32_t* d_pos,
                   uint32_t* d_hist16);
 int sa_shard_split(sa_index* idx, const uint64_t* d_keys, const uint32_t* d_pos, uint64_t m,

@@ -64,7 +64,7 @@ all_dg = [torch.zeros_like(dg) for _ in range(world)]
 dist.all_gather(all_dg, dg)
 replicas_equal = all(bool(torch.equal(all_dg[0], x)) for x in all_dg)
 # every rank answers its own share of a query batch
-text = builder.text
+text = builder.idx.text()
 qbytes, qoff = W.substring_queries(text, args.queries, seed=3002 + rank)
 s, e, off = builder.idx.query_ranges_packed(qbytes, qoff, k=1000)
 pos, row = builder.idx.query_hits(int(off[-1]))
@@ -72,9 +72,13 @@ qms = builder.idx.stats()["ms_query"]
 report = None
 if rank == 0:
     single = S.Index(L, device=local)
-    t0 = time.perf_counter()
-    single.build_csv(path, "name", timing=True)
-    single_ms = (time.perf_counter() - t0) * 1e3
+    single_runs = []
+    for _ in range(3):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        single.build_csv(path, "name", timing=True)
+        single_runs.append((time.perf_counter() - t0) * 1e3)
+    single_ms = min(single_runs[1:])
     same = bool(np.array_equal(single.sa(), mine)) and bool(np.array_equal(single.quoted_bits(), builder.idx.quoted_bits()))
     s1, e1, off1 = single.query_ranges_packed(qbytes, qoff, k=1000)
     pos1, row1 = single.query_hits(int(off1[-1]))
@@ -83,7 +87,7 @@ if rank == 0:
               "e2e_ms_runs": [round(w, 1) for w in walls], "e2e_ms": round(min(walls[1:]), 1),
               "mchars_per_s_e2e": round(n / min(walls[1:]) / 1e3, 1),
               "phases_ms_last_rank0": {k: round(v, 2) for k, v in phases.items()},
-              "single_gpu_e2e_ms_first_call": round(single_ms, 1), "single_gpu_device_build_ms": round(single.stats()["ms_total"], 2),
+              "single_gpu_e2e_ms": round(single_ms, 1), "single_gpu_device_build_ms": round(single.stats()["ms_total"], 2),
               "array_and_quoted_bits_equal_single_gpu": same, "replicas_equal": replicas_equal,
               "queries_equal_single_gpu": qsame, "range_queries_per_s_device_per_rank": round(args.queries / qms * 1e3, 0),
               "row_ids_in_range": bool(int(row.max()) <= rows)}

@@ -105,7 +105,7 @@ def lib():
     L.sa_shard_begin_csv.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint32]
     L.sa_shard_text_size.argtypes = [_vp]
     L.sa_shard_text_size.restype = C.c_uint64
-    L.sa_shard_copy_text.argtypes = [_vp, _vp, C.c_uint64]
+    L.sa_shard_copy_text.argtypes = [_vp, C.c_uint64, C.c_uint64, _vp]
     L.sa_shard_pack.argtypes = [_vp, C.c_uint64, C.c_uint64, _vp, _vp, _vp]
     L.sa_shard_split.argtypes = [_vp, _vp, _vp, C.c_uint64, _vp, C.c_int, _vp, _vp, _vp]
     L.sa_shard_sort.argtypes = [_vp, _vp, _vp, C.c_uint64]

@@ -616,17 +616,18 @@ extern "C" int sa_shard_mark_built(sa_index* idx)
     return SA_OK;
 }
 
-// Text the shard build works on (after sa_shard_begin / sa_shard_begin_csv): its size, and a copy for the
-// host side of the driver (a few boundary LCPs are computed there).
+// Text the shard build works on (after sa_shard_begin / sa_shard_begin_csv): its size, and a copy of
+// any byte range of it for the host side of the driver (a few boundary LCPs are computed there).
 extern "C" uint64_t sa_shard_text_size(const sa_index* idx) { return idx && idx->shard_prepared ? idx->n : 0; }
 
-extern "C" int sa_shard_copy_text(sa_index* idx, uint8_t* out, uint64_t cap)
+extern "C" int sa_shard_copy_text(sa_index* idx, uint64_t offset, uint64_t len, uint8_t* out)
 {
-    SH_REQUIRE(idx && idx->shard_prepared && out, SA_ERR_INVALID, "sa_shard_copy_text: bad argument");
-    SH_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "sa_shard_copy_text: cap too small");
+    SH_REQUIRE(idx && idx->shard_prepared && (out || len == 0), SA_ERR_INVALID, "sa_shard_copy_text: bad argument");
+    SH_REQUIRE(offset <= idx->n && len <= idx->n - offset, SA_ERR_INVALID, "sa_shard_copy_text: range outside the text");
+    if (len == 0) return SA_OK;
     std::lock_guard<std::mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
-    SA_CU(cudaMemcpyAsync(out, idx->text.p, (size_t)idx->n, cudaMemcpyDeviceToHost, idx->stream));
+    SA_CU(cudaMemcpyAsync(out, idx->text.as<uint8_t>() + offset, (size_t)len, cudaMemcpyDeviceToHost, idx->stream));
     SA_CU(cudaStreamSynchronize(idx->stream));
     return SA_OK;
 }

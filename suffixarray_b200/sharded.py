@@ -134,6 +134,25 @@ def assemble_halos(edges: list[dict], rank: int, text: np.ndarray, lprime: int, 
             cat(right_pos, np.uint32), cat(right_lcp, np.uint16))
 
 
+class DeviceText:
+    """The text of a shard build that only exists on the device (a scanned CSV column): `size` and
+    slicing, which is all boundary_lcp needs -- a window is fetched when it is asked for."""
+
+    def __init__(self, idx, n: int):
+        self._idx, self.size = idx, int(n)
+
+    def __getitem__(self, sl):
+        a, b, step = sl.indices(self.size)
+        assert step == 1
+        out = np.empty(max(b - a, 0), dtype=np.uint8)
+        if out.size:
+            S.check(S.lib().sa_shard_copy_text(self._idx._h, a, out.size, out.ctypes.data_as(S._vp)))
+        return out
+
+    def whole(self) -> np.ndarray:
+        return self[0:self.size]
+
+
 # ----------------------------------------------------------------------------- one rank
 class ShardBuilder:
     """The per-rank phases.  Buffers that cross a collective are torch CUDA tensors."""
@@ -176,8 +195,7 @@ class ShardBuilder:
         """(Re)start a build whose text is a CSV column (sa_shard_begin_csv)."""
         S.check(S.lib().sa_shard_begin_csv(self.idx._h, path.encode(), column.encode(), S.SA_FLAG_TIMING if timing else 0))
         self.n = int(S.lib().sa_shard_text_size(self.idx._h))
-        self.text = np.empty(self.n, dtype=np.uint8)          # host copy for the boundary LCPs
-        S.check(S.lib().sa_shard_copy_text(self.idx._h, self.text.ctypes.data_as(S._vp), self.n))
+        self.text = DeviceText(self.idx, self.n)               # windows are fetched for the boundary LCPs only
         self.lowercase = False                                 # the column scan lower-cases (engine.c:559,581,593)
         self.lprime = min(self.L, self.n)
         b = slice_bounds(self.n, self.world)
