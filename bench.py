@@ -75,6 +75,10 @@ def parse_args():
     ap.add_argument("--verify-single", action="store_true",
                     help="N > 1: after the timed steps rank 0 also builds the same text on ONE GPU and the arrays are "
                          "compared bit for bit; every rank's replica is compared through a digest")
+    ap.add_argument("--verify-properties", action="store_true",
+                    help="N > 1: size-independent checks of the global array on every rank (for n > 2^31, where no "
+                         "single-GPU build exists): permutation of [0, n), first-8-byte keys non-decreasing over the "
+                         "ranks, replicas identical by digest")
     ap.add_argument("--mode", default="global", choices=["global", "partition"],
                     help="N > 1: one global index built as a sample sort (default) or one independent "
                          "partition per GPU (the reference's own partitioning, suffix_array.pyx:148-180)")
@@ -436,6 +440,8 @@ def run_ours_global(args, world, rank, local):
             single.close()
         del mine
         dist.barrier()
+    if args.verify_properties:
+        verify = verify_properties(builders["dev"], d_text, n, dev, world)
     K = args.steps
     phase_names = list(recs[-1]["phases"].keys())
     sums = torch.tensor([sum(r["build_dev_ms"] for r in recs), sum(r["query_dev_ms"] for r in recs),
@@ -482,6 +488,59 @@ def run_ours_global(args, world, rank, local):
     dist.barrier()
     dist.destroy_process_group()
     return result
+
+
+class _DeviceU32:
+    """zero-copy torch view of a raw device array (CUDA array interface)"""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<i4", "data": (int(ptr), True), "version": 2}
+
+
+def verify_properties(builder, d_text, n, dev, world):
+    """Checks that need no reference array, on the device, in chunks:
+    the array is a permutation of [0, n); K(SA[i]) <= K(SA[i+1]) for the masked big-endian key K of
+    the first 8 bytes (ORDER-E refines this order, it never contradicts it); all replicas agree."""
+    import torch
+    import torch.distributed as dist
+    from suffixarray_b200 import _lib as S
+    sa = torch.as_tensor(_DeviceU32(S.lib().sa_device_sa(builder.idx._h), n), device=dev)
+    CH = 1 << 25
+    seen = torch.zeros(n, dtype=torch.uint8, device=dev)
+    text = torch.cat([d_text, torch.zeros(8, dtype=torch.uint8, device=dev)])
+    ar8 = torch.arange(8, device=dev, dtype=torch.int64)
+    shifts = 8 * (7 - ar8)
+    sorted_ok, prev_last = True, None
+    digest = torch.zeros(2, dtype=torch.int64, device=dev)
+    ascii_only = bool((d_text < 128).all())
+    for a in range(0, n, CH):
+        z = min(n, a + CH)
+        pos = sa[a:z].to(torch.int64) & 0xFFFFFFFF
+        seen[pos] = 1
+        weight = torch.arange(a, z, device=dev, dtype=torch.int64) % 1000003 + 1
+        digest[0] += (pos * weight).sum()
+        digest[1] += (pos * pos).sum()
+        if ascii_only:
+            b = text[pos[:, None] + ar8[None, :]].to(torch.int64)
+            term = ((b == 10) | (b == 255)).to(torch.int32)
+            after = (torch.cumsum(term, dim=1) - term) > 0
+            b = torch.where(after, torch.zeros_like(b), b)
+            key = (b << shifts[None, :]).sum(dim=1)
+            sorted_ok = sorted_ok and bool((key[1:] >= key[:-1]).all())
+            if prev_last is not None:
+                sorted_ok = sorted_ok and bool(key[0] >= prev_last)
+            prev_last = key[-1].clone()
+            del b, term, after, key
+        del pos, weight
+    perm_ok = bool(seen.all())
+    all_dg = [torch.zeros_like(digest) for _ in range(world)]
+    dist.all_gather(all_dg, digest)
+    flags = torch.tensor([int(perm_ok), int(sorted_ok)], dtype=torch.int32, device=dev)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    return {"n": int(n), "permutation_on_every_rank": bool(flags[0].item()),
+            "first_8_byte_keys_non_decreasing_on_every_rank": bool(flags[1].item()) if ascii_only else None,
+            "replicas_equal": all(bool(torch.equal(all_dg[0], x)) for x in all_dg),
+            "positions_above_2^31": int(max(0, n - (1 << 31)))}
 
 
 # ------------------------------------------------------------------------------ CPU reference legs
