@@ -494,7 +494,7 @@ class _DeviceU32:
     """zero-copy torch view of a raw device array (CUDA array interface)"""
 
     def __init__(self, ptr: int, n: int):
-        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<i4", "data": (int(ptr), True), "version": 2}
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
 
 
 def verify_properties(builder, d_text, n, dev, world):
