@@ -179,6 +179,8 @@ def load_ncu_traffic():
 
 
 def dist_setup(args):
+    # NCCL's own "NCCL version ..." banner goes to stdout by default: keep stdout to the ONE JSON line
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
