@@ -79,6 +79,8 @@ def parse_args():
                     help="N > 1: size-independent checks of the global array on every rank (for n > 2^31, where no "
                          "single-GPU build exists): permutation of [0, n), first-8-byte keys non-decreasing over the "
                          "ranks, replicas identical by digest")
+    ap.add_argument("--share-builder", action="store_true",
+                    help="global mode: the host-buffer leg reuses the device leg's index (half the scratch; for scale runs)")
     ap.add_argument("--mode", default="global", choices=["global", "partition"],
                     help="N > 1: one global index built as a sample sort (default) or one independent "
                          "partition per GPU (the reference's own partitioning, suffix_array.pyx:148-180)")
@@ -103,7 +105,20 @@ def make_workload(name: str, rank: int):
         np.cumsum(lens, out=qoff[1:])
         qbytes = np.frombuffer(b"".join(qs), dtype=np.uint8).copy()
         return text, qbytes, qoff, True
-    text = W.english_documents(n_chars, seed=2001 + rank)
+    CH = 250_000_000                                   # scale runs: generated in pieces (the generator's index arrays are 8 B per char)
+    if n_chars <= CH:
+        text = W.english_documents(n_chars, seed=2001 + rank)
+    else:
+        parts, left, k = [], n_chars, 0
+        while left > 0:
+            take = min(CH, left) - (1 if left > CH else 0)
+            parts.append(W.english_documents(take, seed=2001 + rank + 1000 * k))
+            left -= take
+            if left > 0:
+                parts.append(np.frombuffer(b"\n", np.uint8))
+                left -= 1
+            k += 1
+        text = np.concatenate(parts)
     qbytes, qoff = W.substring_queries(text, nq, seed=2002 + rank)
     return text, qbytes, qoff, False
 
@@ -364,14 +379,15 @@ def run_ours_global(args, world, rank, local):
         dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
+        slot = "dev" if args.share_builder else kind
         b, phases = SH.build_distributed(h_text, L, local, lowercase=lower, timing=True,
-                                         device_text=d_text if kind == "dev" else None, builder=builders[kind],
+                                         device_text=d_text if kind == "dev" else None, builder=builders[slot],
                                          exchange=args.exchange, replicate=args.replicate)
-        if builders[kind] is None:                                    # tuning experiments: key=value,... (from the 2nd build on)
+        if builders[slot] is None:                                    # tuning experiments: key=value,... (from the 2nd build on)
             for kv in (os.environ.get("SA_BENCH_DEBUG") or "").split(","):
                 if "=" in kv:
                     b.idx.debug_set(kv.split("=")[0], int(kv.split("=")[1]))
-        builders[kind] = b
+        builders[slot] = b
         torch.cuda.synchronize()
         return b, (time.perf_counter() - t0) * 1e3, phases
 
