@@ -64,3 +64,18 @@ def test_invalid_arguments_do_not_crash():
     L.sa_destroy(None)
     out = np.zeros(4, np.uint32)
     assert L.sa_copy_sa_u32(None, out.ctypes.data_as(ctypes.c_void_p), 4) == -1
+
+
+def test_multi_column_entry_validates_before_touching_the_device():
+    L = S.lib()
+    vp, cp = ctypes.c_void_p, ctypes.c_char_p
+    assert L.sa_build_csv_columns(None, None, 1, b"x.csv", 0) == -1
+    hs = (vp * 1)(None)
+    cs = (cp * 1)(b"name")
+    assert L.sa_build_csv_columns(hs, cs, 0, b"x.csv", 0) == -1          # no columns
+    assert L.sa_build_csv_columns(hs, cs, 65, b"x.csv", 0) == -5         # more than 64 per call
+    assert L.sa_build_csv_columns(hs, cs, 1, b"x.csv", 0) == -1          # NULL handle in the list
+    assert b"NULL entry" in L.sa_last_error()
+    assert L.sa_build_csv(None, b"x.csv", b"name", 0) == -1
+    assert L.sa_shard_begin_csv(None, b"x.csv", b"name", 0) == -1
+    assert L.sa_shard_text_size(None) == 0
