@@ -418,7 +418,8 @@ def build_distributed(text, max_suffix_length: int, device: int, lowercase: bool
 
     def lap(name):
         nonlocal t0
-        torch.cuda.synchronize(device)
+        if torch.cuda.is_available():          # (the host-logic tests drive this function with a CPU stand-in over gloo)
+            torch.cuda.synchronize(device)
         now = time.perf_counter()
         t[name] = (now - t0) * 1e3
         t0 = now
