@@ -194,8 +194,6 @@ def load_ncu_traffic():
 
 
 def dist_setup(args):
-    # NCCL's own "NCCL version ..." banner goes to stdout by default: keep stdout to the ONE JSON line
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -216,7 +214,19 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device (libsa_cuda has no CPU fallback)")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # the "NCCL version ..." banner is written to fd 1 when the first communicator comes up: point
+        # fd 1 at stderr until then, so that stdout carries the ONE JSON line and nothing else
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     S.lib()   # fail loudly when the extension is missing
     L = args.max_suffix_length
     if world > 1 and args.mode == "global":
