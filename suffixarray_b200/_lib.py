@@ -9,6 +9,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 import subprocess
+import sys
 
 import numpy as np
 
@@ -63,6 +64,28 @@ def build_library(force: bool = False) -> None:
     r = subprocess.run(["make", "-C", CSRC, "-j8"], capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("building libsa_cuda.so failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+
+
+def build_cython_extension() -> str:
+    """Cythonize + compile suffix_array_cy.pyx (the reference's host language for this layer) in-tree,
+    linked against libsa_cuda.so next to it ($ORIGIN rpath).  -> path of the extension module."""
+    import sysconfig
+    src = os.path.join(_HERE, "suffix_array_cy.pyx")
+    bdir = os.path.join(CSRC, "build")
+    os.makedirs(bdir, exist_ok=True)
+    c_file = os.path.join(bdir, "suffix_array_cy.c")
+    out = os.path.join(_HERE, "suffix_array_cy" + sysconfig.get_config_var("EXT_SUFFIX"))
+    if os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), os.path.getmtime(LIB_PATH)):
+        return out
+    inc = os.path.join(os.path.dirname(_HERE), "include")
+    cmds = [[sys.executable, "-m", "cython", "-3", "-I", inc, src, "-o", c_file],
+            ["gcc", "-shared", "-fPIC", "-O2", "-Wno-unused-function", "-I", inc, "-I", sysconfig.get_paths()["include"],
+             c_file, "-L", _HERE, "-lsa_cuda", "-Wl,-rpath,$ORIGIN", "-o", out]]
+    for cmd in cmds:
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("building suffix_array_cy failed:\n" + " ".join(cmd) + "\n" + r.stdout[-3000:] + r.stderr[-3000:])
+    return out
 
 
 _lib = None

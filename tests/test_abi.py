@@ -79,3 +79,19 @@ def test_multi_column_entry_validates_before_touching_the_device():
     assert L.sa_build_csv(None, b"x.csv", b"name", 0) == -1
     assert L.sa_shard_begin_csv(None, b"x.csv", b"name", 0) == -1
     assert L.sa_shard_text_size(None) == 0
+
+
+def test_cython_host_side_builds_and_fails_loudly_without_gpu():
+    """suffix_array_cy.pyx (the reference's Cython class over sa_cuda.h) cythonizes, compiles and links
+    against the in-tree libsa_cuda.so; it exposes the reference's method names; without a device the
+    constructor raises (no CPU fallback)."""
+    path = S.build_cython_extension()
+    assert os.path.exists(path)
+    from suffixarray_b200 import suffix_array_cy as cy
+    for name in ("construct_truncated_suffix_array_documents", "construct_truncated_suffix_array_from_csv",
+                 "query_records", "query_records_batch", "save", "load", "suffix_array"):
+        assert hasattr(cy.SuffixArray, name), name
+    if not _cuda_available():
+        with pytest.raises(cy.SaCudaError) as ei:
+            cy.SuffixArray(documents=["a", "b"], max_suffix_length=8)
+        assert ei.value.code == -3 and "no CPU fallback" in str(ei.value)
