@@ -19,9 +19,12 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module")
 def CySuffixArray():
-    from suffixarray_b200 import _lib
-    _lib.build_cython_extension()                 # no-op when the in-tree extension is current
-    from suffixarray_b200.suffix_array_cy import SuffixArray
+    try:                                           # the in-tree extension travels with the snapshot
+        from suffixarray_b200.suffix_array_cy import SuffixArray
+    except ImportError:
+        from suffixarray_b200 import _lib
+        _lib.build_cython_extension()
+        from suffixarray_b200.suffix_array_cy import SuffixArray
     return SuffixArray
 
 
