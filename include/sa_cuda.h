@@ -93,7 +93,9 @@ int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32
  * (engine.h:209-215) but indexes search_cols[0] only (engine.c:1476; suffix_array.pyx:197 "TODO:
  * Allow multiple columns").  The file is read, uploaded and analysed once (quote parity, delimiter
  * counts, row table); each column then costs its emit pass, its build and its remap.
- * sa_build_csv(idx, path, column, flags) == sa_build_csv_columns(&idx, &column, 1, path, flags). */
+ * sa_build_csv(idx, path, column, flags) == sa_build_csv_columns(&idx, &column, 1, path, flags).
+ * Every column name is resolved before anything is touched; if a later stage fails, the handles of
+ * the columns already finished stay built and the others are left unbuilt (sa_size() == 0). */
 int sa_build_csv_columns(sa_index* const* idxs, const char* const* columns, uint32_t ncols, const char* csv_path,
                          uint32_t flags);
 
