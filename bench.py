@@ -537,15 +537,12 @@ class _DeviceU32:
         self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
 
 
-def verify_properties(builder, d_text, n, dev, world):
-    """Checks that need no reference array (SURVEY 8(c)-iii), on the device, in chunks:
-    the array is a permutation of [0, n); K(SA[i]) <= K(SA[i+1]) for the masked big-endian key K of
-    the first 8 bytes (ORDER-E refines this order, it never contradicts it); all replicas agree."""
+def array_properties(sa, d_text, n, chunk=1 << 25):
+    """sa: int32 tensor (u32 bit patterns) of n entries, d_text: uint8 tensor of the n text bytes, both on
+    one device.  -> (is a permutation of [0, n), masked first-8-byte keys non-decreasing or None for
+    non-ASCII text, 2-word digest).  Chunked: scratch is 8 index words per entry of a chunk."""
     import torch
-    import torch.distributed as dist
-    from suffixarray_b200 import _lib as S
-    sa = torch.as_tensor(_DeviceU32(S.lib().sa_device_sa(builder.idx._h), n), device=dev)
-    CH = 1 << 25
+    dev = d_text.device
     seen = torch.zeros(n, dtype=torch.uint8, device=dev)
     text = torch.cat([d_text, torch.zeros(8, dtype=torch.uint8, device=dev)])
     ar8 = torch.arange(8, device=dev, dtype=torch.int64)
@@ -553,9 +550,11 @@ def verify_properties(builder, d_text, n, dev, world):
     sorted_ok, prev_last = True, None
     digest = torch.zeros(2, dtype=torch.int64, device=dev)
     ascii_only = bool((d_text < 128).all())
-    for a in range(0, n, CH):
-        z = min(n, a + CH)
+    for a in range(0, n, chunk):
+        z = min(n, a + chunk)
         pos = sa[a:z].to(torch.int64) & 0xFFFFFFFF
+        if bool((pos >= n).any()):
+            return False, False if ascii_only else None, digest
         seen[pos] = 1
         weight = torch.arange(a, z, device=dev, dtype=torch.int64) % 1000003 + 1
         digest[0] += (pos * weight).sum()
@@ -572,13 +571,24 @@ def verify_properties(builder, d_text, n, dev, world):
             prev_last = key[-1].clone()
             del b, term, after, key
         del pos, weight
-    perm_ok = bool(seen.all())
+    return bool(seen.all()), (sorted_ok if ascii_only else None), digest
+
+
+def verify_properties(builder, d_text, n, dev, world):
+    """Checks that need no reference array (SURVEY 8(c)-iii), on the device, in chunks:
+    the array is a permutation of [0, n); K(SA[i]) <= K(SA[i+1]) for the masked big-endian key K of
+    the first 8 bytes (ORDER-E refines this order, it never contradicts it); all replicas agree."""
+    import torch
+    import torch.distributed as dist
+    from suffixarray_b200 import _lib as S
+    sa = torch.as_tensor(_DeviceU32(S.lib().sa_device_sa(builder.idx._h), n), device=dev)
+    perm_ok, sorted_ok, digest = array_properties(sa, d_text, n)
     all_dg = [torch.zeros_like(digest) for _ in range(world)]
     dist.all_gather(all_dg, digest)
-    flags = torch.tensor([int(perm_ok), int(sorted_ok)], dtype=torch.int32, device=dev)
+    flags = torch.tensor([int(perm_ok), int(sorted_ok is not False)], dtype=torch.int32, device=dev)
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     return {"n": int(n), "permutation_on_every_rank": bool(flags[0].item()),
-            "first_8_byte_keys_non_decreasing_on_every_rank": bool(flags[1].item()) if ascii_only else None,
+            "first_8_byte_keys_non_decreasing_on_every_rank": bool(flags[1].item()) if sorted_ok is not None else None,
             "replicas_equal": all(bool(torch.equal(all_dg[0], x)) for x in all_dg),
             "positions_above_2^31": int(max(0, n - (1 << 31)))}
 

@@ -239,3 +239,30 @@ def test_gloo_sample_sort_choreography(tmp_path, world):
     res = json.loads(line[len("RESULT"):])
     assert res["ok"] and res["world"] == world
     assert {"split", "exchange", "sort+refine", "edges", "finish", "gather", "adopt"} <= set(res["phases"])
+
+
+def test_array_properties_check_used_above_2_31():
+    """bench.py --verify-properties (the checks for indexes too large for any reference array): on the
+    oracle's array they hold; a swap of two entries breaks the key order, a duplicate the permutation."""
+    import numpy as np
+    import torch
+    sys.path.insert(0, ROOT)
+    import bench
+    from oracle import pyoracle as O
+    from suffixarray_b200 import workloads as W
+    text = W.english_documents(120_000, seed=11)
+    want = O.oracle_build(text, 32)
+    t = torch.from_numpy(text)
+    good = torch.from_numpy(want.view(np.int32).copy())
+    perm, order, dg = bench.array_properties(good, t, int(text.size), chunk=1 << 14)
+    assert perm and order
+    swapped = good.clone()
+    swapped[1000], swapped[90_000] = good[90_000].item(), good[1000].item()
+    perm2, order2, dg2 = bench.array_properties(swapped, t, int(text.size), chunk=1 << 14)
+    assert perm2 and not order2 and not torch.equal(dg, dg2)
+    dup = good.clone()
+    dup[5] = good[6]
+    assert not bench.array_properties(dup, t, int(text.size), chunk=1 << 14)[0]
+    raw = torch.from_numpy(np.random.default_rng(1).integers(0, 256, 5000).astype(np.uint8))
+    sa_raw = torch.from_numpy(O.oracle_build(raw.numpy(), 32).view(np.int32).copy())
+    assert bench.array_properties(sa_raw, raw, 5000)[1] is None          # non-ASCII text: key check not applicable
