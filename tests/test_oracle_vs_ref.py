@@ -114,3 +114,47 @@ def test_newline_prefix_closed_form():
         assert np.array_equal(O.oracle_build(T, 32).astype(np.int64), want), j
         if O.have_ref():
             assert np.array_equal(O.ref_build(T, 32).astype(np.int64), want), j
+
+
+HAND_WRITTEN_CSV = {
+    "plain": b"a,b,c\nx1,y1,z1\nx2,y2,z2\n",
+    "no_trailing_newline": b"a,b,c\nx1,y1,z1\nx2,y2,z2",
+    "no_trailing_newline_quoted": b'a,b,c\nx1,y1,"z,1"\nx2,y2,"z2"',
+    "ends_with_comma": b"a,b,c\nx1,y1,z1\nx2,y2,",
+    "empty_cells": b"a,b,c\n,,\nx,,z\n,y,\n",
+    "quoted": b'a,b,c\n"hello, world",y1,"z""1"\n"",y2,"""q"""\n"multi\nline",y3,z3\n',
+    "upper_and_crlf": b'a,b,c\r\nHeLLo,"WORLD",Z\r\n"Fo""O",Bar,baz\r\n',
+    "ragged_rows": b"a,b,c\nx1,y1\nx2,y2,z2,w2\nx3\n",
+    "one_column": b"a\nfoo\nbar\n\nbaz\n",
+    "only_header": b"a,b,c\n",
+    "only_header_no_newline": b"a,b,c",
+    "escaped_pairs_at_edges": b'a,b\n"""x""","y"""\n"""""",""""\n',
+    "high_bytes": b"a,b\n\xff\xfe,caf\xc3\xa9\n\x80,\x7f\n",
+    "multiline_cells": b'a,b,c\n"line one\nline two",y1,z1\nx2,"p\nq\nr",z2\nx3,y3,"tail\ncell"\nx4,y4,z4\n',
+    "crlf_multiline": b'a,b,c\r\nHeLLo,"WOR\r\nLD",Z\r\nfoo,Bar,baz\r\n',
+}
+
+
+@needs_ref
+@pytest.mark.parametrize("name", sorted(HAND_WRITTEN_CSV))
+def test_csv_oracle_matches_reference_on_hand_written_files(name):
+    """The files the GPU column scanner is checked on (tests/test_gpu_csv_scan.py REGULAR,
+    tests/test_gpu_csv_columns.py FILES) through the UNMODIFIED reference: text length, remapped array
+    and quoted bits of every column.  (The reference keeps the '\\r' of a CRLF header line in the last
+    column's name, engine.c:40-44 -- it is asked for that name; libsa_cuda strips it.)"""
+    data = HAND_WRITTEN_CSV[name]
+    first = data.split(b"\n")[0]
+    header = first.rstrip(b"\r").decode().split(",")
+    with tempfile.NamedTemporaryFile(suffix=".csv", delete=False) as f:
+        f.write(data)
+        path = f.name
+    try:
+        for col, cname in enumerate(header):
+            text, mp, qd = O.oracle_csv_scan(data, col, len(header))
+            sa_file, q_rank = O.oracle_csv_remap(O.oracle_build(text, 32), mp, qd)
+            ref_name = cname + "\r" if (first.endswith(b"\r") and col == len(header) - 1) else cname
+            rsa, rq = O.ref_csv_build(path, ref_name, 32, cap=len(data) + 64)
+            assert rsa.size == text.size, cname
+            assert np.array_equal(sa_file, rsa) and np.array_equal(q_rank, rq), cname
+    finally:
+        os.unlink(path)
