@@ -158,3 +158,36 @@ def test_csv_oracle_matches_reference_on_hand_written_files(name):
             assert np.array_equal(sa_file, rsa) and np.array_equal(q_rank, rq), cname
     finally:
         os.unlink(path)
+
+
+@needs_ref
+def test_csv_oracle_matches_reference_on_random_files():
+    """60 random RFC-4180 files (1-4 columns, cells over a small alphabet that includes , " and raw
+    newlines, written by Python's csv module; every third one without a trailing newline): the oracle's
+    scan + build + remap equals the unmodified reference for every column."""
+    import csv
+    import io
+    rng = np.random.default_rng(123)
+    alpha = list('abcXYZ ,"\n.')
+    for trial in range(60):
+        ncols = int(rng.integers(1, 5))
+        header = [f"c{i}" for i in range(ncols)]
+        rows = [header] + [["".join(rng.choice(alpha, size=int(rng.integers(0, 9)))) for _ in range(ncols)]
+                           for _ in range(int(rng.integers(1, 40)))]
+        buf = io.StringIO()
+        csv.writer(buf, lineterminator="\n").writerows(rows)
+        data = buf.getvalue().encode()
+        if trial % 3 == 0:
+            data = data[:-1]
+        with tempfile.NamedTemporaryFile(suffix=".csv", delete=False) as f:
+            f.write(data)
+            path = f.name
+        try:
+            for col, cname in enumerate(header):
+                text, mp, qd = O.oracle_csv_scan(data, col, ncols)
+                sa_file, q_rank = O.oracle_csv_remap(O.oracle_build(text, 32), mp, qd)
+                rsa, rq = O.ref_csv_build(path, cname, 32, cap=len(data) + 64)
+                assert rsa.size == text.size, (trial, cname)
+                assert np.array_equal(sa_file, rsa) and np.array_equal(q_rank, rq), (trial, cname)
+        finally:
+            os.unlink(path)
