@@ -201,3 +201,52 @@ def model_build(text, L: int, trace=None) -> np.ndarray:
         return np.arange(n, dtype=np.uint32)
     SA, lcp = refine_state(T, n, lprime, trace=trace)
     return finish(T, SA, lcp, n, lprime, trace=trace).astype(np.uint32)
+
+
+# ------------------------------------------------------------------------------ CSV column scan (csv_scan.cu)
+CSV_IRREGULAR_NUL = 1
+CSV_IRREGULAR_QUOTE = 2
+
+
+def csv_scan_model(data: bytes, wanted: int, num_columns: int):
+    """NumPy twin of the device column scanner (csrc/csv_scan.cu: quote parity -> unquoted delimiter
+    counts -> emit): the reference's byte state machine (engine.c:522-605) restated as prefix sums,
+    with the same irregularity flags.  -> (flags, text u8, map u32 with the quoted flag in bit 31).
+    For flags == 0 the streams must equal sao_csv_scan's (tests/test_model.py)."""
+    f = np.frombuffer(data, np.uint8)
+    size = f.size
+    flags = CSV_IRREGULAR_NUL if (f == 0).any() else 0
+    q = f == 34
+    inq_before = ((np.cumsum(q) - q) & 1).astype(bool)                 # in quotes in front of byte p
+    draw = (f == 44) | (f == 10)
+    d = draw & ~inq_before                                             # delimiters outside quotes
+    col = (np.cumsum(d) - d) % num_columns                             # a delimiter belongs to the cell it ends
+    prev = np.concatenate([[44], f[:-1]]) if size else f               # the file start behaves like a cell start
+    nxt = np.concatenate([f[1:], [0]]) if size else f
+    qprev, qnext = prev == 34, nxt == 34
+    opening, closing = q & ~inq_before, q & inq_before
+    if (opening & ~((prev == 44) | (prev == 10) | qprev)).any():
+        flags |= CSV_IRREGULAR_QUOTE
+    dnext = (nxt == 44) | (nxt == 10)
+    if size:
+        dnext[-1] = True                                               # the byte behind the last one counts as a delimiter
+    if (closing & ~(dnext | qnext)).any():
+        flags |= CSV_IRREGULAR_QUOTE
+    if int(q.sum()) & 1:
+        flags |= CSV_IRREGULAR_QUOTE                                   # unterminated quote
+    escaped = closing & qnext                                          # first quote of a "" pair inside quotes
+    emit = (col == wanted) & (~q | escaped)
+    p = np.flatnonzero(emit)
+    c = f[p].copy()
+    up = (c >= 65) & (c <= 90) & ~d[p]
+    c[up] += 32
+    c[d[p]] = 10                                                       # the cell's delimiter -> row sentinel
+    qf = np.where(d[p], qprev[p], inq_before[p]).astype(np.uint32)
+    mp = p.astype(np.uint32) | (qf << np.uint32(31))
+    if size:                                                           # end of the file inside the wanted cell
+        last = int(f[-1])
+        last_is_delim = last in (44, 10) and not inq_before[-1]
+        if not last_is_delim and int(d.sum()) % num_columns == wanted:
+            c = np.concatenate([c, [10]]).astype(np.uint8)
+            mp = np.concatenate([mp, [np.uint32(size) | (np.uint32(1 << 31) if last == 34 else np.uint32(0))]]).astype(np.uint32)
+    return flags, c.astype(np.uint8), mp.astype(np.uint32)
