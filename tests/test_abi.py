@@ -95,3 +95,18 @@ def test_cython_host_side_builds_and_fails_loudly_without_gpu():
         with pytest.raises(cy.SaCudaError) as ei:
             cy.SuffixArray(documents=["a", "b"], max_suffix_length=8)
         assert ei.value.code == -3 and "no CPU fallback" in str(ei.value)
+
+
+def test_library_is_usable_from_plain_c(tmp_path):
+    """tests/c_abi_smoke.c: compiled with gcc against include/sa_cuda.h and the in-tree library -- no
+    Python or torch types anywhere in the boundary.  On a machine without a GPU it must report the loud
+    failure of sa_create; with one it builds and queries "banana\\nbandana" and checks the known answers."""
+    import subprocess
+    exe = str(tmp_path / "c_abi_smoke")
+    libdir = os.path.dirname(S.LIB_PATH)
+    r = subprocess.run(["gcc", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "c_abi_smoke.c"),
+                        "-L", libdir, "-lsa_cuda", f"-Wl,-rpath,{libdir}", "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    assert r.stdout.startswith("ok" if _cuda_available() else "nogpu"), r.stdout
