@@ -250,3 +250,36 @@ def csv_scan_model(data: bytes, wanted: int, num_columns: int):
             c = np.concatenate([c, [10]]).astype(np.uint8)
             mp = np.concatenate([mp, [np.uint32(size) | (np.uint32(1 << 31) if last == 34 else np.uint32(0))]]).astype(np.uint32)
     return flags, c.astype(np.uint8), mp.astype(np.uint32)
+
+
+# ------------------------------------------------------------------------------ finish, per-rank rules (finish.cu)
+def finish_flat(T, SA, lcp, n, lprime, lo=0, hi=None):
+    """finish() the way finish_kernel decides it -- per rank, with no walk from rank 0: rank j heads a
+    bucket iff lcp[j] < d*(j); a bucket is re-sorted iff d* < L', it has two members or more and its
+    shared prefix holds no terminator.  Only ranks in [lo, hi) are placed (the rest of `out` keeps the
+    input order): with SA / lcp = [left halo | own shard | right halo] this is the sharded finish
+    (sa_shard.cu), which must reproduce the slice of the global result when the halos are >= 96 ranks
+    (or reach the ends of the array)."""
+    hi = n if hi is None else hi
+    dstar = dstar_from_lcp(lcp, n)
+    out = SA.copy()
+    head = np.ones(n, dtype=bool)
+    head[1:] = lcp[1:n] < dstar[1:]
+    starts = np.flatnonzero(head)
+    ends = np.concatenate([starts[1:], [n]])
+    for r, e1 in zip(starts.tolist(), ends.tolist()):
+        if e1 <= lo or r >= hi:
+            continue
+        d, size = int(dstar[r]), e1 - r
+        if d >= lprime or size < 2:
+            continue
+        assert size <= SMALL, (r, e1, d)
+        p0 = int(SA[r])
+        pref = T[p0: p0 + d]
+        if ((pref == 10) | (pref == 255)).any():
+            continue
+        members = sorted((int(x) for x in SA[r: e1]), key=lambda p: (w17_key(T, p + d, lprime), p))
+        for x, p in zip(range(r, e1), members):
+            if lo <= x < hi:
+                out[x] = p
+    return out

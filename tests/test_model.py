@@ -62,3 +62,26 @@ def test_csv_scan_model_equals_oracle_or_flags_the_file():
             assert np.array_equal(mp & 0x7FFFFFFF, want_map), (trial, col, data)
             assert np.array_equal((mp >> 31).astype(np.uint8), want_q), (trial, col, data)
     assert regular > 300 and irregular > 50
+
+
+def test_finish_per_rank_rules_and_128_record_halos():
+    """(a) finish_kernel's per-rank bucket rule (head iff lcp < d*) gives the sequential walk's result;
+    (b) the sharded finish: a shard extended by min(128, what exists) records on either side, finished
+    on its own, reproduces its slice of the global result -- for random shard boundaries, including
+    ones inside tied buckets and shards shorter than the halo (sa_shard.cu, sharded.EDGE)."""
+    rng = np.random.default_rng(21)
+    EDGE = 128
+    for sigma, n, L in ((2, 3000, 32), (3, 5000, 16), (4, 4000, 64), (26, 6000, 32), (2, 700, 8), (3, 90, 32)):
+        text = random_text(rng, n, sigma, newline_p=0.03)
+        lprime = min(L, n)
+        T = M.padded(text)
+        SA, lcp = M.refine_state(T, n, lprime)
+        want = M.finish(T, SA, lcp, n, lprime)
+        assert np.array_equal(M.finish_flat(T, SA, lcp, n, lprime), want), (sigma, n, L)
+        assert np.array_equal(want.astype(np.uint32), O.oracle_build(text, L))
+        cuts = sorted(set([0, n] + rng.integers(0, n + 1, size=12).tolist() + [n // 2, n // 2 + 1, n // 2 + 40]))
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            hl, hr = min(EDGE, a), min(EDGE, n - b)
+            ext_sa, ext_lcp = SA[a - hl: b + hr].copy(), lcp[a - hl: b + hr].copy()
+            got = M.finish_flat(T, ext_sa, ext_lcp, ext_sa.size, lprime, lo=hl, hi=hl + (b - a))
+            assert np.array_equal(got[hl: hl + (b - a)], want[a:b]), (sigma, n, L, a, b)
