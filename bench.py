@@ -498,22 +498,23 @@ def run_ours_global(args, world, rank, local):
         range_e2e_ms, range_dev_ms = (sums[5:7] / K).tolist()
         phases = {p: round(v / K, 3) for p, v in zip(phase_names, sums[7:].tolist())}
         result = assemble(args, world, recs, n // world, nq, float(n), float(nq * world), build_ms, query_ms,
-                          build_e2e_ms, query_e2e_ms, sums[4].item(), clocks, qbytes.size, None, None, None, lower,
+                          build_e2e_ms, query_e2e_ms, sums[4].item(), clocks, qbytes.size, text_r, qbytes, qoff, lower,
                           range_e2e_ms, range_dev_ms)
         result["e2e"]["h2d_bytes_per_step"] = int(n + qbytes.size + (nq + 1) * 8)     # per rank: the replicated text
         shard_sizes = [int(x[0].item()) for x in ms_all]
         xbytes = [int(x[1].item()) for x in ms_all]
         xms = phases.get("exchange", 0.0)
-        result["config"]["sharding"] = ("one global index over the N concatenated partitions: sample sort, splitters from "
+        result["config_detail"] = {}
+        result["config_detail"]["sharding"] = ("one global index over the N concatenated partitions: sample sort, splitters from "
                                         "the all-reduced 65536-bin key histogram, one exchange of (key, pos) records, "
                                         "128-record halos for the bucket finish, " +
                                         ("each shard finished in chunks straight into the final array while the previous chunk is copied "
                                          "into every peer's array over NVLink (CUDA IPC, one stream per peer)"
                                          if args.replicate == "fused" else "NCCL all-gather of the slices"))
-        result["config"]["exchange"] = ("split kernel stores records straight into the destination GPU's sort buffers "
+        result["config_detail"]["exchange"] = ("split kernel stores records straight into the destination GPU's sort buffers "
                                         "(CUDA IPC peer stores over NVLink)" if args.exchange == "p2p"
                                         else "split into send buffers + NCCL all_to_all_single")
-        result["config"]["n_chars_total"] = n
+        result["config_detail"]["n_chars_total"] = n
         result["timing"] = "wall clock between barrier + cudaDeviceSynchronize pairs, max over ranks (the build is host-driven across collectives)"
         if verify is not None:
             result["verify"] = verify
@@ -594,19 +595,24 @@ def verify_properties(builder, d_text, n, dev, world):
 
 
 # ------------------------------------------------------------------------------ CPU reference legs
-def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample=200_000, threads=0,
-                        record_sample=20_000):
+def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample=0, threads=0,
+                        record_sample=20_000, keep=False):
     """Times the reference's own CPU path (engine.c through oracle/_ref/libsa_ref.so when present,
-    else the oracle port) on the host cores.  -> dict."""
+    else the oracle port) on the host cores.  query_sample = 0: the whole batch.  The OpenMP
+    thread count is set explicitly to the cores this process may run on (torch.distributed.run
+    exports OMP_NUM_THREADS=1 to its workers).  keep=True also returns what the parity check
+    needs (the text as indexed, the reference's array and ranges).  -> dict."""
     from oracle import pyoracle as O
     nq_all = int(qoff.size - 1)
-    nqs = min(nq_all, query_sample)
+    nqs = min(nq_all, query_sample) if query_sample else nq_all
     low = O.oracle_lowercase(text) if lower else text
     n = int(low.size)
     kind = "reference" if O.have_ref() else "port"
-    cores = O.ref_max_threads() if kind == "reference" else 1
+    cores = (threads or O.ref_use_all_cores()) if kind == "reference" else 1
     rec = {"record_sample": 0, "record_s": 0.0, "records": 0}
+    kept = None
     if kind == "reference":
+        O.ref_lib().ref_set_threads(cores)
         # The CPU arm indexes '\n' + text (one empty leading record): get_matching_records scans back
         # to the previous '\n' with a uint32 offset (engine.c:1189-1191) and leaves the buffer for any
         # hit in record 0.  [ text' | 64 zero bytes | '\n' | slack ] keeps the forward scan
@@ -624,7 +630,7 @@ def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample
             t0 = time.perf_counter()
             O.ref_build_padded(tp, n, L, sa)
             best = min(best, time.perf_counter() - t0)
-        # query sample: NUL-terminated C strings, an omp parallel-for over the batch
+        # query batch: NUL-terminated C strings, an omp parallel-for over the batch
         lens = (qoff[1:nqs + 1] - qoff[:nqs]).astype(np.int64)
         zoff = np.zeros(nqs + 1, dtype=np.uint64)
         np.cumsum(lens + 1, out=zoff[1:].view(np.int64))
@@ -632,8 +638,8 @@ def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample
         src = qbytes[: int(qoff[nqs])]
         dst_idx = np.arange(src.size, dtype=np.int64) + np.repeat(np.arange(nqs, dtype=np.int64), lens)
         zbytes[dst_idx] = src
-        start = np.empty(nqs, dtype=np.uint32)
-        end = np.empty(nqs, dtype=np.uint32)
+        start = np.full(nqs, 0xFFFFFFFF, dtype=np.uint32)
+        end = np.full(nqs, 0xFFFFFFFF, dtype=np.uint32)
         skipped = np.zeros(nqs, dtype=np.uint8)
         import ctypes as C
         rl = O.ref_lib()
@@ -641,15 +647,17 @@ def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample
         t0 = time.perf_counter()
         rl.ref_query_batch(tp.ctypes.data, sa.ctypes.data_as(u32p), n, L, zbytes.ctypes.data,
                            zoff.ctypes.data_as(u64p), nqs, start.ctypes.data_as(u32p), end.ctypes.data_as(u32p),
-                           skipped.ctypes.data_as(u8p), threads)
+                           skipped.ctypes.data_as(u8p), cores)
         tq = time.perf_counter() - t0
         # record path: get_matching_records (bisection + newline scans + malloc/memcpy per hit), smaller sample
         nrec = min(nqs, record_sample)
         hits = np.zeros(max(nrec, 1), dtype=np.uint32)
         t0 = time.perf_counter()
         total = rl.ref_query_records_batch(tp.ctypes.data, sa.ctypes.data_as(u32p), n, L, zbytes.ctypes.data,
-                                           zoff.ctypes.data_as(u64p), nrec, K_HITS, hits.ctypes.data_as(u32p), threads)
+                                           zoff.ctypes.data_as(u64p), nrec, K_HITS, hits.ctypes.data_as(u32p), cores)
         rec = {"record_sample": nrec, "record_s": time.perf_counter() - t0, "records": int(total)}
+        if keep:
+            kept = {"text": tp[:n], "sa": sa, "start": start, "end": end, "skipped": skipped, "nq": nqs}
     else:
         t0 = time.perf_counter()
         sa = O.oracle_build(low, L)
@@ -657,13 +665,56 @@ def cpu_reference_times(text, qbytes, qoff, lower, L, build_reps=1, query_sample
         from suffixarray_b200 import workloads as W
         qs = W.unpack_queries(qbytes[: int(qoff[nqs])], qoff[: nqs + 1])
         t0 = time.perf_counter()
-        O.oracle_query(low, sa, L, qs)
+        ws, we = O.oracle_query(low, sa, L, qs)
         tq = time.perf_counter() - t0
+        if keep:
+            kept = {"text": low, "sa": sa, "start": ws, "end": we, "skipped": np.zeros(nqs, np.uint8), "nq": nqs}
     out = {"kind": kind, "cores": int(cores), "n": n, "build_s": best, "build_mchars_s": n / best / 1e6,
            "query_sample": nqs, "query_s": tq, "queries_per_s": nqs / tq}
     out.update(rec)
     out["record_queries_per_s"] = rec["record_sample"] / rec["record_s"] if rec["record_s"] > 0 else None
+    if keep:
+        out["kept"] = kept
     return out
+
+
+def parity_check(kept, qbytes, qoff, L, device):
+    """The bench's own parity gate: the SAME text the CPU arm indexed is built on the GPU (outside the
+    timed region) and the arrays are compared entry by entry; so are the rank ranges of every query
+    the reference answered without its out-of-bounds wrap, and the hit lists of a 5 000-query sample."""
+    from oracle import pyoracle as O
+    from suffixarray_b200 import _lib as S
+    idx = S.Index(L, device=device)
+    idx.build_text(kept["text"])
+    sa_equal = bool(np.array_equal(idx.sa(), kept["sa"]))
+    nq = kept["nq"]
+    s, e, off = idx.query_ranges_packed(qbytes[: max(int(qoff[nq]), 1)], qoff[: nq + 1], k=K_HITS)
+    keep = kept["skipped"] == 0
+    ranges_equal = bool(np.array_equal(s[keep], kept["start"][keep]) and np.array_equal(e[keep], kept["end"][keep]))
+    pos, doc = idx.query_hits(int(off[-1]))
+    pick = np.flatnonzero(keep)[:5000]
+    woff, wpos, wdoc = O.oracle_hits(kept["text"], kept["sa"], kept["start"][pick], kept["end"][pick], K_HITS)
+    hits_equal = True
+    for t, q in enumerate(pick.tolist()):
+        a, b, wa, wb = int(off[q]), int(off[q + 1]), int(woff[t]), int(woff[t + 1])
+        if b - a != wb - wa or not np.array_equal(pos[a:b], wpos[wa:wb]) or not np.array_equal(doc[a:b], wdoc[wa:wb]):
+            hits_equal = False
+            break
+    idx.close()
+    return {"sa_equal": sa_equal, "n": int(kept["sa"].size), "ranges_equal": ranges_equal,
+            "queries_compared": int(keep.sum()), "queries_skipped_reference_wrap": int((~keep).sum()),
+            "hit_lists_equal": hits_equal, "hit_lists_compared": int(pick.size),
+            "against": "oracle/_ref (engine.c)" if O.have_ref() else "oracle port"}
+
+
+def make_config(args, world, n, nq):
+    """The workload description, identical in both arms (`ours` and `--impl reference`)."""
+    glob = world > 1 and args.mode == "global"
+    return {"workload": WORKLOADS[args.workload][2], "name": args.workload, "n_chars_per_gpu": int(n),
+            "queries_per_gpu": int(nq), "max_suffix_length": args.max_suffix_length, "k": K_HITS,
+            "sharding": ("one global index over the N concatenated per-GPU texts (sample sort)" if glob else
+                         "one independent partition per GPU (suffix_array.pyx:148-180)"),
+            "l2": "inputs larger than L2 (keys 8n + positions 4n = 1.2 GB per pass vs 126 MB L2)"}
 
 
 def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_e2e_ms, query_e2e_ms, wall_ms,
@@ -696,10 +747,8 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8 text / u64 keys / u32 positions (integer compare + scatter)",
         "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload][2], "name": args.workload, "n_chars_per_gpu": n,
-                   "queries_per_gpu": nq, "max_suffix_length": args.max_suffix_length, "k": K_HITS,
-                   "hits_per_batch": hits, "sharding": "one independent partition per GPU (suffix_array.pyx:148-180)",
-                   "l2": "inputs larger than L2 (keys 8n + positions 4n = 1.2 GB per pass vs 126 MB L2)"},
+        "config": make_config(args, world, n, nq),
+        "hits_per_batch": hits,
         "e2e": {"value": round(n_all / (build_e2e_ms * 1e-3) / 1e6, 2), "unit": "Mchars/s (SA build)",
                 "queries_per_s": round(nq_all / (range_e2e_ms * 1e-3), 1),
                 "record_queries_per_s": round(nq_all / (query_e2e_ms * 1e-3), 1),
@@ -731,23 +780,51 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
         out["e2e"]["build_plus_sa_d2h_mchars_per_s"] = round(n_all / ((build_e2e_ms + SA_D2H["ms"]) * 1e-3) / 1e6, 2)
         out["e2e"]["sa_d2h_note"] = ("sa_copy_sa_u32 into a pinned buffer, per GPU, outside the timed region (SURVEY 8(d): "
                                      "text H2D is inside `build_ms`, the array's D2H is reported apart and combined here)")
-    if world == 1 and not args.no_cpu_baseline:
-        cb = cpu_reference_times(text, qbytes, qoff, lower, args.max_suffix_length)
+    # query kernel against its roofline (SURVEY 8(d) B_query): per query 2*ceil(log2 n) probes, each an
+    # SA entry (4 B) + the compared window (c = min(|q|, L) bytes), + the 16-byte result; the sector
+    # figure counts what the memory system moves for them (32 B per SA entry, 32*(ceil(c/32)+1) per window)
+    if qoff is not None and range_dev_ms > 0:
+        import math
+        n_index = n * world if (world > 1 and args.mode == "global") else n
+        probes = 2 * math.ceil(math.log2(max(n_index, 2)))
+        lens = np.minimum((qoff[1:] - qoff[:-1]).astype(np.int64), args.max_suffix_length)
+        useful = float(probes) * float((4 + lens).sum()) + 16.0 * lens.size
+        sector = float(probes) * float((32 + 32 * ((lens + 31) // 32 + 1)).sum())
+        t = range_dev_ms * 1e-3
+        out["roofline_query"] = {"kernel": "query_thread_kernel (two bisections per query, one query per thread)",
+                                 "bound": "hbm", "unit": "GB/s", "peak": peak,
+                                 "achieved": round(useful / t / 1e9, 1), "frac": round(useful / t / 1e9 / peak, 4),
+                                 "sector_achieved": round(sector / t / 1e9, 1),
+                                 "sector_frac": round(sector / t / 1e9 / peak, 4),
+                                 "probes_per_query": probes, "bytes_per_query": round(useful / lens.size, 1),
+                                 "sector_bytes_per_query": round(sector / lens.size, 1), "launch_ms": round(range_dev_ms, 4),
+                                 "note": "achieved = useful bytes (probes*(4+c)+16) / kernel time; sector_* = 32-byte "
+                                         "sectors those dependent random accesses touch"}
+    if not args.no_cpu_baseline and text is not None:
+        cb = cpu_reference_times(text, qbytes, qoff, lower, args.max_suffix_length, keep=True)
         out["cpu_baseline"] = {"value": round(cb["build_mchars_s"], 2), "unit": "Mchars/s (SA build)",
                                "queries_per_s": round(cb["queries_per_s"], 1),
                                "record_queries_per_s": round(cb["record_queries_per_s"], 1) if cb["record_queries_per_s"] else None,
                                "cores": cb["cores"], "kind": cb["kind"],
-                               "sample": f"build: the full {cb['n']}-char text once ({cb['build_s']:.2f} s); "
-                                         f"queries: first {cb['query_sample']} of the batch ({cb['query_s']:.2f} s), "
+                               "sample": ("rank 0's text and batch; " if world > 1 else "") +
+                                         f"build: the full {cb['n']}-char text once ({cb['build_s']:.2f} s); "
+                                         f"queries: all {cb['query_sample']} of the batch ({cb['query_s']:.2f} s), "
                                          "get_substring_positions under an omp parallel-for; records: first "
                                          f"{cb['record_sample']} queries through get_matching_records, k = {K_HITS} "
                                          f"({cb['records']} records, {cb['record_s']:.2f} s)"}
-        if cb["kind"] == "reference":
+        try:
+            pc = parity_check(cb.pop("kept"), qbytes, qoff, args.max_suffix_length, int(os.environ.get("LOCAL_RANK", "0")))
+            out["parity_checked"] = bool(pc["sa_equal"] and pc["ranges_equal"] and pc["hit_lists_equal"])
+            out["parity"] = pc
+        except Exception as ex:      # the bench line must still be printed
+            out["parity_checked"] = False
+            out["parity"] = {"error": repr(ex)[:300]}
+        if cb["kind"] == "reference" and world == 1:
             # BASELINE.json's other CPU arm: the vendored libsais (a FULL suffix array, not ORDER-E: timing only)
             from oracle import pyoracle as O
             low = (O.oracle_lowercase(text) if lower else text)[:50_000_000]      # bounded sample
             t0 = time.perf_counter()
-            O.ref_libsais(low, threads=0)
+            O.ref_libsais(low, threads=cb["cores"])
             tl = time.perf_counter() - t0
             out["cpu_baseline"]["libsais_omp"] = {"value": round(low.size / tl / 1e6, 2), "unit": "Mchars/s (full SA, untruncated)",
                                                   "cores": cb["cores"], "seconds": round(tl, 2), "sample_chars": int(low.size),
@@ -756,37 +833,41 @@ def assemble(args, world, recs, n, nq, n_all, nq_all, build_ms, query_ms, build_
 
 
 def run_reference(args):
-    """The reference's own CPU implementation (engine.c) on the host cores: rank 0 only."""
+    """The reference's own CPU implementation (engine.c) on the host cores: rank 0 only, all the
+    cores this process may run on.  Each step = the per-GPU workload of the GPU arm's config: the
+    whole text built once + the whole query batch (+ a 20 000-query sample of the record path).  At
+    N > 1 that is rank 0's share of the N-GPU job (a 1/N sample of the global text)."""
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return None
     text, qbytes, qoff, lower = make_workload(args.workload, 0)
-    # each step = one bounded sample: build over the first `sample_n` chars + 100k queries
-    sample_n = min(int(text.size), 50_000_000)
-    text = text[:sample_n]
-    nqs = min(int(qoff.size - 1), 100_000)
+    n, nq = int(text.size), int(qoff.size - 1)
     recs = []
     for i in range(args.warmup + args.steps):
-        cb = cpu_reference_times(text, qbytes, qoff, lower, args.max_suffix_length, query_sample=nqs)
+        cb = cpu_reference_times(text, qbytes, qoff, lower, args.max_suffix_length)
         if i >= args.warmup:
             recs.append(cb)
     K = len(recs)
     bs = sum(r["build_s"] for r in recs) / K
     qs = sum(r["query_s"] for r in recs) / K
-    v = sample_n / bs / 1e6
+    v = recs[0]["n"] / bs / 1e6
     rqs = [r["record_queries_per_s"] for r in recs if r.get("record_queries_per_s")]
     rq = round(sum(rqs) / len(rqs), 1) if rqs else None
+    sample = (f"per step: construct_truncated_suffix_array over the whole {recs[0]['n']}-char text + "
+              f"get_substring_positions for all {recs[0]['query_sample']} queries of the batch (omp parallel-for) + "
+              f"get_matching_records for the first {recs[0]['record_sample']} queries" +
+              (f"; N = {world}: rank 0's share of the {world}-GPU job" if world > 1 else ""))
     return {"impl": "reference", "metric": METRIC, "value": round(v, 2), "unit": "Mchars/s (SA build)",
-            "queries_per_s": round(nqs / qs, 1), "record_queries_per_s": rq, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "queries_per_s": round(recs[0]["query_sample"] / qs, 1), "record_queries_per_s": rq, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round((bs + qs) * 1e3, 2), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8 text / u32 positions", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][2], "name": args.workload,
-                       "max_suffix_length": args.max_suffix_length},
+            "vs_baseline": None, "dtype": "u8 text / u64 keys / u32 positions (integer compare + scatter)", "data": "synthetic",
+            "config": make_config(args, world, n, nq),
             "cpu_baseline": {"value": round(v, 2), "unit": "Mchars/s (SA build)", "kind": recs[0]["kind"],
-                             "cores": recs[0]["cores"], "queries_per_s": round(nqs / qs, 1),
-                             "sample": f"per step: build over the first {sample_n} chars of the workload text + the "
-                                       f"first {nqs} queries of its batch (searched in that prefix)"},
-            "e2e": {"value": round(v, 2), "unit": "Mchars/s (SA build)", "queries_per_s": round(nqs / qs, 1),
+                             "cores": recs[0]["cores"], "queries_per_s": round(recs[0]["query_sample"] / qs, 1),
+                             "record_queries_per_s": rq, "sample": sample},
+            "e2e": {"value": round(v, 2), "unit": "Mchars/s (SA build)", "queries_per_s": round(recs[0]["query_sample"] / qs, 1),
                     "record_queries_per_s": rq, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
 

@@ -103,6 +103,8 @@ def ref_lib():
         lib.ref_libsais.restype = C.c_int
         lib.ref_max_threads.argtypes = []
         lib.ref_max_threads.restype = C.c_int
+        lib.ref_set_threads.argtypes = [C.c_int]
+        lib.ref_set_threads.restype = None
         _ref = lib
     return _ref
 
@@ -266,3 +268,12 @@ def ref_libsais(text, threads: int = 1) -> np.ndarray:
 
 def ref_max_threads() -> int:
     return int(ref_lib().ref_max_threads())
+
+
+def ref_use_all_cores() -> int:
+    """Set the OpenMP thread count of the reference library to the cores this process may run on
+    (torchrun exports OMP_NUM_THREADS=1 to its workers) -> that count."""
+    import os
+    n = len(os.sched_getaffinity(0))
+    ref_lib().ref_set_threads(n)
+    return n

@@ -155,3 +155,7 @@ int ref_libsais(const uint8_t* text, int32_t* sa, int32_t n, int threads)
 }
 
 int ref_max_threads(void) { return omp_get_max_threads(); }
+
+/* torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the timed CPU arm sets the
+ * thread count explicitly (engine.c's own `#pragma omp parallel for`s take the default). */
+void ref_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }

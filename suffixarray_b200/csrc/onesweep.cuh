@@ -12,7 +12,25 @@
 #pragma once
 #include "common.cuh"
 
+#include <atomic>
+
 namespace sa {
+
+// One cached int per CUDA device (launch configuration derived from per-device attributes:
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) and occupancy are properties of the device a
+// kernel runs on, not of the process).  0 = not computed yet; a race between two threads computes
+// the same value twice, which is harmless.
+struct PerDeviceInt {
+    std::atomic<int> v[64] = {};
+    static int dev()
+    {
+        int d = 0;
+        cudaGetDevice(&d);
+        return (d >= 0 && d < 64) ? d : 0;
+    }
+    int get() const { return v[dev()].load(std::memory_order_acquire); }
+    void set(int x) { v[dev()].store(x, std::memory_order_release); }
+};
 
 // Look-back status word of one (tile, digit): 0 = not published; bit 31 clear = the tile's own
 // count + 1; bit 31 set = inclusive prefix over tiles 0..t in the low 31 bits (a prefix is at most
@@ -497,7 +515,8 @@ cudaError_t launch_onesweep2_cfg(const uint64_t* keys_in, const uint32_t* vals_i
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(tile_counter, 0, sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
-    static int grid = 0;
+    static PerDeviceInt grid_cache;     // per device: the attribute below is per device too
+    int grid = grid_cache.get();
     if (!grid) {
         auto k1 = onesweep2_kernel<THREADS, IPT, MINB, true, RANK_MODE, LBW, PF>;
         auto k0 = onesweep2_kernel<THREADS, IPT, MINB, false, RANK_MODE, LBW, PF>;
@@ -509,6 +528,7 @@ cudaError_t launch_onesweep2_cfg(const uint64_t* keys_in, const uint32_t* vals_i
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k0, THREADS, SMEM);
         if (per_sm < 1) per_sm = 1;
         grid = sms * per_sm;
+        grid_cache.set(grid);
     }
     const uint32_t g = tiles < (uint32_t)grid ? tiles : (uint32_t)grid;
     if (identity_vals)
@@ -773,7 +793,8 @@ cudaError_t launch_onesweep4_cfg(const uint64_t* keys_in, const uint32_t* vals_i
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(tile_counter, 0, sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
-    static int grid = 0;
+    static PerDeviceInt grid_cache;     // per device: the attribute below is per device too
+    int grid = grid_cache.get();
     if (!grid) {
         auto k1 = onesweep4_kernel<IPT, MINB, true, LBW, LB_REGS>;
         auto k0 = onesweep4_kernel<IPT, MINB, false, LBW, LB_REGS>;
@@ -785,6 +806,7 @@ cudaError_t launch_onesweep4_cfg(const uint64_t* keys_in, const uint32_t* vals_i
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k0, 512, SMEM);
         if (per_sm < 1) per_sm = 1;
         grid = sms * per_sm;
+        grid_cache.set(grid);
     }
     const uint32_t g = tiles < (uint32_t)grid ? tiles : (uint32_t)grid;
     if (identity_vals)
@@ -811,13 +833,13 @@ cudaError_t launch_onesweep_cfg(const uint64_t* keys_in, const uint32_t* vals_in
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(tile_counter, 0, sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceInt attr_set;
+    if (!attr_set.get()) {
         cudaFuncSetAttribute(onesweep_kernel<THREADS, IPT, MINB, true, RANK_MODE>,
                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
         cudaFuncSetAttribute(onesweep_kernel<THREADS, IPT, MINB, false, RANK_MODE>,
                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
-        attr_set = true;
+        attr_set.set(1);
     }
     if (identity_vals)
         onesweep_kernel<THREADS, IPT, MINB, true, RANK_MODE><<<tiles, THREADS, SMEM, s>>>(

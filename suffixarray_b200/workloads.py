@@ -215,3 +215,43 @@ def csv_file_bytes(num_rows: int, seed: int = 3001, quoted_fraction: float = 0.0
             nm = b'"' + nm[:half] + b', ""' + nm[half:] + b'"" co"'
         rows.append(b"%d,%s,%s,%d" % (i, nm, cities[city[i]], score[i]))
     return b"\n".join(rows) + b"\n"
+
+
+def write_csv_file(path: str, target_mb: int, seed: int = 3001, quoted_rows_per_chunk: int = 0):
+    """C3-shaped file `name,city,score`: rows until the name column holds about target_mb MB.
+    Assembled with numpy (a Python row loop would cost minutes at 40 M rows).  With
+    quoted_rows_per_chunk > 0 every 2 M-row chunk is followed by that many rows whose name cell is
+    quoted with an embedded ',' and a doubled '""' (RFC 4180).  -> (rows, file bytes)."""
+    import os
+    suffix = np.frombuffer(b",riverton,0421", dtype=np.uint8)
+    ns = suffix.size
+    col_bytes = 0
+    total_rows = 0
+    chunk = 0
+    with open(path, "wb") as f:
+        f.write(b"name,city,score\n")
+        while col_bytes < target_mb * 1_000_000:
+            rows = int(min(2_000_000, max(1000, (target_mb * 1_000_000 - col_bytes) // 14)))
+            text, _ = company_names_joined(rows, seed=seed + 17 * chunk, upper=False)
+            text = np.concatenate([text, np.frombuffer(b"\n", np.uint8)])
+            nl = text == 10
+            k = np.cumsum(nl, dtype=np.int64)
+            dst = np.arange(text.size, dtype=np.int64) + ns * k
+            out = np.empty(text.size + ns * int(k[-1]), dtype=np.uint8)
+            out[dst] = text
+            at = dst[nl] - ns
+            out[(at[:, None] + np.arange(ns)[None, :]).ravel()] = np.tile(suffix, at.size)
+            out.tofile(f)
+            col_bytes += text.size
+            total_rows += rows
+            if quoted_rows_per_chunk:
+                names = company_names(quoted_rows_per_chunk, seed=seed + 17 * chunk + 5, upper=False)
+                blk = []
+                for nm in names:
+                    half = len(nm) // 2
+                    blk.append(b'"' + nm[:half] + b', ""' + nm[half:] + b'"" co",lakeside,0007')
+                    col_bytes += len(nm) + 11
+                f.write(b"\n".join(blk) + b"\n")
+                total_rows += quoted_rows_per_chunk
+            chunk += 1
+    return total_rows, os.path.getsize(path)

@@ -9,6 +9,7 @@ import pytest
 
 from oracle import pyoracle as O
 from suffixarray_b200 import SuffixArray
+from suffixarray_b200 import _lib as S
 from suffixarray_b200 import workloads as W
 
 pytestmark = pytest.mark.gpu
@@ -143,3 +144,20 @@ def test_save_load_round_trip(tmp_path):
         S.Index(16).load(str(tmp_path / "csv.sa"))        # max_suffix_length mismatch
     a.close()
     b.close()
+
+
+def test_two_devices_in_one_process():
+    """launch configuration (dynamic shared-memory opt-in, occupancy grid) is cached per
+    DEVICE, so a second index on another GPU of the same process builds too."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs in one process")
+    rng = np.random.default_rng(5)
+    t = (rng.integers(0, 4, size=300_000) + ord("a")).astype(np.uint8)
+    t[rng.random(t.size) < 0.02] = 10
+    want = O.oracle_build(t, 32)
+    for dev in (0, 1, 0):
+        idx = S.Index(32, device=dev)
+        idx.build_text(t)
+        assert np.array_equal(idx.sa(), want), dev
+        idx.close()
