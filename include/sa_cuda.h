@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SA_CUDA_ABI_VERSION 1
+#define SA_CUDA_ABI_VERSION 2
 
 typedef enum sa_status {
     SA_OK = 0,
@@ -128,6 +128,69 @@ int sa_query_ranges(sa_index* idx, const uint8_t* qbytes, const uint64_t* qoff, 
  * file row.  Replaces the hit loop of get_matching_records / get_matching_records_file
  * (engine.c:1185-1211, :1356-1388). */
 int sa_query_hits(sa_index* idx, uint32_t* hit_pos, uint32_t* hit_doc, uint64_t cap);
+
+/* ---- Per-call query results (ABI 2).  An sa_result owns the device scratch of ONE query batch
+ * (queries, ranges, hit offsets, hits, records), a stream and two event pairs.  Any number of
+ * threads may query one built index at the same time, each through its own sa_result (the index
+ * is only read; the reference's query functions are re-entrant in the same way, engine.c:869-999).
+ * sa_query_ranges / sa_query_hits above are the same calls on a result object the index keeps
+ * for callers that do not care (one batch at a time per index). */
+typedef struct sa_result sa_result;
+int sa_result_create(sa_index* idx, sa_result** out);
+void sa_result_destroy(sa_result* res);
+
+/* query flags */
+#define SA_QUERY_FILE_SEMANTICS 1u /* CSV index only: the probes of get_substring_positions_file
+                                      (engine.c:920-999) instead of get_substring_positions: each probe
+                                      compares the LOWER-CASED RAW FILE BYTES at offset SA[mid] (a probe that
+                                      runs past the end of a cell sees `,next cell` / `""`, not '\n' + the next
+                                      row's cell), `start` / `end` are only set when cmp == 0 (:949-958,
+                                      :983-991), the second bisection starts at first = start (:969), and a
+                                      read that crosses the end of the file keeps the bytes of the previous
+                                      probe in the tail of the compare buffer (fread into the same malloc'd
+                                      line, :943-944).  This is the only query the reference's Python class
+                                      reaches (suffix_array.pyx:221-247 -> get_matching_records_file). */
+#define SA_QUERY_DEDUPE 2u         /* sa_query_hits_r / sa_query_records_size: per query, keep the first hit (in
+                                      rank order) of every record id -- the "segmented dedupe" of the
+                                      north star.  The reference keeps duplicates (engine.c:1187), so this is
+                                      off unless asked for. */
+#define SA_RECORDS_REFERENCE_COMPAT 4u /* sa_query_records_size: cut CSV records the way
+                                      get_matching_records_file does (engine.c:1217-1323, :1369-1385): the last
+                                      byte in front of the record's '\n' is dropped (:1314 returns
+                                      `num_chars_ahead + char_idx - 1`), and for hits at file offsets >= 4096 so
+                                      is the record's first byte (:1262 starts the backward scan at
+                                      line[4095] = file[idx - 1] but :1277 subtracts one more).  Default: the
+                                      whole line without its '\n'. */
+
+int sa_query_ranges_r(sa_index* idx, sa_result* res, const uint8_t* qbytes, const uint64_t* qoff, uint64_t nq,
+                      uint32_t k, uint32_t flags, uint32_t* start, uint32_t* end, uint64_t* hit_off);
+/* Hits of the ranges held by res.  flags: SA_QUERY_DEDUPE or 0.  With dedupe the lists are compacted:
+ * hit_off_out[nq + 1] (required then, optional otherwise) receives the offsets of the lists actually
+ * written; cap must hold the un-deduplicated total (hit_off[nq] of sa_query_ranges_r). */
+int sa_query_hits_r(sa_index* idx, sa_result* res, uint32_t flags, uint32_t* hit_pos, uint32_t* hit_doc, uint64_t cap,
+                    uint64_t* hit_off_out);
+/* Record materialisation in the library (replaces the record copies of get_matching_records[_file],
+ * engine.c:1207-1210, :1382-1387, and the per-hit Python loop above them): every hit's record -- the
+ * document of a text index, the line of the FILE of a CSV index -- gathered on the device into one
+ * packed buffer.  sa_query_records_size expands the hits (flags: SA_QUERY_DEDUPE,
+ * SA_RECORDS_REFERENCE_COMPAT) and returns the number of records and of bytes;
+ * sa_query_records copies them out: record j is out[rec_off[j] .. rec_off[j + 1]) (no terminator),
+ * rec_off has num_records + 1 entries, hit_off_out[nq + 1] (optional) the per-query record offsets
+ * and hit_doc (optional) the record ids. */
+int sa_query_records_size(sa_index* idx, sa_result* res, uint32_t flags, uint64_t* num_records, uint64_t* num_bytes);
+int sa_query_records(sa_index* idx, sa_result* res, uint8_t* out, uint64_t cap_bytes, uint64_t* rec_off,
+                     uint64_t cap_records, uint64_t* hit_off_out, uint32_t* hit_doc);
+/* device time of the last ranges / hits+records calls on res (CUDA events), kernels launched */
+int sa_result_stats(const sa_result* res, float* ms_query, float* ms_hits, uint64_t* kernel_launches);
+
+/* CSV index: the row table of the file.  sa_num_rows = record ends ('\n' outside quotes) + 1;
+ * row_start[r] = offset of row r's first byte (row 0 = the header line), row_start[num_rows] = file size.
+ * Replaces the host-side newline scans of engine.c:1217-1323 for callers that cut rows themselves. */
+uint64_t sa_num_rows(const sa_index* idx);
+int sa_copy_row_starts(sa_index* idx, uint64_t* out, uint64_t cap);
+/* A CSV index restored by sa_load holds no copy of the file: attach it again (read + upload) before
+ * SA_QUERY_FILE_SEMANTICS queries or sa_query_records.  The file must be the one that was indexed. */
+int sa_attach_csv_file(sa_index* idx, const char* csv_path);
 
 /* Device-resident variants for callers that keep batches in HBM (bench `value` path). */
 int sa_query_ranges_device(sa_index* idx, const uint8_t* d_qbytes, const uint64_t* d_qoff, uint64_t nq,

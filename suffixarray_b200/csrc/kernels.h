@@ -92,3 +92,28 @@ cudaError_t sa_launch_csv_rows(const uint8_t* f, uint64_t size, const uint32_t* 
                                uint32_t* tile_r, cudaStream_t s);
 cudaError_t sa_launch_csv_rowrank(const unsigned long long* rowbits, uint64_t size, const uint32_t* tile_r, uint32_t* rowrank,
                                   cudaStream_t s);
+
+// ---- query.cu: file-semantics bisection (get_substring_positions_file, engine.c:920-999)
+cudaError_t sa_launch_query_file(const uint8_t* file, uint64_t file_size, const uint32_t* sa_file, uint32_t n,
+                                 uint32_t max_suffix_length, const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq,
+                                 uint32_t* start, uint32_t* end, cudaStream_t s);
+
+// ---- records.cu: segmented dedupe of hit lists, record table of a CSV file, record materialisation
+// in-place: per query the first ucount[q] entries of its segment of hit_pos / hit_doc become the hits
+// whose record id occurs for the first time (rank order kept).  table: scratch of 4 u32 per hit, only
+// touched by queries with more than 1024 hits.
+cudaError_t sa_launch_dedupe_mark(const uint64_t* hit_off, uint32_t nq, uint32_t* hit_pos, uint32_t* hit_doc,
+                                  uint32_t* ucount, uint32_t* table, cudaStream_t s);
+cudaError_t sa_launch_segment_compact(const uint64_t* hit_off, const uint64_t* uoff, uint32_t nq, const uint32_t* hit_pos,
+                                      const uint32_t* hit_doc, uint32_t* upos, uint32_t* udoc, cudaStream_t s);
+// positions of the set bits of a rank structure (bits: one per byte, 64 per word; rank: set bits in
+// front of every word) -> pos[rank + i]
+cudaError_t sa_launch_rank_positions(const unsigned long long* bits, const uint32_t* rank, uint64_t nwords, uint32_t* pos,
+                                     cudaStream_t s);
+// per hit: source offset + length of its record.  ends: ascending positions of the record-ending '\n'
+// (num_ends of them), total: bytes of the source (text or file); compat: see SA_RECORDS_REFERENCE_COMPAT
+cudaError_t sa_launch_record_bounds(const uint32_t* hit_pos, const uint32_t* hit_doc, uint64_t num, const uint32_t* ends,
+                                    uint64_t num_ends, uint64_t total, bool compat, unsigned long long* src_off,
+                                    uint32_t* len, cudaStream_t s);
+cudaError_t sa_launch_record_gather(const uint8_t* src, const unsigned long long* src_off, const uint64_t* rec_off,
+                                    uint64_t num, uint8_t* out, cudaStream_t s);

@@ -35,7 +35,7 @@ extern "C" int sa_build_text(sa_index* idx, const uint8_t* text, uint64_t n, uin
 {
     SA_REQUIRE(idx, SA_ERR_INVALID, "index is NULL");
     SA_REQUIRE(text || n == 0, SA_ERR_INVALID, "text is NULL");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     int rc = prepare_text(idx, n, flags);
     if (rc != SA_OK) return rc;
     idx->stats.ms_h2d = 0.f;
@@ -50,7 +50,7 @@ extern "C" int sa_build_text_device(sa_index* idx, const uint8_t* d_text, uint64
 {
     SA_REQUIRE(idx, SA_ERR_INVALID, "index is NULL");
     SA_REQUIRE(d_text || n == 0, SA_ERR_INVALID, "d_text is NULL");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     int rc = prepare_text(idx, n, flags);
     if (rc != SA_OK) return rc;
     idx->stats.ms_h2d = 0.f;
@@ -81,7 +81,7 @@ extern "C" int sa_copy_sa_u32(sa_index* idx, uint32_t* out, uint64_t cap)
     SA_REQUIRE(idx && idx->built, SA_ERR_INVALID, "index not built");
     SA_REQUIRE(out || idx->n == 0, SA_ERR_INVALID, "out is NULL");
     SA_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "cap %llu < n %llu", (unsigned long long)cap, (unsigned long long)idx->n);
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     return copy_out(idx, sa_device_sa(idx), out, (size_t)idx->n * 4);
 }
 
@@ -89,7 +89,7 @@ extern "C" int sa_copy_text_positions_u32(sa_index* idx, uint32_t* out, uint64_t
 {
     SA_REQUIRE(idx && idx->built, SA_ERR_INVALID, "index not built");
     SA_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "cap too small");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     return copy_out(idx, idx->sa_final.p, out, (size_t)idx->n * 4);
 }
 
@@ -111,7 +111,7 @@ extern "C" int sa_copy_quoted_bits(sa_index* idx, uint8_t* out_bits, uint64_t ca
     SA_REQUIRE(idx && idx->built && idx->csv, SA_ERR_INVALID, "no CSV index built");
     const uint64_t need = (idx->n + 7) / 8;
     SA_REQUIRE(cap_bytes >= need, SA_ERR_INVALID, "cap too small");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     return copy_out(idx, idx->qbits.p, out_bits, (size_t)need);
 }
 
@@ -119,7 +119,7 @@ extern "C" int sa_copy_text(sa_index* idx, uint8_t* out, uint64_t cap)
 {
     SA_REQUIRE(idx && idx->built, SA_ERR_INVALID, "index not built");
     SA_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "cap too small");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     return copy_out(idx, idx->text.p, out, (size_t)idx->n);
 }
 
@@ -128,7 +128,7 @@ extern "C" int sa_copy_doc_starts(sa_index* idx, uint32_t* out, uint64_t cap)
     SA_REQUIRE(idx && idx->built, SA_ERR_INVALID, "index not built");
     const uint64_t nd = (uint64_t)idx->num_nl + 1;
     SA_REQUIRE(cap >= nd, SA_ERR_INVALID, "cap too small");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     out[0] = 0;
     int rc = copy_out(idx, idx->nlpos.p, out + 1, (size_t)idx->num_nl * 4);
     if (rc != SA_OK) return rc;
@@ -148,7 +148,7 @@ extern "C" int sa_debug_copy_lcp(sa_index* idx, uint16_t* out, uint64_t cap)
     SA_REQUIRE(idx && idx->built, SA_ERR_INVALID, "index not built");
     SA_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "cap too small");
     SA_REQUIRE(idx->lcp.p, SA_ERR_INVALID, "no lcp array");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     return copy_out(idx, idx->lcp.p, out, (size_t)idx->n * 2);
 }
 
@@ -199,9 +199,9 @@ extern "C" int sa_query_ranges(sa_index* idx, const uint8_t* qbytes, const uint6
     SA_REQUIRE(idx && idx->built, SA_ERR_INVALID, "index not built");
     SA_REQUIRE(qoff || nq == 0, SA_ERR_INVALID, "qoff is NULL");
     SA_REQUIRE(nq < (1ull << 28), SA_ERR_LIMIT, "too many queries in one batch");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
-    idx->have_ranges = false;
+    sa_invalidate_results(idx);
     idx->stats.ms_query = idx->stats.ms_hits = 0.f;
     idx->stats.kernel_launches = 0;
     if (hit_off) hit_off[0] = 0;
@@ -245,7 +245,7 @@ extern "C" int sa_query_ranges(sa_index* idx, const uint8_t* qbytes, const uint6
 extern "C" int sa_query_hits(sa_index* idx, uint32_t* hit_pos, uint32_t* hit_doc, uint64_t cap)
 {
     SA_REQUIRE(idx && idx->built && idx->have_ranges, SA_ERR_INVALID, "no sa_query_ranges result to expand");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     const uint64_t total = idx->last_total_hits;
     SA_REQUIRE(cap >= total, SA_ERR_INVALID, "cap %llu < %llu hits", (unsigned long long)cap, (unsigned long long)total);
@@ -281,7 +281,7 @@ extern "C" int sa_query_ranges_device(sa_index* idx, const uint8_t* d_qbytes, co
     SA_REQUIRE(idx->n > 0, SA_ERR_INVALID, "empty index");
     SA_REQUIRE(d_qbytes && d_qoff && d_start && d_end, SA_ERR_INVALID, "NULL device pointer");
     SA_REQUIRE(nq < (1ull << 28), SA_ERR_LIMIT, "too many queries in one batch");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     idx->stats.ms_query = idx->stats.ms_hits = 0.f;
     idx->stats.kernel_launches = 0;

@@ -413,7 +413,7 @@ int sa_build_resident(sa_index* idx, uint32_t flags)
     idx->lprime = idx->L < n ? idx->L : n;                    // engine.c:841
     st.n = n; st.max_suffix_length = idx->L; st.lprime = idx->lprime;
     idx->built = false;
-    idx->have_ranges = false;
+    sa_invalidate_results(idx);
     idx->csv = false;
     idx->shard_prepared = false;
     idx->shard_csv = false;

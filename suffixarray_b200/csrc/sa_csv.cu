@@ -375,7 +375,7 @@ extern "C" int sa_build_csv_columns(sa_index* const* idxs, const char* const* co
         sa_set_error("sa_build_csv_columns: one index per column (a handle was passed twice)");
         return SA_ERR_INVALID;
     }
-    std::vector<std::unique_lock<std::mutex>> locks;      // address order: concurrent callers cannot deadlock
+    std::vector<std::unique_lock<std::shared_mutex>> locks;      // address order: concurrent callers cannot deadlock
     for (sa_index* p : order) locks.emplace_back(p->mu);
     sa_index* src = idxs[0];
     SA_CU(cudaSetDevice(src->device));
@@ -392,7 +392,7 @@ extern "C" int sa_build_csv_columns(sa_index* const* idxs, const char* const* co
         sa_index* idx = idxs[c];
         idx->timing = (flags & SA_FLAG_TIMING) != 0;
         idx->built = false;
-        idx->have_ranges = false;
+        sa_invalidate_results(idx);
         idx->shard_prepared = false;
         idx->shard_csv = false;
         idx->stats.ms_h2d = 0.f;
@@ -448,7 +448,7 @@ extern "C" int sa_build_csv(sa_index* idx, const char* csv_path, const char* col
 extern "C" int sa_shard_begin_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags)
 {
     if (!idx || !csv_path || !column) { sa_set_error("sa_shard_begin_csv: NULL argument"); return SA_ERR_INVALID; }
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     Mapped m;
     std::vector<std::string> cells;
@@ -459,7 +459,7 @@ extern "C" int sa_shard_begin_csv(sa_index* idx, const char* csv_path, const cha
     if (rc != SA_OK) return rc;
     idx->timing = (flags & SA_FLAG_TIMING) != 0;
     idx->built = false;
-    idx->have_ranges = false;
+    sa_invalidate_results(idx);
     idx->csv = false;
     idx->shard_prepared = false;
     idx->shard_csv = false;

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <mutex>
+#include <shared_mutex>
 #include <string>
 #include <vector>
 
@@ -55,6 +56,30 @@ struct PhaseTimer {
     float* target = nullptr;
 };
 
+struct sa_index;
+
+// Per-call query state (sa_cuda.h "Per-call query results"): device scratch of one batch, its own
+// stream and events.  Created by sa_result_create, bound to one index.
+struct sa_result {
+    sa_index* idx = nullptr;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
+    DevBuf ucount, uoff, upos, udoc, table;     // dedupe: unique counts / compacted offsets / lists, hash scratch
+    DevBuf reclen, recoff, recbytes, recsrc;    // records: lengths, offsets, packed bytes, source offsets
+    uint64_t nq = 0, total_hits = 0, generation = 0;
+    uint32_t k = 0, range_flags = 0;
+    bool have_ranges = false;
+    // after an expansion (sa_query_hits_r / sa_query_records_size)
+    bool have_hits = false, deduped = false, have_records = false;
+    uint64_t out_hits = 0, rec_bytes = 0;
+    cudaEvent_t ev[4] = {};          // query begin/end, hits begin/end
+    float ms_query = 0.f, ms_hits = 0.f;
+    uint64_t launches = 0;
+    uint64_t* h_pin = nullptr;       // pinned, 8 words
+};
+
 struct sa_index {
     int device = 0;
     int num_sms = 148;
@@ -64,7 +89,7 @@ struct sa_index {
     uint32_t lprime = 0;
     bool built = false;
     bool csv = false;
-    std::mutex mu;
+    std::shared_mutex mu;       // builds / loads: exclusive; queries (one sa_result each): shared
 
     // persistent after a build
     DevBuf text;        // n + SA_TEXT_PAD bytes, zero padded
@@ -106,10 +131,17 @@ struct sa_index {
     cudaStream_t copy_streams[16] = {};        // replication copies (one stream per peer) run beside the finishing kernels
     cudaEvent_t chunk_ev[16] = {};
 
-    // query scratch / results of the last batch
-    DevBuf qbytes, qoff, qstart, qend, qcounts, hitoff, blocksums, hitpos, hitdoc;
-    uint64_t last_nq = 0, last_total_hits = 0;
-    bool have_ranges = false;
+    // queries: per-call state lives in sa_result; `generation` changes with every build / load so a
+    // result of an older array cannot be expanded against a newer one
+    uint64_t generation = 1;
+    sa_result* default_res = nullptr;   // the result object behind sa_query_ranges / sa_query_hits
+    std::mutex res_mu;                  // creates default_res
+    float ms_query_last = 0.f, ms_hits_last = 0.f;   // mirrored into sa_stats for the legacy calls
+    // CSV: positions of the record ends of the file (built on first use from rowbits / rowrank)
+    DevBuf rowpos;
+    uint64_t num_row_ends = 0;
+    bool rowpos_ready = false;
+    std::mutex rowpos_mu;
 
     uint32_t* h_small = nullptr;   // pinned mirror for tiny read-backs (H_SMALL_WORDS words)
 
@@ -174,4 +206,5 @@ int sa_stage_finish(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint
 int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, uint32_t m, uint32_t r_begin,
                        uint32_t r_end, const sa::FinishOut& outs, uint32_t block0 = 0, uint32_t nblocks = 0xFFFFFFFFu);
 int sa_check_device_error(sa_index* idx);
-int sa_csv_finalize_shard(sa_index* idx);   // sa_csv.cu: SA[i] = map[SA[i]] + quoted bits on the complete array of a sharded CSV build
+int sa_csv_finalize_shard(sa_index* idx);
+inline void sa_invalidate_results(sa_index* idx) { idx->generation += 1; idx->rowpos_ready = false; }   // sa_csv.cu: SA[i] = map[SA[i]] + quoted bits on the complete array of a sharded CSV build

@@ -66,7 +66,7 @@ extern "C" int sa_save(sa_index* idx, const char* path)
 {
     if (!idx || !path) { sa_set_error("sa_save: NULL argument"); return SA_ERR_INVALID; }
     if (!idx->built) { sa_set_error("sa_save: index not built"); return SA_ERR_INVALID; }
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     File out;
     out.f = fopen(path, "wb");
@@ -94,7 +94,7 @@ extern "C" int sa_save(sa_index* idx, const char* path)
 extern "C" int sa_load(sa_index* idx, const char* path)
 {
     if (!idx || !path) { sa_set_error("sa_load: NULL argument"); return SA_ERR_INVALID; }
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     File in;
     in.f = fopen(path, "rb");
@@ -110,7 +110,7 @@ extern "C" int sa_load(sa_index* idx, const char* path)
     }
     if (h.n > SA_MAX_INDEX_BYTES) { sa_set_error("%s: n exceeds the 2^31 limit", path); return SA_ERR_LIMIT; }
     idx->built = false;
-    idx->have_ranges = false;
+    sa_invalidate_results(idx);
     idx->n = h.n;
     const size_t n = (size_t)h.n;
     memset(&idx->stats, 0, sizeof idx->stats);
@@ -157,7 +157,7 @@ extern "C" int sa_export_reference_files(sa_index* idx, const char* sa_path, con
 {
     if (!idx || !sa_path) { sa_set_error("sa_export_reference_files: NULL argument"); return SA_ERR_INVALID; }
     if (!idx->built) { sa_set_error("sa_export_reference_files: index not built"); return SA_ERR_INVALID; }
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     const size_t n = (size_t)idx->n;
     if (n >= (1ull << 32)) { sa_set_error("n does not fit the reference's u32 count"); return SA_ERR_LIMIT; }

@@ -251,13 +251,13 @@ extern "C" int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, ui
 {
     SH_REQUIRE(idx && (text || n == 0), SA_ERR_INVALID, "sa_shard_begin: NULL argument");
     SH_REQUIRE(n > 0 && n < 0xFFFFFFFFull - 1024ull, SA_ERR_LIMIT, "sa_shard_begin: n out of range");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     idx->timing = (flags & SA_FLAG_TIMING) != 0;
     idx->n = n;
     idx->built = false;
-    idx->have_ranges = false;
+    sa_invalidate_results(idx);
     idx->csv = false;
     idx->shard_prepared = false;
     idx->shard_csv = false;
@@ -288,7 +288,7 @@ extern "C" int sa_shard_pack(sa_index* idx, uint64_t pos_begin, uint64_t pos_end
     SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_pack: call sa_shard_begin first");
     SH_REQUIRE(pos_begin <= pos_end && pos_end <= idx->n, SA_ERR_INVALID, "sa_shard_pack: bad slice");
     SH_REQUIRE((pos_begin & 15) == 0, SA_ERR_INVALID, "sa_shard_pack: pos_begin must be a multiple of 16");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = (uint32_t)(pos_end - pos_begin);
@@ -316,7 +316,7 @@ extern "C" int sa_shard_split(sa_index* idx, const uint64_t* d_keys, const uint3
     SH_REQUIRE(bin2rank && counts_out, SA_ERR_INVALID, "sa_shard_split: NULL argument");
     SH_REQUIRE(nranks >= 1 && nranks <= sa::SPLIT_MAXR, SA_ERR_LIMIT, "sa_shard_split: 1..16 ranks supported");
     SH_REQUIRE(m64 < (1ull << 32), SA_ERR_LIMIT, "sa_shard_split: too many records");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = (uint32_t)m64;
@@ -354,7 +354,7 @@ extern "C" int sa_shard_sort(sa_index* idx, const uint64_t* d_keys, const uint32
     SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_sort: call sa_shard_begin first");
     SH_REQUIRE(m64 <= SA_MAX_INDEX_BYTES, SA_ERR_LIMIT, "sa_shard_sort: %llu records exceed the 2^31 per-GPU limit",
                (unsigned long long)m64);
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = (uint32_t)m64;
@@ -376,7 +376,7 @@ extern "C" int sa_shard_edges(sa_index* idx, uint32_t edge, uint32_t* head_pos, 
                               uint32_t* tail_pos, uint16_t* tail_lcp)
 {
     SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_edges: no sorted shard");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = idx->shard_m, k = edge < m ? edge : m;
@@ -437,7 +437,7 @@ extern "C" int sa_shard_finish(sa_index* idx, const uint32_t* left_pos, const ui
 {
     SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_finish: no sorted shard");
     SH_REQUIRE(nleft <= 4096 && nright <= 4096, SA_ERR_LIMIT, "sa_shard_finish: halo too large");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = idx->shard_m;
@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(512) replicate_kernel(const uint32_t* __restri
 extern "C" int sa_shard_final_prepare(sa_index* idx, uint8_t* handle_final)
 {
     SH_REQUIRE(idx && idx->shard_prepared && handle_final, SA_ERR_INVALID, "sa_shard_final_prepare: bad argument");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     idx->built = false;
     SA_CU(idx->sa_final.ensure((size_t)(idx->n ? idx->n : 1) * 4));
@@ -520,7 +520,7 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     SH_REQUIRE(nranks >= 1 && nranks <= 16 && my_rank >= 0 && my_rank < nranks, SA_ERR_INVALID, "sa_shard_finish_bcast: bad rank");
     SH_REQUIRE(global_offset + idx->shard_m <= idx->n, SA_ERR_INVALID, "sa_shard_finish_bcast: slice outside the array");
     SH_REQUIRE(idx->sa_final.p, SA_ERR_INVALID, "sa_shard_finish_bcast: call sa_shard_final_prepare first");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     const uint32_t m = idx->shard_m;
     uint32_t* peer_base[16] = {};
@@ -606,7 +606,7 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
 extern "C" int sa_shard_mark_built(sa_index* idx)
 {
     SH_REQUIRE(idx && idx->shard_prepared && idx->sa_final.p, SA_ERR_INVALID, "sa_shard_mark_built: nothing to adopt");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     if (idx->shard_csv) {
         SA_CU(cudaSetDevice(idx->device));
         int rc = sa_csv_finalize_shard(idx);
@@ -625,7 +625,7 @@ extern "C" int sa_shard_copy_text(sa_index* idx, uint64_t offset, uint64_t len, 
     SH_REQUIRE(idx && idx->shard_prepared && (out || len == 0), SA_ERR_INVALID, "sa_shard_copy_text: bad argument");
     SH_REQUIRE(offset <= idx->n && len <= idx->n - offset, SA_ERR_INVALID, "sa_shard_copy_text: range outside the text");
     if (len == 0) return SA_OK;
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     SA_CU(cudaMemcpyAsync(out, idx->text.as<uint8_t>() + offset, (size_t)len, cudaMemcpyDeviceToHost, idx->stream));
     SA_CU(cudaStreamSynchronize(idx->stream));
@@ -639,7 +639,7 @@ extern "C" int sa_adopt_sa(sa_index* idx, const uint32_t* d_sa_full, uint64_t n)
     SH_REQUIRE(idx && d_sa_full, SA_ERR_INVALID, "sa_adopt_sa: NULL argument");
     SH_REQUIRE(idx->shard_prepared && n == idx->n, SA_ERR_INVALID, "sa_adopt_sa: the index holds no text of %llu bytes",
                (unsigned long long)n);
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     SA_CU(idx->sa_final.ensure((size_t)n * 4));
     SA_CU(cudaMemcpyAsync(idx->sa_final.p, d_sa_full, (size_t)n * 4, cudaMemcpyDeviceToDevice, idx->stream));
@@ -662,7 +662,7 @@ extern "C" int sa_shard_count(sa_index* idx, const uint64_t* d_keys, uint64_t m6
     SH_REQUIRE(bin2rank && counts_out, SA_ERR_INVALID, "sa_shard_count: NULL argument");
     SH_REQUIRE(nranks >= 1 && nranks <= sa::SPLIT_MAXR, SA_ERR_LIMIT, "sa_shard_count: 1..16 ranks supported");
     SH_REQUIRE(m64 < (1ull << 32), SA_ERR_LIMIT, "sa_shard_count: too many records");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = (uint32_t)m64;
@@ -696,7 +696,7 @@ extern "C" int sa_shard_recv_prepare(sa_index* idx, uint64_t m_recv, uint8_t* ha
     SH_REQUIRE(m_recv <= SA_MAX_INDEX_BYTES, SA_ERR_LIMIT, "sa_shard_recv_prepare: %llu records exceed the 2^31 per-GPU limit",
                (unsigned long long)m_recv);
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     SA_CU(cudaStreamSynchronize(idx->stream));                  // nothing of an earlier build still uses them
     int rc = sa_ensure_scratch(idx, m_recv ? (uint32_t)m_recv : 1u);
@@ -727,7 +727,7 @@ extern "C" int sa_shard_scatter_p2p(sa_index* idx, const uint64_t* d_keys, const
     SH_REQUIRE(idx && idx->shard_prepared && handles && dst_offset, SA_ERR_INVALID, "sa_shard_scatter_p2p: bad argument");
     SH_REQUIRE(nranks >= 1 && nranks <= sa::SPLIT_MAXR && my_rank >= 0 && my_rank < nranks, SA_ERR_INVALID,
                "sa_shard_scatter_p2p: bad rank");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     const uint32_t m = (uint32_t)m64;
@@ -780,7 +780,7 @@ extern "C" int sa_shard_sort_recv(sa_index* idx, uint64_t m64)
 {
     SH_REQUIRE(idx && idx->shard_prepared, SA_ERR_INVALID, "sa_shard_sort_recv: call sa_shard_begin first");
     SH_REQUIRE(m64 <= SA_MAX_INDEX_BYTES, SA_ERR_LIMIT, "sa_shard_sort_recv: too many records");
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     const uint32_t m = (uint32_t)m64;
     idx->shard_m = m;
@@ -802,7 +802,7 @@ extern "C" int sa_adopt_sa_parts(sa_index* idx, const uint32_t* d_parts, uint64_
     for (int g = 0; g < nparts; ++g) total += counts[g];
     SH_REQUIRE(total == idx->n, SA_ERR_INVALID, "sa_adopt_sa_parts: parts hold %llu entries, text has %llu bytes",
                (unsigned long long)total, (unsigned long long)idx->n);
-    std::lock_guard<std::mutex> lock(idx->mu);
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     SA_CU(idx->sa_final.ensure((size_t)idx->n * 4));
     uint64_t off = 0;
