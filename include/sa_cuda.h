@@ -78,6 +78,12 @@ void sa_destroy(sa_index* idx);
  * engine.c:837-866, producing the identical uint32 order.  H2D copy included. */
 int sa_build_text(sa_index* idx, const uint8_t* text, uint64_t n, uint32_t flags);
 
+/* One partition of a longer text.  The reference passes `text + idx * 2 GiB` of ONE contiguous buffer
+ * (suffix_array.pyx:176-180), so suffixes near the end of a partition are sorted and compared on the
+ * first bytes of the next partition.  text holds n + tail bytes; the n first are indexed, up to 960
+ * tail bytes are kept as look-ahead (enough for max_suffix_length <= 900; a longer tail is cut). */
+int sa_build_text_tail(sa_index* idx, const uint8_t* text, uint64_t n, uint64_t tail, uint32_t flags);
+
 /* Same, text already resident in HBM (copied device-to-device into the index). */
 int sa_build_text_device(sa_index* idx, const uint8_t* d_text, uint64_t n, uint32_t flags);
 

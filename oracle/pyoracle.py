@@ -71,6 +71,18 @@ def oracle_lib():
         lib.sao_csv_scan.restype = C.c_uint64
         lib.sao_csv_remap.argtypes = [_u32p, C.c_uint64, _u32p, _u8p, _u8p]
         lib.sao_csv_remap.restype = None
+        lib.sao_build_tail.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, _u32p]
+        lib.sao_build_tail.restype = C.c_int
+        lib.sao_query_batch_tail.argtypes = [_u8p, C.c_uint64, C.c_uint64, _u32p, C.c_uint32, _u8p, _u64p, C.c_uint64,
+                                             _u32p, _u32p]
+        lib.sao_query_batch_tail.restype = C.c_int
+        lib.sao_query_file_batch.argtypes = [_u8p, C.c_uint64, _u32p, C.c_uint64, C.c_uint32, _u8p, _u64p, C.c_uint64,
+                                             _u32p, _u32p, C.c_int]
+        lib.sao_query_file_batch.restype = C.c_int
+        lib.sao_csv_row_starts.argtypes = [_u8p, C.c_uint64, _u64p]
+        lib.sao_csv_row_starts.restype = C.c_uint64
+        lib.sao_dedupe.argtypes = [_u64p, C.c_uint64, _u32p, _u32p, _u64p, _u32p, _u32p]
+        lib.sao_dedupe.restype = C.c_int
         _oracle = lib
     return _oracle
 
@@ -105,6 +117,18 @@ def ref_lib():
         lib.ref_max_threads.restype = C.c_int
         lib.ref_set_threads.argtypes = [C.c_int]
         lib.ref_set_threads.restype = None
+        lib.ref_csv_open.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32]
+        lib.ref_csv_open.restype = C.c_void_p
+        lib.ref_csv_n.argtypes = [C.c_void_p]
+        lib.ref_csv_n.restype = C.c_uint32
+        lib.ref_csv_copy.argtypes = [C.c_void_p, _u32p, _u8p]
+        lib.ref_csv_copy.restype = None
+        lib.ref_csv_close.argtypes = [C.c_void_p]
+        lib.ref_csv_close.restype = None
+        lib.ref_csv_query_batch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, _u64p, C.c_uint64, _u32p, _u32p, _u8p, C.c_int]
+        lib.ref_csv_query_batch.restype = None
+        lib.ref_csv_records.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_uint32, C.c_void_p, C.c_uint64, _u64p]
+        lib.ref_csv_records.restype = C.c_int64
         _ref = lib
     return _ref
 
@@ -135,6 +159,30 @@ def oracle_build(text, L: int) -> np.ndarray:
     if rc != 0:
         raise RuntimeError(f"sao_build failed: {rc}")
     return sa
+
+
+def oracle_build_tail(text, n: int, L: int) -> np.ndarray:
+    """ORDER-E of the first n positions of `text`; the bytes after n are look-ahead (a partition of a
+    longer text, suffix_array.pyx:176-180)."""
+    t = _as_u8(text)
+    sa = np.empty(max(n, 1), dtype=np.uint32)
+    rc = oracle_lib().sao_build_tail(_p(t, _u8p), n, t.size - n, L, _p(sa, _u32p))
+    if rc != 0:
+        raise RuntimeError(f"sao_build_tail failed: {rc}")
+    return sa[:n]
+
+
+def oracle_query_tail(text, n: int, sa: np.ndarray, L: int, queries):
+    t = _as_u8(text)
+    qbytes, qoff = pack_queries(queries)
+    nq = len(queries)
+    start = np.empty(max(nq, 1), dtype=np.uint32)
+    end = np.empty(max(nq, 1), dtype=np.uint32)
+    rc = oracle_lib().sao_query_batch_tail(_p(t, _u8p), n, t.size - n, _p(np.ascontiguousarray(sa, np.uint32), _u32p), L,
+                                           _p(qbytes, _u8p), _p(qoff, _u64p), nq, _p(start, _u32p), _p(end, _u32p))
+    if rc != 0:
+        raise RuntimeError("sao_query_batch_tail failed")
+    return start[:nq], end[:nq]
 
 
 def oracle_query(text, sa: np.ndarray, L: int, queries, nthreads: int = 0):
@@ -204,7 +252,107 @@ def oracle_csv_remap(sa: np.ndarray, mp: np.ndarray, quoted_by_text: np.ndarray)
     return sa2, qr[: sa2.size]
 
 
+def oracle_query_file(file_bytes: bytes, sa_file: np.ndarray, L: int, queries, nthreads: int = 0):
+    """get_substring_positions_file (engine.c:920-999) restated: probes compare raw file bytes."""
+    size = len(file_bytes)
+    f = np.zeros(size + 8, dtype=np.uint8)
+    f[:size] = np.frombuffer(file_bytes, dtype=np.uint8)
+    qbytes, qoff = pack_queries(queries)
+    nq = len(queries)
+    start = np.empty(max(nq, 1), dtype=np.uint32)
+    end = np.empty(max(nq, 1), dtype=np.uint32)
+    sa_ = np.ascontiguousarray(sa_file, dtype=np.uint32) if sa_file.size else np.zeros(1, np.uint32)
+    rc = oracle_lib().sao_query_file_batch(_p(f, _u8p), size, _p(sa_, _u32p), sa_file.size, L, _p(qbytes, _u8p),
+                                           _p(qoff, _u64p), nq, _p(start, _u32p), _p(end, _u32p), nthreads)
+    if rc != 0:
+        raise RuntimeError("sao_query_file_batch failed")
+    return start[:nq], end[:nq]
+
+
+def oracle_csv_row_starts(file_bytes: bytes) -> np.ndarray:
+    """-> u64[rows + 1]: first byte of every row of the file (row 0 = header), then the file size."""
+    size = len(file_bytes)
+    f = np.zeros(size + 8, dtype=np.uint8)
+    f[:size] = np.frombuffer(file_bytes, dtype=np.uint8)
+    out = np.zeros(size + 2, dtype=np.uint64)
+    rows = oracle_lib().sao_csv_row_starts(_p(f, _u8p), size, _p(out, _u64p))
+    return out[: rows + 1].copy()
+
+
+def oracle_hits_rows(sa_file: np.ndarray, row_starts: np.ndarray, start: np.ndarray, end: np.ndarray, k: int):
+    """CSV hit expansion: hit_pos = file offset SA[rank], hit_doc = row of the file holding it."""
+    nq = start.size
+    hit_off = np.zeros(nq + 1, dtype=np.uint64)
+    s_ = np.ascontiguousarray(start, np.uint32) if nq else np.zeros(1, np.uint32)
+    e_ = np.ascontiguousarray(end, np.uint32) if nq else np.zeros(1, np.uint32)
+    oracle_lib().sao_hit_offsets(_p(s_, _u32p), _p(e_, _u32p), nq, k, _p(hit_off, _u64p))
+    pos = [sa_file[int(start[i]): int(start[i]) + int(hit_off[i + 1] - hit_off[i])] for i in range(nq)]
+    hit_pos = np.concatenate(pos).astype(np.uint32) if pos else np.zeros(0, np.uint32)
+    hit_doc = (np.searchsorted(row_starts[:-1], hit_pos.astype(np.uint64), side="right") - 1).astype(np.uint32)
+    return hit_off, hit_pos, hit_doc
+
+
+def oracle_dedupe(hit_off: np.ndarray, hit_pos: np.ndarray, hit_doc: np.ndarray):
+    """-> (off, pos, doc): per query the first hit (rank order) of every record id."""
+    nq = hit_off.size - 1
+    total = int(hit_off[-1])
+    off = np.zeros(nq + 1, dtype=np.uint64)
+    pos = np.zeros(max(total, 1), dtype=np.uint32)
+    doc = np.zeros(max(total, 1), dtype=np.uint32)
+    hp = np.ascontiguousarray(hit_pos, np.uint32) if total else np.zeros(1, np.uint32)
+    hd = np.ascontiguousarray(hit_doc, np.uint32) if total else np.zeros(1, np.uint32)
+    rc = oracle_lib().sao_dedupe(_p(np.ascontiguousarray(hit_off, np.uint64), _u64p), nq, _p(hp, _u32p), _p(hd, _u32p),
+                                 _p(off, _u64p), _p(pos, _u32p), _p(doc, _u32p))
+    if rc != 0:
+        raise RuntimeError("sao_dedupe failed")
+    u = int(off[-1])
+    return off, pos[:u], doc[:u]
+
+
 # ----------------------------------------------------------------------------- reference
+class RefCsvIndex:
+    """The reference's own CSV index (engine.c:1454) kept alive for its query functions."""
+
+    def __init__(self, path: str, column: str, L: int):
+        self.path = path
+        self.h = ref_lib().ref_csv_open(path.encode(), column.encode(), L)
+        if not self.h:
+            raise RuntimeError("ref_csv_open failed")
+        self.n = int(ref_lib().ref_csv_n(self.h))
+
+    def arrays(self):
+        sa = np.zeros(max(self.n, 1), dtype=np.uint32)
+        qd = np.zeros(max(self.n, 1), dtype=np.uint8)
+        ref_lib().ref_csv_copy(self.h, _p(sa, _u32p), _p(qd, _u8p))
+        return sa[: self.n], qd[: self.n]
+
+    def query(self, queries, nthreads: int = 0):
+        """get_substring_positions_file -> (start, end, skipped)."""
+        nq = len(queries)
+        qbytes, qoff = pack_queries([q + b"\0" for q in queries])
+        start = np.full(max(nq, 1), 0xFFFFFFFF, dtype=np.uint32)
+        end = np.full(max(nq, 1), 0xFFFFFFFF, dtype=np.uint32)
+        skipped = np.zeros(max(nq, 1), dtype=np.uint8)
+        ref_lib().ref_csv_query_batch(self.h, self.path.encode(), qbytes.ctypes.data, _p(qoff, _u64p), nq,
+                                      _p(start, _u32p), _p(end, _u32p), _p(skipped, _u8p), nthreads)
+        return start[:nq], end[:nq], skipped[:nq]
+
+    def records(self, query: bytes, k: int, cap: int = 1 << 22):
+        """get_matching_records_file -> list[bytes], or None when the shim fenced the query."""
+        out = np.zeros(cap, dtype=np.uint8)
+        off = np.zeros(k + 2, dtype=np.uint64)
+        got = ref_lib().ref_csv_records(self.h, self.path.encode(), query, k, out.ctypes.data, cap, _p(off, _u64p))
+        if got < 0:
+            return None
+        b = out.tobytes()
+        return [b[int(off[j]): int(off[j + 1])] for j in range(int(got))]
+
+    def close(self):
+        if self.h:
+            ref_lib().ref_csv_close(self.h)
+            self.h = None
+
+
 def _padded(text) -> np.ndarray:
     t = _as_u8(text)
     out = np.zeros(t.size + REF_PAD, dtype=np.uint8)

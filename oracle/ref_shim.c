@@ -14,6 +14,7 @@
 #include <unistd.h>
 #include <fcntl.h>
 #include <omp.h>
+#include <ctype.h>
 #include "engine.h"
 #include "libsais.h"
 
@@ -141,6 +142,112 @@ uint32_t ref_csv_build(const char* path, const char* column, uint32_t max_suffix
     }
     free(s->suffix_array);
     return n;
+}
+
+/* ---- the reference's CSV query path on an index it built itself ------------------------------
+ * ref_csv_open  = construct_truncated_suffix_array_from_csv_partitioned_mmap_full (engine.c:1454)
+ * ref_csv_query = get_substring_positions_file (engine.c:920-999) on partition 0
+ * ref_csv_records = get_matching_records_file (engine.c:1326-1390)
+ * Single-partition files only (< 2 GiB).  Two fences, both around undefined behaviour of the
+ * reference (out-of-bounds reads, use of a closed FILE): ref_csv_query returns 1 without calling it
+ * when the probe at rank 0 would compare >= 0 (`last = mid - 1` wraps at mid == 0, :951), and
+ * ref_csv_records only calls get_matching_records_file for queries that match and whose hits all
+ * lie behind the header line (the backward newline seek of a hit in row 0 returns UINT32_MAX, :1283). */
+void* ref_csv_open(const char* path, const char* column, uint32_t max_suffix_length)
+{
+    SuffixArrayIndex* idx = NULL;
+    char* cols[1];
+    cols[0] = (char*)column;
+    hush();
+    construct_truncated_suffix_array_from_csv_partitioned_mmap_full(&idx, path, max_suffix_length, cols, 1);
+    unhush();
+    return idx;
+}
+
+uint32_t ref_csv_n(void* h) { return ((SuffixArrayIndex*)h)->suffix_arrays[0].n; }
+
+void ref_csv_copy(void* h, uint32_t* sa_out, uint8_t* quoted_out)
+{
+    SuffixArray_struct* s = &((SuffixArrayIndex*)h)->suffix_arrays[0];
+    memcpy(sa_out, s->suffix_array, (size_t)s->n * sizeof(uint32_t));
+    for (uint32_t i = 0; i < s->n; ++i) quoted_out[i] = get_buffer_bit(s->is_quoted_bitflag, i);
+}
+
+void ref_csv_close(void* h)
+{
+    SuffixArrayIndex* idx = (SuffixArrayIndex*)h;
+    free(idx->suffix_arrays[0].suffix_array);
+}
+
+static int rank0_wraps(FILE* f, const SuffixArray_struct* s, const char* q)
+{
+    size_t m = strlen(q);
+    size_t c = m < s->max_suffix_length ? m : s->max_suffix_length;
+    char* line = (char*)calloc(c + 8, 1);
+    fseek(f, (long)(s->global_byte_start_idx + s->suffix_array[0]), SEEK_SET);
+    fread(line, 1, c, f);
+    for (size_t i = 0; i < c; ++i) line[i] = (char)tolower(line[i]);
+    int r = strncmp(line, q, c) >= 0;
+    free(line);
+    return r;
+}
+
+int ref_csv_query(void* h, const char* path, const char* q, uint32_t* start, uint32_t* end)
+{
+    SuffixArray_struct* s = &((SuffixArrayIndex*)h)->suffix_arrays[0];
+    FILE* f = fopen(path, "r");
+    if (!f || s->n == 0) { if (f) fclose(f); return 1; }
+    if (rank0_wraps(f, s, q)) { fclose(f); return 1; }
+    pair_u32 r = get_substring_positions_file(f, s, q);
+    fclose(f);
+    *start = r.first; *end = r.second;
+    return 0;
+}
+
+/* Batch of NUL-terminated queries under an omp parallel-for (each thread its own FILE*). */
+void ref_csv_query_batch(void* h, const char* path, const char* qbytes, const uint64_t* qoff, uint64_t nq,
+                         uint32_t* start, uint32_t* end, uint8_t* skipped, int nthreads)
+{
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 16) num_threads(nthreads)
+    for (long i = 0; i < (long)nq; ++i)
+        skipped[i] = (uint8_t)ref_csv_query(h, path, qbytes + qoff[i], &start[i], &end[i]);
+}
+
+/* -> number of records (>= 0), -1 when the query was fenced.  Records are copied into out
+ * (rec_off[j] .. rec_off[j + 1]) and freed. */
+int64_t ref_csv_records(void* h, const char* path, const char* q, uint32_t k, char* out, uint64_t cap,
+                        uint64_t* rec_off)
+{
+    SuffixArray_struct* s = &((SuffixArrayIndex*)h)->suffix_arrays[0];
+    uint32_t start = UINT32_MAX, end = UINT32_MAX;
+    rec_off[0] = 0;
+    if (ref_csv_query(h, path, q, &start, &end)) return -1;
+    if (start == UINT32_MAX || end == UINT32_MAX || start == end + 1) return 0;      /* the reference fclose()s and goes on, :1346-1356 */
+    uint32_t take = end - start + 1 < k ? end - start + 1 : k;
+    FILE* f = fopen(path, "r");
+    if (!f) return -1;
+    long header_end = 0;
+    int ch;
+    while ((ch = fgetc(f)) != EOF && ch != '\n') ++header_end;
+    fclose(f);
+    for (uint32_t i = 0; i < take; ++i)
+        if ((long)s->suffix_array[start + i] <= header_end) return -1;
+    char** recs = (char**)calloc(k ? k : 1, sizeof(char*));
+    uint32_t got = 0;
+    hush();
+    get_matching_records_file(path, s, q, k, recs, &got);
+    unhush();
+    uint64_t w = 0;
+    for (uint32_t j = 0; j < got; ++j) {
+        size_t len = strlen(recs[j]);
+        if (w + len <= cap) memcpy(out + w, recs[j], len);
+        w += len;
+        rec_off[j + 1] = w;
+        free(recs[j]);
+    }
+    free(recs);
+    return (w <= cap) ? (int64_t)got : -1;
 }
 
 /* libsais (vendored 2.8.4), the "baseline B" timing arm -- a FULL suffix array, never a

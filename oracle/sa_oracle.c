@@ -125,11 +125,20 @@ static uint8_t* padded_copy(const uint8_t* text, uint64_t n)
 /* ORDER-E.  text: n bytes (no padding needed; a zero-padded copy is made).  sa: n entries.
  * Restates construct_truncated_suffix_array, engine.c:837-866.  Returns 0, or -1 on OOM,
  * -2 on n >= 2^32-1 or L == 0 handled as: L == 0 gives the identity (depth 0 == max depth). */
+int sao_build_tail(const uint8_t* text, uint64_t n, uint64_t tail, uint32_t max_suffix_length, uint32_t* sa);
 int sao_build(const uint8_t* text, uint64_t n, uint32_t max_suffix_length, uint32_t* sa)
+{
+    return sao_build_tail(text, n, 0, max_suffix_length, sa);
+}
+
+/* One partition of a longer text: the reference calls construct_truncated_suffix_array on
+ * `text + idx * 2 GiB` of one contiguous buffer (suffix_array.pyx:176-180), so the compares of the
+ * last suffixes read on into the next partition.  text holds n + tail bytes, n are indexed. */
+int sao_build_tail(const uint8_t* text, uint64_t n, uint64_t tail, uint32_t max_suffix_length, uint32_t* sa)
 {
     if (n >= 0xFFFFFFFFull) return -2;
     if (n == 0) return 0;
-    uint8_t* t = padded_copy(text, n);
+    uint8_t* t = padded_copy(text, n + tail);
     uint32_t* tmp = (uint32_t*)malloc((size_t)n * sizeof(uint32_t));
     if (!t || !tmp) { free(t); free(tmp); return -1; }
     const uint32_t lprime = max_suffix_length < n ? max_suffix_length : (uint32_t)n;   /* :841 */
@@ -220,6 +229,19 @@ int sao_query_batch(const uint8_t* text, uint64_t n, const uint32_t* sa, uint32_
                      &start[i], &end[i]);
     }
     (void)nthreads;
+    free(t);
+    return 0;
+}
+
+/* Partition variant: text holds n + tail bytes (see sao_build_tail); the bisection runs over the n
+ * entries of sa and its compares read the look-ahead bytes. */
+int sao_query_batch_tail(const uint8_t* text, uint64_t n, uint64_t tail, const uint32_t* sa, uint32_t max_suffix_length,
+                         const uint8_t* qbytes, const uint64_t* qoff, uint64_t nq, uint32_t* start, uint32_t* end)
+{
+    uint8_t* t = padded_copy(text, n + tail);
+    if (!t) return -1;
+    for (uint64_t i = 0; i < nq; ++i)
+        query_padded(t, n, sa, max_suffix_length, qbytes + qoff[i], (uint32_t)(qoff[i + 1] - qoff[i]), &start[i], &end[i]);
     free(t);
     return 0;
 }
@@ -371,4 +393,128 @@ void sao_csv_remap(uint32_t* sa, uint64_t n, const uint32_t* map, const uint8_t*
         quoted_by_rank[i] = (p < copied) ? quoted_by_text[p] : 0;
         sa[i] = map[p];
     }
+}
+
+
+/* Restates get_substring_positions_file, engine.c:920-999 -- the bisection of the reference's CSV
+ * query (suffix_array.pyx:221-247 -> get_matching_records_file -> here).  `file` are the raw bytes of
+ * the CSV file, sa_file the remapped array (file offsets, engine.c:647-651; one partition starting at
+ * byte 0, so global_byte_start_idx == 0).  Every probe is fseek + fread of cmp_length bytes into ONE
+ * buffer + tolower (:939-947): a read that crosses the end of the file fills fewer bytes and the tail
+ * keeps what earlier probes left there (zero at first: the checker's reference is built with
+ * zero-filled malloc, ref_prelude.h).  start / end only move on cmp == 0 (:953-957, :987-991); the
+ * second loop starts at first = start (:969).  Signed bounds fence the mid == 0 wrap (as in
+ * query_padded above). */
+static int strncmp_u8(const uint8_t* a, const uint8_t* b, uint32_t c)
+{
+    for (uint32_t i = 0; i < c; ++i) {
+        if (a[i] != b[i]) return (int)a[i] - (int)b[i];
+        if (a[i] == 0) return 0;
+    }
+    return 0;
+}
+
+static void probe_file(const uint8_t* file, uint64_t fsize, uint64_t pos, uint8_t* line, uint32_t c)
+{
+    uint64_t avail = pos < fsize ? fsize - pos : 0;
+    if (avail > c) avail = c;
+    memcpy(line, file + pos, (size_t)avail);                     /* fread, :943-944 */
+    for (uint32_t i = 0; i < c; ++i) line[i] = lower_ascii(line[i]);   /* :945-947 */
+}
+
+static void query_file_one(const uint8_t* file, uint64_t fsize, const uint32_t* sa, uint64_t n, uint32_t max_suffix_length,
+                           const uint8_t* q, uint32_t qlen, uint32_t* out_start, uint32_t* out_end)
+{
+    uint32_t m = 0;
+    while (m < qlen && q[m] != 0) ++m;
+    const uint32_t c = m < max_suffix_length ? m : max_suffix_length;     /* :932 */
+    uint32_t start = UINT32_MAX, end = UINT32_MAX;
+    uint8_t* line = (uint8_t*)calloc((size_t)c + 8, 1);                   /* :934 */
+    int64_t first = 0, last = (int64_t)n - 1;
+    while (first <= last) {                                               /* :937-960 */
+        int64_t mid = (first + last) / 2;
+        probe_file(file, fsize, sa[mid], line, c);
+        int cmp = strncmp_u8(line, q, c);
+        if (cmp < 0) first = mid + 1;
+        else { last = mid - 1; if (cmp == 0) start = (uint32_t)mid; }
+    }
+    if (start != UINT32_MAX) {
+        first = start; last = (int64_t)n - 1;                             /* :969 */
+        while (first <= last) {                                           /* :971-993 */
+            int64_t mid = (first + last) / 2;
+            probe_file(file, fsize, sa[mid], line, c);
+            int cmp = strncmp_u8(line, q, c);
+            if (cmp > 0) last = mid - 1;
+            else { first = mid + 1; if (cmp == 0) end = (uint32_t)mid; }
+        }
+    }
+    free(line);
+    *out_start = start; *out_end = end;
+}
+
+int sao_query_file_batch(const uint8_t* file, uint64_t fsize, const uint32_t* sa_file, uint64_t n,
+                         uint32_t max_suffix_length, const uint8_t* qbytes, const uint64_t* qoff, uint64_t nq,
+                         uint32_t* start, uint32_t* end, int nthreads)
+{
+#ifdef _OPENMP
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+#endif
+    for (long i = 0; i < (long)nq; ++i) {
+        if (n == 0) { start[i] = end[i] = UINT32_MAX; continue; }
+        query_file_one(file, fsize, sa_file, n, max_suffix_length, qbytes + qoff[i], (uint32_t)(qoff[i + 1] - qoff[i]),
+                       &start[i], &end[i]);
+    }
+    (void)nthreads;
+    return 0;
+}
+
+/* Row table of a CSV file: a record ends at a '\n' with an even number of '"' in front of it
+ * (RFC 4180; the line get_matching_records_file seeks for around a hit, engine.c:1217-1323, on files
+ * whose quotes balance).  out[r] = first byte of row r (row 0 = header), out[rows] = size.
+ * out must hold size + 2 entries.  Returns rows = record ends + 1. */
+uint64_t sao_csv_row_starts(const uint8_t* file, uint64_t size, uint64_t* out)
+{
+    uint64_t rows = 0, quotes = 0;
+    out[rows++] = 0;
+    for (uint64_t i = 0; i < size; ++i) {
+        if (file[i] == '"') ++quotes;
+        else if (file[i] == '\n' && (quotes & 1) == 0) out[rows++] = i + 1;
+    }
+    out[rows] = size;
+    return rows;
+}
+
+/* Segmented dedupe of hit lists (no counterpart in the reference, which keeps duplicates,
+ * engine.c:1187): per query, the first hit in rank order of every record id survives. */
+typedef struct { uint32_t doc, j; } sao_dj;
+static int cmp_dj(const void* a, const void* b)
+{
+    const sao_dj* x = (const sao_dj*)a; const sao_dj* y = (const sao_dj*)b;
+    if (x->doc != y->doc) return x->doc < y->doc ? -1 : 1;
+    return x->j < y->j ? -1 : (x->j > y->j);
+}
+
+int sao_dedupe(const uint64_t* hit_off, uint64_t nq, const uint32_t* hit_pos, const uint32_t* hit_doc,
+               uint64_t* out_off, uint32_t* out_pos, uint32_t* out_doc)
+{
+    uint64_t w = 0;
+    for (uint64_t q = 0; q < nq; ++q) {
+        const uint64_t o = hit_off[q];
+        const uint32_t take = (uint32_t)(hit_off[q + 1] - o);
+        out_off[q] = w;
+        if (!take) continue;
+        sao_dj* t = (sao_dj*)malloc((size_t)take * sizeof(sao_dj));
+        uint8_t* keep = (uint8_t*)calloc(take, 1);
+        if (!t || !keep) { free(t); free(keep); return -1; }
+        for (uint32_t j = 0; j < take; ++j) { t[j].doc = hit_doc[o + j]; t[j].j = j; }
+        qsort(t, take, sizeof(sao_dj), cmp_dj);
+        for (uint32_t i = 0; i < take; ++i)
+            if (i == 0 || t[i].doc != t[i - 1].doc) keep[t[i].j] = 1;
+        for (uint32_t j = 0; j < take; ++j)
+            if (keep[j]) { out_pos[w] = hit_pos[o + j]; out_doc[w] = hit_doc[o + j]; ++w; }
+        free(t); free(keep);
+    }
+    out_off[nq] = w;
+    return 0;
 }

@@ -1,0 +1,287 @@
+"""Host logic of the ``SuffixArray`` class -- ONE copy, shared by the Cython class
+(``suffix_array_cy.pyx``, the reference's host language) and the ctypes class (``suffix_array.py``).
+The two differ only in how they reach ``libsa_cuda.so``: each supplies an index type with the small
+method set listed under ``Backend`` below.
+
+Mirrors ``suffix_array/suffix_array.pyx:110-267`` of the reference: same names, argument meaning and
+error behaviour.  This layer joins / encodes strings, walks partitions and turns the packed record
+buffer the library returns into Python objects; all index arithmetic -- build, bisection, hit
+expansion, record ids, dedupe, record cutting -- runs in the CUDA library.
+
+Backend (duck-typed): ``Index(max_suffix_length, device)`` with
+``build_text(u8 array, lowercase, tail)``, ``build_csv(path, column)``, ``sa()``, ``text()``, ``n``,
+``save(path)``, ``load(path)``, ``attach_csv_file(path)``, ``close()``,
+``query(queries, k, file_semantics, dedupe) -> (start, end, hit_off, hit_pos, hit_doc)``,
+``query_records(queries, k, file_semantics, dedupe, compat) -> (hit_off, rec_off, bytes, rec_ids)``;
+and a module-level ``build_csv_columns(indexes, path, columns)``.
+"""
+from __future__ import annotations
+
+import csv
+import json
+import os
+
+import numpy as np
+
+
+class SuffixArrayHost:
+    # The reference cuts the joined text every 2 GiB into independent partitions, each with its own
+    # suffix array, and a query walks them in order until k records are found
+    # (suffix_array.pyx:148-180, :221-247).  Same here; tests shrink this to exercise the walk.
+    PARTITION_BYTES = 1 << 31
+
+    # supplied by the concrete class
+    _Index = None
+    _build_csv_columns = None
+
+    def __init__(self, max_suffix_length: int = 64, documents=None, csv_file: str | None = None,
+                 search_column=None, device: int = 0, csv_query: str = "file", dedupe: bool = False,
+                 reference_records: bool = False):
+        """csv_query: "file" = the reference's CSV bisection (get_substring_positions_file,
+        engine.c:920-999: probes compare the raw file bytes -- the only query its Python class
+        reaches, suffix_array.pyx:221-247) or "text" = get_substring_positions on the parsed
+        column (engine.c:869-918).  dedupe: every record at most once per query (first hit wins; the
+        reference keeps duplicates, engine.c:1187).  reference_records: cut CSV records the way
+        get_matching_records_file does (last byte dropped, engine.c:1314; first byte too for hits at
+        file offsets >= 4096)."""
+        if csv_query not in ("file", "text"):
+            raise ValueError('csv_query must be "file" or "text"')
+        self.max_suffix_length = int(max_suffix_length)
+        self._device = int(device)
+        self.csv_query = csv_query
+        self.dedupe = bool(dedupe)
+        self.reference_records = bool(reference_records)
+        self._parts = [self._Index(self.max_suffix_length, self._device)]   # one index per partition / search column
+        self._mode = None            # "documents" | "csv"
+        self.columns = None          # csv: header cells (pyx:189-194)
+        self.search_columns = None   # csv: the indexed columns, in query order
+        self._csv_path = None
+        if documents is not None and csv_file is not None:
+            raise ValueError("pass either documents= or csv_file=, not both")
+        if documents is not None:
+            self.construct_truncated_suffix_array_documents(documents)
+        elif csv_file is not None:
+            if search_column is None:
+                raise ValueError("csv_file= needs search_column=")
+            self.construct_truncated_suffix_array_from_csv(csv_file, search_column)
+
+    def _resize(self, count: int) -> None:
+        for old in self._parts[count:]:
+            old.close()
+        self._parts = self._parts[:count] + [self._Index(self.max_suffix_length, self._device)
+                                             for _ in range(count - len(self._parts))]
+
+    # ------------------------------------------------------------------ builds
+    def construct_truncated_suffix_array_documents(self, documents) -> None:
+        """pyx:129-180: '\\n'.join(documents) -> utf-8 -> ASCII lower-case -> one index per 2 GiB."""
+        if not isinstance(documents, list):
+            try:
+                documents = list(documents)                       # pyx:130-134
+            except Exception:
+                raise ValueError("Documents must be a list of strings")
+        joined = "\n".join(documents).encode("utf-8")             # pyx:143 (no trailing '\n')
+        text = np.frombuffer(joined, dtype=np.uint8)
+        pb = int(self.PARTITION_BYTES)
+        nparts = max(1, -(-text.size // pb))                      # pyx:148-152
+        self._resize(nparts)
+        look = 960                                                # sa_build_text_tail keeps at most this much
+        for i, part in enumerate(self._parts):                    # pyx:173-180: cut at fixed byte offsets
+            # the reference sorts partition i on `text + i * 2 GiB` of the ONE joined buffer: the bytes after
+            # the cut are visible to the last suffixes of the partition -> pass them as look-ahead tail;
+            # lowercase_string (pyx:103-107) runs on the device copy: SA_FLAG_LOWERCASE
+            end = min(text.size, (i + 1) * pb)
+            tail = min(look, text.size - end)
+            part.build_text(np.ascontiguousarray(text[i * pb: end + tail]), True, tail)
+        self._text = self._doc_starts = None
+        if nparts > 1:
+            # a document may straddle a cut: records of a partitioned text are cut from a host copy of the
+            # joined text by GLOBAL position (a single partition -- any text below 2 GiB -- needs no host copy:
+            # the library cuts the records on the device)
+            low = text.copy()
+            up = (low >= 65) & (low <= 90)
+            low[up] += 32
+            self._text = low.tobytes()
+            self._doc_starts = np.concatenate([[0], np.flatnonzero(low == 10).astype(np.int64) + 1])
+        self._mode = "documents"
+
+    def construct_truncated_suffix_array_from_csv(self, filename: str, search_column) -> None:
+        """pyx:183-207 -> engine.c:1454: scan of the search column(s), build, remap to file offsets.
+        search_column: one name, or a list of names (the reference's C entry takes `char** search_cols`
+        but indexes the first only, engine.c:1476; pyx:197 "TODO: Allow multiple columns"): one index
+        per column from ONE read of the file."""
+        if not os.path.exists(filename):
+            raise FileNotFoundError(filename)
+        with open(filename, "r", newline="") as f:                # pyx:189-194
+            self.columns = f.readline().strip().split(",")
+        cols = [search_column] if isinstance(search_column, str) else list(search_column)
+        if not cols or len(set(cols)) != len(cols):
+            raise ValueError("search_column must name one or more distinct columns")
+        self._resize(len(cols))
+        if len(cols) == 1:
+            self._parts[0].build_csv(filename, cols[0])
+        else:
+            type(self)._build_csv_columns(self._parts, filename, cols)
+        self.search_columns = cols
+        self._csv_path = filename
+        self._mode = "csv"
+
+    # ------------------------------------------------------------------ queries
+    def query_records(self, substring: str, k: int = 1000, column: str | None = None):
+        if substring == "":                                        # pyx:210-211
+            return []
+        return self.query_records_batch([substring], k, column=column)[0]
+
+    def _walk(self, column):
+        if self._mode == "csv" and column is not None:
+            if column not in self.search_columns:
+                raise ValueError(f"column {column!r} is not indexed (indexed: {self.search_columns})")
+            return [self._parts[self.search_columns.index(column)]]
+        return list(self._parts)
+
+    def query_records_batch(self, substrings, k: int = 1000, column: str | None = None):
+        """One list of records per query: the first min(k, matches) hits in suffix-array order
+        (engine.c:1185-1211 / :1356-1388), duplicates kept unless dedupe=True; partitions (documents)
+        or search columns (csv) are walked in order until k records are found (pyx:221-247).
+        Documents index: the matching documents (lower-cased, as indexed); CSV index: one
+        dict(zip(header, row)) per hit (pyx:258-260).  The records are cut on the device and arrive
+        as one packed buffer (sa_query_records)."""
+        if self._mode is None:
+            raise RuntimeError("no suffix array has been constructed")
+        k = int(k)
+        qs = [s.lower().encode("utf-8") for s in substrings]      # pyx:228
+        nonempty = [i for i, q in enumerate(qs) if q]
+        out = [[] for _ in qs]
+        if not nonempty:
+            return out
+        sub = [qs[i] for i in nonempty]
+        is_csv = self._mode == "csv"
+        file_sem = is_csv and self.csv_query == "file"
+        if not is_csv and len(self._parts) > 1:
+            return self._query_partitioned(sub, nonempty, out, k)
+        recs = [[] for _ in sub]
+        seen = [set() for _ in sub] if (self.dedupe and len(self._walk(column)) > 1) else None
+        for p, part in enumerate(self._walk(column)):
+            need = [j for j in range(len(sub)) if len(recs[j]) < k]
+            if not need:
+                break
+            kk = max(k - len(recs[j]) for j in need)
+            hoff, roff, buf, ids = part.query_records([sub[j] for j in need], kk, file_sem, self.dedupe,
+                                                      is_csv and self.reference_records)
+            data = buf.tobytes()
+            ro = roff.tolist()
+            for t, j in enumerate(need):
+                a, b = int(hoff[t]), int(hoff[t + 1])
+                for h in range(a, b):
+                    if len(recs[j]) >= k:
+                        break
+                    if seen is not None:                          # dedupe across partitions / columns
+                        key = (p if not is_csv else 0, int(ids[h]))
+                        if key in seen[j]:
+                            continue
+                        seen[j].add(key)
+                    recs[j].append(data[ro[h]:ro[h + 1]])
+        for j, i in enumerate(nonempty):
+            if is_csv:
+                lines = [r.decode("utf-8", "replace").rstrip("\r") for r in recs[j]]
+                out[i] = [dict(zip(self.columns, row)) for row in csv.reader(lines)]   # pyx:258-260
+            else:
+                out[i] = [r.decode("utf-8", "replace") for r in recs[j]]
+        return out
+
+    def _query_partitioned(self, sub, nonempty, out, k):
+        """documents cut into several partitions (pyx:148-180): walk them in order until k records are
+        found (pyx:221-247); a hit's record is the document around its GLOBAL text position."""
+        pb = int(self.PARTITION_BYTES)
+        ds, text = self._doc_starts, self._text
+        docs = [[] for _ in sub]
+        for p, part in enumerate(self._parts):
+            need = [j for j in range(len(sub)) if len(docs[j]) < k]
+            if not need:
+                break
+            kk = max(k - len(docs[j]) for j in need)
+            _, _, off, pos, _ = part.query([sub[j] for j in need], kk, False, False)
+            for t, j in enumerate(need):
+                gpos = pos[int(off[t]):int(off[t + 1])].astype(np.int64) + p * pb
+                for d in (np.searchsorted(ds, gpos, side="right") - 1).tolist():
+                    if len(docs[j]) >= k:
+                        break
+                    if self.dedupe and d in docs[j]:
+                        continue
+                    docs[j].append(d)
+        for j, i in enumerate(nonempty):
+            recs = []
+            for d in docs[j]:
+                a = int(ds[d])
+                b = int(ds[d + 1]) - 1 if d + 1 < ds.size else len(text)
+                recs.append(text[a:b].decode("utf-8", "replace"))
+            out[i] = recs
+        return out
+
+    def query_positions(self, substrings, k: int = 1000):
+        """-> (start, end, hit_off, hit_pos, hit_doc) NumPy arrays straight from the C ABI (first
+        partition / column): inclusive rank range with the reference's UINT32_MAX sentinels, positions
+        (file offsets on the CSV path) and record ids of the first min(k, count) hits."""
+        qs = [s.lower().encode("utf-8") if isinstance(s, str) else bytes(s) for s in substrings]
+        return self._parts[0].query(qs, int(k), self._mode == "csv" and self.csv_query == "file", self.dedupe)
+
+    # ------------------------------------------------------------------ persistence
+    def save(self, path: str) -> None:
+        """Write the built index to `path` (+ `path.partNNN` for further partitions / columns, +
+        `path.json` with what the host side needs).  The reference only sketches this
+        (engine.c:1098-1165, TODO.md)."""
+        if self._mode is None:
+            raise RuntimeError("no suffix array has been constructed")
+        for i, idx in enumerate(self._parts):
+            idx.save(path if i == 0 else f"{path}.part{i:03d}")
+        meta = {"mode": self._mode, "max_suffix_length": self.max_suffix_length, "partitions": len(self._parts),
+                "partition_bytes": int(self.PARTITION_BYTES), "columns": self.columns, "csv_path": self._csv_path,
+                "search_columns": self.search_columns, "csv_query": self.csv_query, "dedupe": self.dedupe,
+                "reference_records": self.reference_records}
+        with open(path + ".json", "w") as f:
+            json.dump(meta, f)
+
+    @classmethod
+    def load(cls, path: str, device: int = 0):
+        """Restore an index written by save(): no sorting, the arrays go straight to the device; a CSV
+        index re-attaches its file (records and file-semantics probes read it)."""
+        with open(path + ".json") as f:
+            meta = json.load(f)
+        self = cls(max_suffix_length=int(meta["max_suffix_length"]), device=device,
+                   csv_query=meta.get("csv_query", "file"), dedupe=bool(meta.get("dedupe", False)),
+                   reference_records=bool(meta.get("reference_records", False)))
+        self.PARTITION_BYTES = int(meta["partition_bytes"])
+        self._resize(int(meta["partitions"]))
+        for i, idx in enumerate(self._parts):
+            idx.load(path if i == 0 else f"{path}.part{i:03d}")
+        self._mode = meta["mode"]
+        self._text = self._doc_starts = None
+        if self._mode == "documents" and len(self._parts) > 1:
+            low = np.concatenate([idx.text() for idx in self._parts])
+            self._text = low.tobytes()
+            self._doc_starts = np.concatenate([[0], np.flatnonzero(low == 10).astype(np.int64) + 1])
+        if self._mode == "csv":
+            self.columns = meta["columns"]
+            self.search_columns = meta["search_columns"]
+            self._csv_path = meta["csv_path"]
+            for idx in self._parts:
+                idx.attach_csv_file(self._csv_path)
+        return self
+
+    # ------------------------------------------------------------------ misc
+    @property
+    def suffix_array(self):
+        """uint32 array as SuffixArray_struct.suffix_array holds it (file offsets on the CSV path);
+        a list of arrays when the index has several partitions / search columns."""
+        arrays = [idx.sa() for idx in self._parts]
+        return arrays[0] if len(arrays) == 1 else arrays
+
+    def close(self) -> None:
+        for idx in self._parts:
+            idx.close()
+        self._parts = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -21,11 +21,14 @@ SA_OK = 0
 SA_FLAG_LOWERCASE = 1
 SA_FLAG_TIMING = 2
 SA_FLAG_DEVICE_TEXT = 4
+SA_QUERY_FILE_SEMANTICS = 1
+SA_QUERY_DEDUPE = 2
+SA_RECORDS_REFERENCE_COMPAT = 4
 UINT32_MAX = 0xFFFFFFFF
 
 # every symbol include/sa_cuda.h declares (checked by tests/test_abi.py)
 EXPORTS = [
-    "sa_last_error", "sa_abi_version", "sa_create", "sa_destroy", "sa_build_text", "sa_build_text_device",
+    "sa_last_error", "sa_abi_version", "sa_create", "sa_destroy", "sa_build_text", "sa_build_text_tail", "sa_build_text_device",
     "sa_build_csv", "sa_build_csv_columns", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
     "sa_copy_quoted_bits", "sa_copy_text", "sa_device_sa", "sa_get_stats", "sa_query_ranges", "sa_query_hits",
     "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
@@ -33,6 +36,8 @@ EXPORTS = [
     "sa_adopt_sa", "sa_adopt_sa_parts", "sa_shard_count", "sa_shard_recv_prepare", "sa_shard_scatter_p2p", "sa_shard_sort_recv",
     "sa_shard_final_prepare", "sa_shard_finish_bcast", "sa_shard_mark_built",
     "sa_save", "sa_load", "sa_export_reference_files",
+    "sa_result_create", "sa_result_destroy", "sa_query_ranges_r", "sa_query_hits_r", "sa_query_records_size",
+    "sa_query_records", "sa_result_stats", "sa_num_rows", "sa_copy_row_starts", "sa_attach_csv_file",
 ]
 
 
@@ -108,6 +113,7 @@ def lib():
     L.sa_destroy.restype = None
     L.sa_build_text.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
     L.sa_build_text_device.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
+    L.sa_build_text_tail.argtypes = [_vp, _vp, C.c_uint64, C.c_uint64, C.c_uint32]
     L.sa_build_csv.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint32]
     L.sa_build_csv_columns.argtypes = [C.POINTER(_vp), C.POINTER(C.c_char_p), C.c_uint32, C.c_char_p, C.c_uint32]
     L.sa_size.argtypes = [_vp]
@@ -147,6 +153,18 @@ def lib():
     L.sa_save.argtypes = [_vp, C.c_char_p]
     L.sa_load.argtypes = [_vp, C.c_char_p]
     L.sa_export_reference_files.argtypes = [_vp, C.c_char_p, C.c_char_p]
+    L.sa_result_create.argtypes = [_vp, C.POINTER(_vp)]
+    L.sa_result_destroy.argtypes = [_vp]
+    L.sa_result_destroy.restype = None
+    L.sa_query_ranges_r.argtypes = [_vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, C.c_uint32, _vp, _vp, _vp]
+    L.sa_query_hits_r.argtypes = [_vp, _vp, C.c_uint32, _vp, _vp, C.c_uint64, _vp]
+    L.sa_query_records_size.argtypes = [_vp, _vp, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.sa_query_records.argtypes = [_vp, _vp, _vp, C.c_uint64, _vp, C.c_uint64, _vp, _vp]
+    L.sa_result_stats.argtypes = [_vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
+    L.sa_num_rows.argtypes = [_vp]
+    L.sa_num_rows.restype = C.c_uint64
+    L.sa_copy_row_starts.argtypes = [_vp, _vp, C.c_uint64]
+    L.sa_attach_csv_file.argtypes = [_vp, C.c_char_p]
     _lib = L
     return L
 
@@ -169,6 +187,10 @@ class Index:
         self.max_suffix_length = max_suffix_length
 
     def close(self):
+        r = getattr(self, "_res", None)
+        if r is not None:
+            r.close()
+            self._res = None
         if getattr(self, "_h", None) is not None and self._h:
             lib().sa_destroy(self._h)
             self._h = None
@@ -176,11 +198,12 @@ class Index:
     __del__ = close
 
     # ---- builds
-    def build_text(self, text, lowercase: bool = False, timing: bool = False):
+    def build_text(self, text, lowercase: bool = False, timing: bool = False, tail: int = 0):
+        """tail: the last `tail` bytes of `text` are look-ahead only (the next partition's first bytes)."""
         t = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray, memoryview)) \
             else np.ascontiguousarray(text, dtype=np.uint8)
         flags = (SA_FLAG_LOWERCASE if lowercase else 0) | (SA_FLAG_TIMING if timing else 0)
-        check(lib().sa_build_text(self._h, _ptr(t) if t.size else None, t.size, flags))
+        check(lib().sa_build_text_tail(self._h, _ptr(t) if t.size else None, t.size - tail, tail, flags))
 
     def build_text_ptr(self, host_ptr: int, n: int, flags: int = 0):
         check(lib().sa_build_text(self._h, host_ptr, n, flags))
@@ -279,3 +302,115 @@ class Index:
         doc = np.empty(max(total, 1), dtype=np.uint32)
         check(lib().sa_query_hits(self._h, _ptr(pos), _ptr(doc), total))
         return pos[:total], doc[:total]
+
+    # ---- CSV row table
+    @property
+    def num_rows(self) -> int:
+        return int(lib().sa_num_rows(self._h))
+
+    def row_starts(self) -> np.ndarray:
+        """u64[num_rows + 1]: first byte of every row of the file (row 0 = header), then the file size."""
+        rows = self.num_rows
+        out = np.zeros(rows + 1, dtype=np.uint64)
+        check(lib().sa_copy_row_starts(self._h, _ptr(out), rows + 1))
+        return out
+
+    def attach_csv_file(self, path: str):
+        check(lib().sa_attach_csv_file(self._h, path.encode()))
+
+    def result(self) -> "Result":
+        return Result(self)
+
+    # ---- the backend surface of suffixarray_b200/_host.py
+    def _own_result(self) -> "Result":
+        r = getattr(self, "_res", None)
+        if r is None or r._h is None:
+            r = self._res = Result(self)
+        return r
+
+    def query(self, queries, k: int = 1000, file_semantics: bool = False, dedupe: bool = False):
+        """-> (start, end, hit_off, hit_pos, hit_doc)"""
+        r = self._own_result()
+        s, e, _ = r.ranges(queries, k, SA_QUERY_FILE_SEMANTICS if file_semantics else 0)
+        off, pos, doc = r.hits(dedupe)
+        return s, e, off, pos, doc
+
+    def query_records(self, queries, k: int = 1000, file_semantics: bool = False, dedupe: bool = False,
+                      compat: bool = False):
+        """-> (hit_off, rec_off, bytes u8, record ids)"""
+        r = self._own_result()
+        r.ranges(queries, k, SA_QUERY_FILE_SEMANTICS if file_semantics else 0)
+        return r.records(dedupe, compat)
+
+
+def _pack(queries):
+    lens = np.fromiter((len(q) for q in queries), dtype=np.uint64, count=len(queries))
+    qoff = np.zeros(len(queries) + 1, dtype=np.uint64)
+    np.cumsum(lens, out=qoff[1:])
+    joined = b"".join(queries)
+    qbytes = np.frombuffer(joined, dtype=np.uint8) if joined else np.zeros(1, np.uint8)
+    return qbytes, qoff
+
+
+class Result:
+    """Per-call query state (``sa_result``): one batch at a time per Result, any number of Results
+    (threads) per built Index."""
+
+    def __init__(self, index: Index):
+        self._index = index
+        self._h = _vp()
+        check(lib().sa_result_create(index._h, C.byref(self._h)))
+        self.nq = 0
+        self.total_hits = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().sa_result_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def ranges_packed(self, qbytes: np.ndarray, qoff: np.ndarray, k: int = 1000, flags: int = 0):
+        nq = qoff.size - 1
+        start = np.empty(max(nq, 1), dtype=np.uint32)
+        end = np.empty(max(nq, 1), dtype=np.uint32)
+        hit_off = np.zeros(nq + 1, dtype=np.uint64)
+        check(lib().sa_query_ranges_r(self._index._h, self._h, _ptr(qbytes), _ptr(qoff), nq, k, flags, _ptr(start),
+                                      _ptr(end), _ptr(hit_off)))
+        self.nq = nq
+        self.total_hits = int(hit_off[nq])
+        return start[:nq], end[:nq], hit_off
+
+    def ranges(self, queries, k: int = 1000, flags: int = 0):
+        qbytes, qoff = _pack(queries)
+        return self.ranges_packed(qbytes, qoff, k, flags)
+
+    def hits(self, dedupe: bool = False):
+        """-> (hit_off u64[nq+1], hit_pos u32, hit_doc u32) of the last ranges() call."""
+        total = self.total_hits
+        pos = np.empty(max(total, 1), dtype=np.uint32)
+        doc = np.empty(max(total, 1), dtype=np.uint32)
+        off = np.zeros(self.nq + 1, dtype=np.uint64)
+        check(lib().sa_query_hits_r(self._index._h, self._h, SA_QUERY_DEDUPE if dedupe else 0, _ptr(pos), _ptr(doc), total,
+                                    _ptr(off)))
+        out = int(off[self.nq]) if self.nq else 0
+        return off, pos[:out], doc[:out]
+
+    def records(self, dedupe: bool = False, compat: bool = False):
+        """-> (hit_off u64[nq+1], rec_off u64[records+1], bytes u8, record ids u32): every hit's record
+        (document / line of the CSV file) gathered on the device into one packed buffer."""
+        flags = (SA_QUERY_DEDUPE if dedupe else 0) | (SA_RECORDS_REFERENCE_COMPAT if compat else 0)
+        num, nbytes = C.c_uint64(0), C.c_uint64(0)
+        check(lib().sa_query_records_size(self._index._h, self._h, flags, C.byref(num), C.byref(nbytes)))
+        num, nbytes = int(num.value), int(nbytes.value)
+        out = np.empty(max(nbytes, 1), dtype=np.uint8)
+        rec_off = np.zeros(num + 1, dtype=np.uint64)
+        hit_off = np.zeros(self.nq + 1, dtype=np.uint64)
+        doc = np.empty(max(num, 1), dtype=np.uint32)
+        check(lib().sa_query_records(self._index._h, self._h, _ptr(out), nbytes, _ptr(rec_off), num, _ptr(hit_off), _ptr(doc)))
+        return hit_off, rec_off, out[:nbytes], doc[:num]
+
+    def stats(self) -> dict:
+        a, b, n = C.c_float(0), C.c_float(0), C.c_uint64(0)
+        check(lib().sa_result_stats(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        return {"ms_query": a.value, "ms_hits": b.value, "kernel_launches": int(n.value)}

@@ -66,7 +66,7 @@ cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa, uint32_t n,
                             const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
                             uint32_t* end, int mode /* 0 auto, 1 thread per query, 2 eight lanes per query */,
                             cudaStream_t s);
-cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k,
+cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k, uint32_t n,
                                  uint32_t* counts, cudaStream_t s);
 // exclusive scan of u32 counts into u64 offsets (off[num] = total)
 cudaError_t sa_launch_scan_u32_to_u64(const uint32_t* counts, uint32_t num, uint64_t* off, uint32_t* block_sums,
@@ -117,3 +117,4 @@ cudaError_t sa_launch_record_bounds(const uint32_t* hit_pos, const uint32_t* hit
                                     uint32_t* len, cudaStream_t s);
 cudaError_t sa_launch_record_gather(const uint8_t* src, const unsigned long long* src_off, const uint64_t* rec_off,
                                     uint64_t num, uint8_t* out, cudaStream_t s);
+cudaError_t sa_launch_count_out_of_range(const uint32_t* a, uint64_t n, uint64_t limit, unsigned int* bad, cudaStream_t s);

@@ -69,13 +69,42 @@ __global__ void __launch_bounds__(1024) block_sum_kernel(const uint32_t* __restr
     }
 }
 
-__global__ void scan_u64_serial_kernel(unsigned long long* __restrict__ sums, uint32_t num)
+// exclusive scan of the num block sums in place (one block, 1024 per step); sums[num] = total
+__global__ void __launch_bounds__(1024) scan_u64_block_kernel(unsigned long long* __restrict__ sums, uint32_t num)
 {
-    // num = ceil(nq / 1024) block sums: a warp-strided serial scan is plenty
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    unsigned long long acc = 0;
-    for (uint32_t i = 0; i < num; ++i) { unsigned long long v = sums[i]; sums[i] = acc; acc += v; }
-    sums[num] = acc;
+    __shared__ unsigned long long ws[32];
+    __shared__ unsigned long long carry;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < num; base += 1024) {
+        const uint32_t i = base + t;
+        const unsigned long long a = (i < num) ? sums[i] : 0ull;
+        unsigned long long ia = a;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long y = __shfl_up_sync(0xffffffffu, ia, o);
+            if (lane >= o) ia += y;
+        }
+        if (lane == 31) ws[warp] = ia;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned long long v = ws[lane], s2 = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                unsigned long long y = __shfl_up_sync(0xffffffffu, s2, o);
+                if (lane >= o) s2 += y;
+            }
+            ws[lane] = s2 - v;
+        }
+        __syncthreads();
+        const unsigned long long ea = carry + ws[warp] + ia - a;
+        if (i < num) sums[i] = ea;
+        __syncthreads();
+        if (t == 1023) carry = ea + a;
+        __syncthreads();
+    }
+    if (t == 0) sums[num] = carry;
 }
 
 __global__ void __launch_bounds__(1024) offsets_kernel(const uint32_t* __restrict__ c, uint32_t num,
@@ -346,14 +375,109 @@ query_thread_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict
     end_out[gq] = end;
 }
 
+// ------------------------------------------------------------------------------ file semantics
+// get_substring_positions_file (engine.c:920-999), the bisection behind the reference's only
+// Python-reachable query (suffix_array.pyx:221-247 -> get_matching_records_file).  Differences to
+// get_substring_positions that make it a different function of (array, query):
+//   * each probe compares the RAW FILE bytes at offset SA[mid] (fseek + fread + tolower, :939-947):
+//     past the end of a cell it sees `,next cell` / `"` / the rest of the line, not '\n' + next row
+//   * start / end are only recorded when cmp == 0 (:953-957, :987-991)
+//   * the second bisection starts at first = start (:969)
+//   * `line` is one malloc'd buffer for all probes: fread near the end of the file fills fewer than
+//     cmp_length bytes and the tail keeps the (lower-cased) bytes of earlier probes -- reproduced
+//     from the list of this query's probe offsets (zero before the first write: the checker builds
+//     the reference with zero-filled malloc, oracle/ref_prelude.h)
+// The mid == 0 wrap of `last = mid - 1` is fenced as in the in-memory kernels (signed bounds).
+__device__ __forceinline__ uint64_t lower8(uint64_t x)
+{
+    const uint64_t hi = x & 0x8080808080808080ull, lo = x & 0x7F7F7F7F7F7F7F7Full;
+    const uint64_t ge_a = lo + 0x3F3F3F3F3F3F3F3Full;      // bit 7 set iff (byte & 0x7f) >= 'A'
+    const uint64_t gt_z = lo + 0x2525252525252525ull;      // bit 7 set iff (byte & 0x7f) >  'Z'
+    return x | ((ge_a & ~gt_z & ~hi & 0x8080808080808080ull) >> 2);
+}
+
+__device__ __forceinline__ uint32_t lower1(uint32_t b) { return (b >= 'A' && b <= 'Z') ? b + 32u : b; }
+
+constexpr int QF_MAX_PROBES = 72;      // 2 * (32 + 1) probes for n < 2^32, rounded up
+
+__global__ void __launch_bounds__(128)
+query_file_kernel(const uint8_t* __restrict__ file, uint64_t fsize, const uint32_t* __restrict__ sa, uint32_t n,
+                  uint32_t L, const uint8_t* __restrict__ qbytes, const uint64_t* __restrict__ qoff, uint32_t nq,
+                  uint32_t* __restrict__ start_out, uint32_t* __restrict__ end_out)
+{
+    const uint32_t gq = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gq >= nq) return;
+    const uint64_t qb = qoff[gq];
+    const uint32_t len = (uint32_t)(qoff[gq + 1] - qb);
+    const uint8_t* q = qbytes + qb;
+    uint32_t c = len < L ? len : L;                                  // :932 min(strlen, L)
+    for (uint32_t i = 0; i < c; ++i)
+        if (q[i] == 0) { c = i; break; }
+    const uint64_t q0 = load_query_word(q, 0, c), q1 = load_query_word(q, 8, c), q2 = load_query_word(q, 16, c),
+                   q3 = load_query_word(q, 24, c);
+    uint32_t probes[QF_MAX_PROBES];
+    int np = 0;
+
+    auto compare = [&](uint32_t pos) -> int {
+        int r = 0;
+        if ((uint64_t)pos + c <= fsize) {
+            for (uint32_t off = 0; off < c; off += 8) {
+                const uint32_t nb = (c - off) < 8u ? (c - off) : 8u;
+                const uint64_t tw = keep_top_bytes(lower8(load_be64(file, (uint64_t)pos + off)), (int)nb);
+                const uint32_t j = off >> 3;
+                const uint64_t w = j == 0 ? q0 : (j == 1 ? q1 : (j == 2 ? q2 : (j == 3 ? q3 : load_query_word(q, off, c))));
+                if (tw != w) { r = tw < w ? -1 : 1; break; }
+            }
+        } else {
+            // the read crosses the end of the file: byte i comes from the latest probe that filled line[i]
+            for (uint32_t i = 0; i < c; ++i) {
+                uint32_t b = 0;
+                if ((uint64_t)pos + i < fsize) b = lower1(file[(uint64_t)pos + i]);
+                else
+                    for (int h = np - 1; h >= 0; --h)
+                        if ((uint64_t)probes[h] + i < fsize) { b = lower1(file[(uint64_t)probes[h] + i]); break; }
+                const uint32_t qc = q[i];
+                if (b != qc) { r = b < qc ? -1 : 1; break; }
+            }
+        }
+        if (np < QF_MAX_PROBES) probes[np++] = pos;
+        return r;
+    };
+
+    uint32_t start = 0xFFFFFFFFu, end = 0xFFFFFFFFu;
+    int64_t first = 0, last = (int64_t)n - 1;
+    while (first <= last) {                                          // :937-960
+        const int64_t mid = (first + last) / 2;
+        const int cmp = compare(__ldg(sa + mid));
+        if (cmp < 0) first = mid + 1;
+        else { last = mid - 1; if (cmp == 0) start = (uint32_t)mid; }
+    }
+    if (start != 0xFFFFFFFFu) {                                      // :962-966
+        first = start; last = (int64_t)n - 1;                        // :969
+        while (first <= last) {                                      // :971-993
+            const int64_t mid = (first + last) / 2;
+            const int cmp = compare(__ldg(sa + mid));
+            if (cmp > 0) last = mid - 1;
+            else { first = mid + 1; if (cmp == 0) end = (uint32_t)mid; }
+        }
+    }
+    start_out[gq] = start;
+    end_out[gq] = end;
+}
+
 // engine.c:1181-1185: first == UINT32_MAX -> 0 hits, else min(k, second - first + 1) in u32
 __global__ void hit_counts_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end,
-                                  uint32_t nq, uint32_t k, uint32_t* __restrict__ counts)
+                                  uint32_t nq, uint32_t k, uint32_t n, uint32_t* __restrict__ counts)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nq) return;
     uint32_t s = start[i], c = 0;
-    if (s != 0xFFFFFFFFu) { c = end[i] - s + 1u; if (c > k) c = k; }
+    if (s != 0xFFFFFFFFu) {
+        c = end[i] - s + 1u;
+        if (c > k) c = k;
+        if (s >= n) c = 0;                       // memory safety only: the reference would read past its array here
+        else if (c > n - s) c = n - s;
+    }
     counts[i] = c;
 }
 
@@ -369,7 +493,7 @@ hits_kernel(const uint32_t* __restrict__ sa, const uint32_t* __restrict__ start,
     const uint32_t take = (uint32_t)(hit_off[wq + 1] - o);
     const uint32_t s = start[wq];
     for (uint32_t j = threadIdx.x & 31; j < take; j += 32) {
-        const uint32_t p = sa[(uint64_t)s + j];
+        const uint32_t p = sa[(uint64_t)s + j];      // s + j <= end < n by construction of the counts
         if (hit_pos) hit_pos[o + j] = p;
         if (hit_doc) {
             // record index = number of '\n' in front of p
@@ -404,13 +528,14 @@ __global__ void remap_kernel(const uint32_t* __restrict__ sa, uint32_t n, const 
 // ------------------------------------------------------------------------------ launchers
 cudaError_t sa_launch_newline_count(const uint8_t* text, uint32_t n, uint32_t* counts, cudaStream_t s)
 {
-    const uint32_t tiles = (n + sa::NL_TILE - 1) / sa::NL_TILE;
+    const uint32_t tiles = sa_newline_tiles(n);
     if (!tiles) return cudaSuccess;
     sa::newline_count_kernel<<<tiles, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), n, counts);
     return cudaGetLastError();
 }
 
-uint32_t sa_newline_tiles(uint32_t n) { return (n + sa::NL_TILE - 1) / sa::NL_TILE; }
+// 64-bit arithmetic: n may be as large as 2^32 - 1025 (sharded indexes), where n + 4095 wraps in 32 bits
+uint32_t sa_newline_tiles(uint32_t n) { return (uint32_t)(((uint64_t)n + sa::NL_TILE - 1) / sa::NL_TILE); }
 
 cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, cudaStream_t s)
 {
@@ -421,7 +546,7 @@ cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, 
 cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint32_t* tile_offsets, uint32_t* nlpos,
                                     unsigned long long* nlbits, uint32_t* nlrank, cudaStream_t s)
 {
-    const uint32_t tiles = (n + sa::NL_TILE - 1) / sa::NL_TILE;
+    const uint32_t tiles = sa_newline_tiles(n);
     if (!tiles) return cudaSuccess;
     sa::newline_write_kernel<<<tiles, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), n, tile_offsets, nlpos, nlbits,
                                                    nlrank);
@@ -444,11 +569,11 @@ cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa_, uint32_t n
     return cudaGetLastError();
 }
 
-cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k,
+cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k, uint32_t n,
                                  uint32_t* counts, cudaStream_t s)
 {
     if (!nq) return cudaSuccess;
-    sa::hit_counts_kernel<<<(nq + 255) / 256, 256, 0, s>>>(start, end, nq, k, counts);
+    sa::hit_counts_kernel<<<(nq + 255) / 256, 256, 0, s>>>(start, end, nq, k, n, counts);
     return cudaGetLastError();
 }
 
@@ -460,7 +585,7 @@ cudaError_t sa_launch_scan_u32_to_u64(const uint32_t* counts, uint32_t num, uint
     const uint32_t nb = (num + 1023) / 1024;
     if (!num) return cudaMemsetAsync(off, 0, sizeof(uint64_t), s);
     sa::block_sum_kernel<<<nb, 1024, 0, s>>>(counts, num, sums);
-    sa::scan_u64_serial_kernel<<<1, 32, 0, s>>>(sums, nb);
+    sa::scan_u64_block_kernel<<<1, 1024, 0, s>>>(sums, nb);
     sa::offsets_kernel<<<nb, 1024, 0, s>>>(counts, num, sums, nb, off);
     return cudaGetLastError();
 }
@@ -481,5 +606,15 @@ cudaError_t sa_launch_remap(const uint32_t* sa_, uint32_t n, const uint32_t* map
 {
     if (!n) return cudaSuccess;
     sa::remap_kernel<<<(n + 255) / 256, 256, 0, s>>>(sa_, n, map, quoted_by_text, sa_out, quoted_bits_by_rank);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_query_file(const uint8_t* file, uint64_t file_size, const uint32_t* sa_file, uint32_t n,
+                                 uint32_t max_suffix_length, const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq,
+                                 uint32_t* start, uint32_t* end, cudaStream_t s)
+{
+    if (!nq) return cudaSuccess;
+    sa::query_file_kernel<<<(nq + 127) / 128, 128, 0, s>>>(file, file_size, sa_file, n, max_suffix_length, qbytes, qoff, nq,
+                                                           start, end);
     return cudaGetLastError();
 }

@@ -142,7 +142,26 @@ record_gather_kernel(const uint8_t* __restrict__ src, const unsigned long long* 
     for (uint32_t i = threadIdx.x & 31; i < len; i += 32) out[o + i] = s[i];
 }
 
+// sa_load: how many entries of a[0, n) are >= limit (a corrupt container must not reach the query kernels)
+__global__ void __launch_bounds__(256)
+count_out_of_range_kernel(const uint32_t* __restrict__ a, uint64_t n, uint64_t limit, unsigned int* __restrict__ bad)
+{
+    uint32_t c = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        c += (uint64_t)a[i] >= limit;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(bad, c);
+}
+
 }  // namespace sa
+
+cudaError_t sa_launch_count_out_of_range(const uint32_t* a, uint64_t n, uint64_t limit, unsigned int* bad, cudaStream_t s)
+{
+    if (!n) return cudaSuccess;
+    const uint64_t blocks = (n + 255) / 256;
+    sa::count_out_of_range_kernel<<<(unsigned)(blocks < 2368 ? blocks : 2368), 256, 0, s>>>(a, n, limit, bad);
+    return cudaGetLastError();
+}
 
 cudaError_t sa_launch_dedupe_mark(const uint64_t* hit_off, uint32_t nq, uint32_t* hit_pos, uint32_t* hit_doc,
                                   uint32_t* ucount, uint32_t* table, cudaStream_t s)

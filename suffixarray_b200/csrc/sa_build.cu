@@ -83,11 +83,11 @@ extern "C" void sa_destroy(sa_index* idx)
     if (!idx) return;
     cudaSetDevice(idx->device);
     if (idx->stream) cudaStreamSynchronize(idx->stream);
+    if (idx->default_res) { sa_result_destroy(idx->default_res); idx->default_res = nullptr; }
     DevBuf* all[] = {&idx->text, &idx->sa_final, &idx->nlpos, &idx->sa_file, &idx->qbits, &idx->map,
                      &idx->quoted_text, &idx->keys[0], &idx->keys[1], &idx->vals[0], &idx->vals[1],
                      &idx->aux[0], &idx->aux[1], &idx->lcp, &idx->tie, &idx->amask, &idx->hmask, &idx->counts,
-                     &idx->status, &idx->small, &idx->nl_counts, &idx->codes, &idx->qbytes, &idx->qoff, &idx->qstart,
-                     &idx->qend, &idx->qcounts, &idx->hitoff, &idx->blocksums, &idx->hitpos, &idx->hitdoc,
+                     &idx->status, &idx->small, &idx->nl_counts, &idx->codes, &idx->rowpos,
                      &idx->ext_sa, &idx->ext_lcp, &idx->ext_out, &idx->split_table, &idx->split_offsets,
                      &idx->csv_file, &idx->csv_tq, &idx->csv_td, &idx->csv_te, &idx->csv_tr, &idx->rowbits, &idx->rowrank,
                      &idx->nlbits, &idx->nlrank};
@@ -187,7 +187,7 @@ int sa_stage_prepare(sa_index* idx, uint32_t flags)
     SA_CU(cudaMemsetAsync(sm + SM_ERR, 0, 4 * sizeof(uint32_t), s));       // err + run counter
 
     if (flags & SA_FLAG_LOWERCASE) {
-        SA_CU(sa_launch_lowercase(idx->text.as<uint8_t>(), n, s));
+        SA_CU(sa_launch_lowercase(idx->text.as<uint8_t>(), (uint64_t)n + idx->tail, s));
         st.kernel_launches += 1;
     }
     // document table: positions of '\n' (the reference scans for them per hit, engine.c:1189-1191)
@@ -199,7 +199,7 @@ int sa_stage_prepare(sa_index* idx, uint32_t flags)
         SA_CU(sa_launch_scan_u32(idx->nl_counts.as<uint32_t>(), tiles, sm + SM_NLTOTAL, s));
         SA_CU(cudaMemcpyAsync(idx->h_small + 8, sm + SM_NLTOTAL, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
         // which byte values occur (decides the code width); read back with the newline total
-        SA_CU(sa_launch_byte_hist(idx->text.as<uint8_t>(), n, sm + SM_BYTEHIST, idx->num_sms, s));
+        SA_CU(sa_launch_byte_hist(idx->text.as<uint8_t>(), (uint64_t)n + idx->tail, sm + SM_BYTEHIST, idx->num_sms, s));
         SA_CU(cudaMemcpyAsync(idx->h_small + 256, sm + SM_BYTEHIST, 256 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
         st.kernel_launches += 1;
         SA_CU(cudaStreamSynchronize(s));

@@ -249,7 +249,7 @@ static int scan_column_device(sa_index* src, sa_index* dst, size_t size, uint32_
     *regular = irregular == 0;
     if (irregular) return SA_OK;
     if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
-    dst->n = n;
+    dst->n = n; dst->tail = 0;
     const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
     SA_CU(dst->text.ensure(bytes));
     SA_CU(dst->map.ensure((size_t)n * 4 + 4));
@@ -276,7 +276,7 @@ static int scan_column_host(sa_index* idx, const Mapped& m, uint32_t col, uint32
     const uint64_t n = scan_column(FileView{m.p, m.size}, col, num_columns, h_text.as<uint8_t>(), h_map.as<uint32_t>(),
                                    h_q.as<uint8_t>());
     if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
-    idx->n = n;
+    idx->n = n; idx->tail = 0;
     cudaStream_t s = idx->stream;
     const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
     SA_CU(idx->text.ensure(bytes));
@@ -423,6 +423,9 @@ extern "C" int sa_build_csv_columns(sa_index* const* idxs, const char* const* co
             SA_CU(idx->rowrank.ensure(sa_csv_rowrank_bytes(m.size)));
             SA_CU(cudaMemcpyAsync(idx->rowbits.p, src->rowbits.p, sa_csv_rowbits_bytes(m.size), cudaMemcpyDeviceToDevice, s));
             SA_CU(cudaMemcpyAsync(idx->rowrank.p, src->rowrank.p, sa_csv_rowrank_bytes(m.size), cudaMemcpyDeviceToDevice, s));
+            // ... and of the file (file-semantics probes, record materialisation)
+            SA_CU(idx->csv_file.ensure(sa_csv_padded_bytes(m.size)));
+            SA_CU(cudaMemcpyAsync(idx->csv_file.p, src->csv_file.p, sa_csv_padded_bytes(m.size), cudaMemcpyDeviceToDevice, s));
         }
         SA_CU(cudaStreamSynchronize(s));
         sa_time_collect(idx);
@@ -481,6 +484,33 @@ extern "C" int sa_shard_begin_csv(sa_index* idx, const char* csv_path, const cha
     idx->shard_csv = true;
     idx->shard_csv_regular = regular;
     idx->shard_prepared = true;
+    return SA_OK;
+}
+
+// A CSV index restored by sa_load has the arrays and the row table but not the file bytes: put them
+// back on the device (file-semantics queries and record materialisation read them).
+extern "C" int sa_attach_csv_file(sa_index* idx, const char* csv_path)
+{
+    if (!idx || !csv_path) { sa_set_error("sa_attach_csv_file: NULL argument"); return SA_ERR_INVALID; }
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
+    if (!idx->built || !idx->csv) { sa_set_error("sa_attach_csv_file: no CSV index built"); return SA_ERR_INVALID; }
+    SA_CU(cudaSetDevice(idx->device));
+    Mapped m;
+    std::vector<std::string> cells;
+    int rc = open_csv(csv_path, m, cells);
+    if (rc != SA_OK) return rc;
+    if (m.size != idx->csv_file_bytes) {
+        sa_set_error("%s has %zu bytes, the indexed file had %llu", csv_path, m.size, (unsigned long long)idx->csv_file_bytes);
+        return SA_ERR_IO;
+    }
+    const uint64_t padded = sa_csv_padded_bytes(m.size);
+    SA_CU(idx->csv_file.ensure(padded));
+    uint8_t* d_file = idx->csv_file.as<uint8_t>();
+    const size_t tail = m.size & ~(size_t)15;
+    SA_CU(cudaMemsetAsync(d_file + tail, 0, padded - tail, idx->stream));
+    rc = stream_file_to_device(idx, m.fd, m.size, d_file);
+    if (rc != SA_OK) return rc;
+    SA_CU(cudaStreamSynchronize(idx->stream));
     return SA_OK;
 }
 

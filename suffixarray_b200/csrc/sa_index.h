@@ -86,6 +86,7 @@ struct sa_index {
     cudaStream_t stream = nullptr;
     uint32_t L = 0;
     uint64_t n = 0;
+    uint32_t tail = 0;          // bytes of look-ahead text kept behind the n indexed positions (sa_build_text_tail)
     uint32_t lprime = 0;
     bool built = false;
     bool csv = false;

@@ -14,6 +14,8 @@
 
 #include <vector>
 
+#include <sys/stat.h>
+
 #include "sa_index.h"
 
 namespace {
@@ -108,10 +110,29 @@ extern "C" int sa_load(sa_index* idx, const char* path)
         sa_set_error("%s was built with max_suffix_length %u, this handle has %u", path, h.max_suffix_length, idx->L);
         return SA_ERR_INVALID;
     }
-    if (h.n > SA_MAX_INDEX_BYTES) { sa_set_error("%s: n exceeds the 2^31 limit", path); return SA_ERR_LIMIT; }
+    // sa_save writes any built index, including sharded ones of up to 2^32 - 1025 entries
+    if (h.n > 0xFFFFFFFFull - 1024ull) { sa_set_error("%s: n exceeds the uint32 position range", path); return SA_ERR_LIMIT; }
+    if ((h.flags & 1u) && (h.csv_file_bytes == 0 || h.csv_file_bytes >= (1ull << 32))) {
+        sa_set_error("%s: implausible CSV file size %llu in the header", path, (unsigned long long)h.csv_file_bytes);
+        return SA_ERR_IO;
+    }
+    {   // the file must hold what the header promises
+        struct stat sb;
+        uint64_t need = sizeof h + (uint64_t)h.n * 5;
+        if (h.flags & 1u)
+            need += (uint64_t)h.n * 4 + ((h.n + 31) / 32) * 4 + sa_csv_rowbits_bytes(h.csv_file_bytes) +
+                    sa_csv_rowrank_bytes(h.csv_file_bytes);
+        if (fstat(fileno(in.f), &sb) != 0 || (uint64_t)sb.st_size < need) {
+            sa_set_error("%s is truncated (%llu bytes needed)", path, (unsigned long long)need);
+            return SA_ERR_IO;
+        }
+    }
     idx->built = false;
     sa_invalidate_results(idx);
-    idx->n = h.n;
+    idx->shard_prepared = false;
+    idx->shard_csv = false;
+    idx->csv_file.release();            // a restored CSV index holds no copy of the file (sa_attach_csv_file)
+    idx->n = h.n; idx->tail = 0;
     const size_t n = (size_t)h.n;
     memset(&idx->stats, 0, sizeof idx->stats);
     idx->lprime = idx->L < (uint32_t)n ? idx->L : (uint32_t)n;
@@ -139,6 +160,18 @@ extern "C" int sa_load(sa_index* idx, const char* path)
         rc = read_device(idx, in.f, idx->rowbits.p, sa_csv_rowbits_bytes(h.csv_file_bytes), buf);
         if (rc == SA_OK) rc = read_device(idx, in.f, idx->rowrank.p, sa_csv_rowrank_bytes(h.csv_file_bytes), buf);
         if (rc != SA_OK) return rc;
+    }
+    {   // positions / offsets out of range would become out-of-bounds device reads in the query kernels
+        unsigned int* bad = reinterpret_cast<unsigned int*>(idx->small.as<uint32_t>() + SM_ERR);
+        SA_CU(cudaMemsetAsync(bad, 0, sizeof(unsigned int), s));
+        SA_CU(sa_launch_count_out_of_range(idx->sa_final.as<uint32_t>(), n, n, bad, s));
+        if (h.flags & 1u) SA_CU(sa_launch_count_out_of_range(idx->sa_file.as<uint32_t>(), n, h.csv_file_bytes, bad, s));
+        SA_CU(cudaMemcpyAsync(idx->h_small, bad, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+        SA_CU(cudaStreamSynchronize(s));
+        if (idx->h_small[0]) {
+            sa_set_error("%s is corrupt: %u array entries out of range", path, idx->h_small[0]);
+            return SA_ERR_IO;
+        }
     }
     if (n) {
         rc = sa_stage_prepare(idx, 0);          // record table (+ alphabet codes, unused by queries)

@@ -255,7 +255,7 @@ extern "C" int sa_shard_begin(sa_index* idx, const uint8_t* text, uint64_t n, ui
     SA_CU(cudaSetDevice(idx->device));
     cudaStream_t s = idx->stream;
     idx->timing = (flags & SA_FLAG_TIMING) != 0;
-    idx->n = n;
+    idx->n = n; idx->tail = 0;
     idx->built = false;
     sa_invalidate_results(idx);
     idx->csv = false;

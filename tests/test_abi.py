@@ -29,7 +29,7 @@ def test_header_symbols_are_exported():
 
 
 def test_abi_version():
-    assert S.lib().sa_abi_version() == 1
+    assert S.lib().sa_abi_version() == 2
 
 
 def test_stats_struct_matches_header():

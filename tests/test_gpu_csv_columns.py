@@ -137,14 +137,14 @@ def test_suffix_array_class_multi_column_and_multiline_rows(tmp_path):
         f.write(data)
     dict_rows = [dict(zip(rows[0], r)) for r in rows]
 
-    one = SuffixArray(csv_file=path, search_column="name", max_suffix_length=L)
+    one = SuffixArray(csv_file=path, search_column="name", max_suffix_length=L, csv_query="text")
     got = one.query_records("unit 297", k=10)                    # after 99 multi-line cells: rows must not drift
     assert got == [dict_rows[298]] and got[0]["name"] == "Globex\nUnit 297"
     got = one.query_records("acme 100 ", k=10)
     assert got == [dict_rows[101]]
     one.close()
 
-    sa = SuffixArray(csv_file=path, search_column=["name", "note", "city"], max_suffix_length=L)
+    sa = SuffixArray(csv_file=path, search_column=["name", "note", "city"], max_suffix_length=L, csv_query="text")
     assert sa.search_columns == ["name", "note", "city"] and len(sa.suffix_array) == 3
     name_hits = sa.query_records("acme", k=1000, column="name")
     note_hits = sa.query_records("acme", k=1000, column="note")

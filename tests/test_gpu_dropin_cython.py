@@ -81,15 +81,16 @@ def test_partitioned_documents_walk(CySuffixArray):
     text = O.oracle_lowercase(np.frombuffer("\n".join(docs).encode(), np.uint8))
     arrays = sa.suffix_array
     assert len(arrays) == -(-text.size // 1500) and len(arrays) > 3
-    for p, got in enumerate(arrays):
-        assert np.array_equal(got, O.oracle_build(text[p * 1500:(p + 1) * 1500], 32))
+    for p, got in enumerate(arrays):               # partition p is sorted on `text + p * cut` of the ONE joined buffer (pyx:176-180)
+        n_p = min(1500, text.size - p * 1500)
+        assert np.array_equal(got, O.oracle_build_tail(text[p * 1500: p * 1500 + n_p + 960], n_p, 32))
     low = [d.lower() for d in docs]
     starts = np.concatenate([[0], np.flatnonzero(text == 10) + 1])
     for q, k in (("inc", 7), ("a", 40), ("group", 1000), (low[13], 5)):
         want = []
         for p in range(len(arrays)):                                # the reference's walk, on the oracle
             part = text[p * 1500:(p + 1) * 1500]
-            s, e = O.oracle_query(part, arrays[p], 32, [q.encode()])
+            s, e = O.oracle_query_tail(text[p * 1500: p * 1500 + part.size + 960], part.size, arrays[p], 32, [q.encode()])
             off, pos, _ = O.oracle_hits(part, arrays[p], s, e, k - len(want))
             want += [low[int(np.searchsorted(starts, int(x) + p * 1500, side="right") - 1)] for x in pos]
             if len(want) >= k:
@@ -111,11 +112,11 @@ def test_csv_rows_columns_and_save_load(CySuffixArray, tmp_path):
         f.write(buf.getvalue().encode())
     dict_rows = [dict(zip(rows[0], r)) for r in rows]
 
-    one = CySuffixArray(csv_file=path, search_column="name", max_suffix_length=32)
+    one = CySuffixArray(csv_file=path, search_column="name", max_suffix_length=32, csv_query="text")
     assert one.columns == rows[0]
     assert one.query_records("unit 297", k=10) == [dict_rows[298]]
     assert one.query_records("name")[0] == dict(zip(rows[0], rows[0]))     # header is row 0
-    py = PySuffixArray(csv_file=path, search_column="name", max_suffix_length=32)
+    py = PySuffixArray(csv_file=path, search_column="name", max_suffix_length=32, csv_query="text")
     assert np.array_equal(one.suffix_array, py.suffix_array)
     for q in ("acme", "globex", "9 hold", "zzz"):
         assert one.query_records(q, k=40) == py.query_records(q, k=40)
@@ -126,7 +127,7 @@ def test_csv_rows_columns_and_save_load(CySuffixArray, tmp_path):
     with pytest.raises(ValueError):
         CySuffixArray(csv_file=path)
 
-    sa = CySuffixArray(csv_file=path, search_column=["name", "note", "city"], max_suffix_length=32)
+    sa = CySuffixArray(csv_file=path, search_column=["name", "note", "city"], max_suffix_length=32, csv_query="text")
     assert sa.search_columns == ["name", "note", "city"] and len(sa.suffix_array) == 3
     name_hits = sa.query_records("acme", k=1000, column="name")
     note_hits = sa.query_records("acme", k=1000, column="note")

@@ -73,32 +73,29 @@ def test_gloo_world2_aggregation(tmp_path):
     assert digests[0] != digests[1]                  # distinct partitions
 
 
-def test_csv_row_table_of_the_python_mirror(tmp_path):
-    """SuffixArray._open_csv (host side of record materialisation) cuts rows at '\\n' outside quotes,
-    header = row 0 -- the same definition the device row table uses (csv_rows_kernel): checked here
-    against Python's csv module on a file with raw newlines inside quoted cells, ragged rows, CRLF."""
+def test_csv_row_table_definition(tmp_path):
+    """The row table the device builds (csv_rows_kernel -> sa_copy_row_starts, records cut by
+    sa_query_records) is checked on the GPU against oracle_csv_row_starts; here that definition --
+    rows end at '\n' outside quotes, header = row 0 -- is checked against Python's csv module on a file
+    with raw newlines inside quoted cells, ragged rows and CRLF."""
     import csv
     import io
-    from suffixarray_b200.suffix_array import SuffixArray
+    from oracle import pyoracle as O
     rows = [["id", "name", "note"], ["1", "plain", "x"], ["2", "two\nlines", 'say "hi"'], ["3", "a,b", "three\n\nlines"],
             ["4"], ["5", "crlf\r\ninside", "y", "extra"], ["6", "last", ""]]
     for term, trailing in (("\n", True), ("\n", False), ("\r\n", True)):
         buf = io.StringIO()
         csv.writer(buf, lineterminator=term).writerows(rows)
-        data = buf.getvalue() if trailing else buf.getvalue()[: -len(term)]
-        path = tmp_path / "rows.csv"
-        path.write_bytes(data.encode())
-        sa = SuffixArray.__new__(SuffixArray)                # no index: only the row table is under test
-        sa._csv_mm = None
-        sa._idx = None
-        sa._open_csv(str(path))
-        assert sa._row_starts.size == len(rows)
+        data = (buf.getvalue() if trailing else buf.getvalue()[: -len(term)]).encode()
+        starts = O.oracle_csv_row_starts(data)
+        nrows = starts.size - 1 - (1 if trailing else 0)          # a trailing '\n' opens one empty last row
+        assert nrows == len(rows)
         got = []
-        for d in range(len(rows)):
-            line = sa._csv_mm[int(sa._row_starts[d]):int(sa._row_ends[d])].decode().rstrip("\r")
+        for d in range(nrows):
+            end = int(starts[d + 1]) - (1 if d + 1 < starts.size - 1 else 0)
+            line = data[int(starts[d]):end].decode().rstrip("\r")
             got.append(next(csv.reader([line])))
         assert got == rows
-        sa.close()
 
 
 SHARD_WORKER = r"""

@@ -15,6 +15,11 @@ from suffixarray_b200 import workloads as W
 needs_ref = pytest.mark.skipif(not O.have_ref(), reason="oracle/_ref/libsa_ref.so not built (no /root/reference)")
 
 
+def need_ref():
+    if not O.have_ref():
+        pytest.skip("oracle/_ref/libsa_ref.so not built (no /root/reference)")
+
+
 @needs_ref
 @pytest.mark.parametrize("sigma", GRID_SIGMA)
 def test_build_grid(sigma):
@@ -191,3 +196,89 @@ def test_csv_oracle_matches_reference_on_random_files():
                 assert np.array_equal(sa_file, rsa) and np.array_equal(q_rank, rq), (trial, cname)
         finally:
             os.unlink(path)
+
+
+# ----------------------------------------------------------------------------- CSV query path (row a9)
+def _csv_cases():
+    from suffixarray_b200 import workloads as W
+    yield "quoted20", W.csv_file_bytes(3000, seed=11, quoted_fraction=0.2), "name", 1, 4
+    yield "plain", W.csv_file_bytes(1500, seed=12, quoted_fraction=0.0), "city", 2, 4
+    # a short file and a long max_suffix_length: probes cross the end of the file (stale line tail)
+    yield "tiny", b"name,x\nabcabcabc,1\nabcab,2\nbcabc,3\nabc,4", "name", 0, 2
+
+
+def _csv_queries(text, rng, nq):
+    qs = []
+    for _ in range(nq):
+        a = int(rng.integers(0, max(1, text.size - 1)))
+        m = int(rng.integers(1, 40))
+        q = bytes(text[a:a + m]).split(b"\n")[0]
+        if q and b"\0" not in q:
+            qs.append(q)
+    return qs + [b"inc", b"llc co", b"a b", b"corp,spring", b'co",lake', b"zzzzzz", b"7", b"abc", b"abcabcabc,1", b"c,4"]
+
+
+@pytest.mark.parametrize("L", [8, 32, 64])
+def test_file_query_oracle_vs_reference(L, tmp_path):
+    """sao_query_file_batch == get_substring_positions_file (engine.c:920-999) on the reference's own
+    CSV index, for every query the shim does not fence."""
+    need_ref()
+    rng = np.random.default_rng(300 + L)
+    for name, data, column, col, ncols in _csv_cases():
+        p = str(tmp_path / f"{name}.csv")
+        with open(p, "wb") as f:
+            f.write(data)
+        R = O.RefCsvIndex(p, column, L)
+        sa, _ = R.arrays()
+        text, _, _ = O.oracle_csv_scan(data, col, ncols)
+        qs = _csv_queries(text, rng, 600)
+        rs, re_, sk = R.query(qs)
+        ws, we = O.oracle_query_file(data, sa, L, qs)
+        keep = sk == 0
+        assert keep.sum() > len(qs) // 2, name
+        assert np.array_equal(rs[keep], ws[keep]) and np.array_equal(re_[keep], we[keep]), name
+        R.close()
+
+
+def test_file_records_formula_vs_reference(tmp_path):
+    """What SA_RECORDS_REFERENCE_COMPAT reproduces: get_matching_records_file (engine.c:1326-1390)
+    returns file[row_start + (offset >= 4096) : row_end - 1] for a hit at file offset `offset` in the row
+    [row_start, row_end) of the file (first byte dropped for offsets >= 4096, last byte always)."""
+    need_ref()
+    from suffixarray_b200 import workloads as W
+    data = W.csv_file_bytes(2000, seed=13, quoted_fraction=0.1)
+    p = str(tmp_path / "r.csv")
+    with open(p, "wb") as f:
+        f.write(data)
+    R = O.RefCsvIndex(p, "name", 32)
+    sa, _ = R.arrays()
+    rows = O.oracle_csv_row_starts(data)
+    text, _, _ = O.oracle_csv_scan(data, 1, 4)
+    rng = np.random.default_rng(5)
+    qs = [q for q in _csv_queries(text, rng, 300) if not q.startswith(b'"')]
+    checked = 0
+    for q in qs:
+        recs = R.records(q, 7)
+        if not recs:
+            continue
+        s, e, sk = R.query([q])
+        assert sk[0] == 0
+        take = min(7, int(e[0]) - int(s[0]) + 1)
+        assert len(recs) == take
+        for j in range(take):
+            off = int(sa[int(s[0]) + j])
+            r = int(np.searchsorted(rows[:-1], off, side="right") - 1)
+            a, b = int(rows[r]), int(rows[r + 1]) - 1          # [a, b): the line without its '\n'
+            want = data[a + (1 if off >= 4096 else 0): max(b - 1, a)]
+            assert recs[j] == want, (q, j, off, recs[j], want)
+            checked += 1
+    assert checked > 200
+    R.close()
+
+
+def test_dedupe_oracle_small():
+    off = np.array([0, 5, 5, 8], dtype=np.uint64)
+    pos = np.array([10, 11, 12, 13, 14, 20, 21, 22], dtype=np.uint32)
+    doc = np.array([3, 1, 3, 1, 2, 9, 9, 9], dtype=np.uint32)
+    o, p, d = O.oracle_dedupe(off, pos, doc)
+    assert o.tolist() == [0, 3, 3, 4] and p.tolist() == [10, 11, 14, 20] and d.tolist() == [3, 1, 2, 9]
