@@ -261,6 +261,30 @@ int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, const uint16_
                           int nranks, int my_rank, const uint8_t* handles, uint64_t global_offset);
 int sa_shard_mark_built(sa_index* idx);
 
+/* ---- The native driver of the multi-GPU build (sa_multi.cu): the whole pipeline above in ONE call
+ * per rank.  The small exchanges (histogram sum, counts, buffer handles, shard edges) and the barriers
+ * go through a node-local communicator; text slices, records and array slices move GPU to GPU as peer
+ * stores over NVLink.  Each rank uploads only ITS slice of the text.
+ *   sa_comm_create_local: the ranks are threads of one process (out: nranks handles)
+ *   sa_comm_create_shm:   one process per GPU on one node (torchrun); `name` ("/..." unique per job)
+ *                         names a POSIX shared-memory object rank 0 creates
+ * sa_shard_build: text_slice = text[slice_off, slice_off + slice_len) (host pointer, or a device
+ * pointer with SA_FLAG_DEVICE_TEXT); the slices of the ranks tile [0, n) in rank order.  phase_ms
+ * (optional, 8 floats): text, prepare, pack+hist, split, exchange, sort+refine, edges, finish+replicate.
+ * Afterwards every rank's index holds the text and the complete array (a replica for queries).
+ * sa_build_text_multi: the same over the GPUs (handles) of ONE process, a thread per handle. */
+typedef struct sa_comm sa_comm;
+int sa_comm_create_local(int nranks, sa_comm** out);
+int sa_comm_create_shm(const char* name, int rank, int nranks, sa_comm** out);
+void sa_comm_destroy(sa_comm* c);
+int sa_comm_rank(const sa_comm* c);
+int sa_comm_size(const sa_comm* c);
+int sa_comm_barrier(sa_comm* c);
+int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_slice, uint64_t slice_off, uint64_t slice_len,
+                   uint64_t n, uint32_t flags, float* phase_ms);
+int sa_shard_info(const sa_index* idx, uint64_t* shard_records, uint64_t* exchange_bytes_sent);
+int sa_build_text_multi(sa_index* const* idxs, int ndev, const uint8_t* text, uint64_t n, uint32_t flags);
+
 /* Persistence (the reference only sketches it: write_suffix_array / read_into_suffix_array_file,
  * engine.c:1098-1165, TODO.md).  sa_save writes one container file (text, ORDER-E positions, and for
  * CSV indexes the file offsets + quoted bits); sa_load restores it into a handle created with the

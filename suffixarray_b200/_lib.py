@@ -38,6 +38,8 @@ EXPORTS = [
     "sa_save", "sa_load", "sa_export_reference_files",
     "sa_result_create", "sa_result_destroy", "sa_query_ranges_r", "sa_query_hits_r", "sa_query_records_size",
     "sa_query_records", "sa_result_stats", "sa_num_rows", "sa_copy_row_starts", "sa_attach_csv_file",
+    "sa_comm_create_local", "sa_comm_create_shm", "sa_comm_destroy", "sa_comm_rank", "sa_comm_size", "sa_comm_barrier",
+    "sa_shard_build", "sa_shard_info", "sa_build_text_multi",
 ]
 
 
@@ -165,6 +167,16 @@ def lib():
     L.sa_num_rows.restype = C.c_uint64
     L.sa_copy_row_starts.argtypes = [_vp, _vp, C.c_uint64]
     L.sa_attach_csv_file.argtypes = [_vp, C.c_char_p]
+    L.sa_comm_create_local.argtypes = [C.c_int, C.POINTER(_vp)]
+    L.sa_comm_create_shm.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(_vp)]
+    L.sa_comm_destroy.argtypes = [_vp]
+    L.sa_comm_destroy.restype = None
+    L.sa_comm_rank.argtypes = [_vp]
+    L.sa_comm_size.argtypes = [_vp]
+    L.sa_comm_barrier.argtypes = [_vp]
+    L.sa_shard_build.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.POINTER(C.c_float)]
+    L.sa_shard_info.argtypes = [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.sa_build_text_multi.argtypes = [C.POINTER(_vp), C.c_int, _vp, C.c_uint64, C.c_uint32]
     _lib = L
     return L
 
@@ -341,6 +353,53 @@ class Index:
         r = self._own_result()
         r.ranges(queries, k, SA_QUERY_FILE_SEMANTICS if file_semantics else 0)
         return r.records(dedupe, compat)
+
+
+SHARD_PHASES = ("text", "prepare", "pack+hist", "split", "exchange", "sort+refine", "edges", "finish+replicate")
+
+
+class Comm:
+    """Node-local communicator of the native multi-GPU driver (``sa_comm``): one per rank (process)."""
+
+    def __init__(self, name: str, rank: int, nranks: int):
+        self._h = _vp()
+        check(lib().sa_comm_create_shm(name.encode(), rank, nranks, C.byref(self._h)))
+        self.rank, self.nranks = rank, nranks
+
+    def barrier(self):
+        check(lib().sa_comm_barrier(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().sa_comm_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+def shard_build(index: "Index", comm: Comm, slice_ptr: int, slice_off: int, slice_len: int, n: int, flags: int = 0):
+    """One rank of the native sample-sort build (sa_shard_build).  slice_ptr: host address of this rank's
+    slice of the text (device address with SA_FLAG_DEVICE_TEXT).  -> dict of per-phase host wall ms."""
+    ph = (C.c_float * 16)()
+    check(lib().sa_shard_build(index._h, comm._h, slice_ptr, slice_off, slice_len, n, flags, ph))
+    return {name: float(ph[i]) for i, name in enumerate(SHARD_PHASES)}
+
+
+def shard_info(index: "Index"):
+    a, b = C.c_uint64(0), C.c_uint64(0)
+    check(lib().sa_shard_info(index._h, C.byref(a), C.byref(b)))
+    return int(a.value), int(b.value)
+
+
+def build_text_multi(indexes, text, lowercase: bool = False, timing: bool = False):
+    """ONE index over the GPUs of `indexes` (handles of one process, a thread per handle): every handle
+    ends up with the text and the complete array."""
+    t = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray, memoryview)) \
+        else np.ascontiguousarray(text, dtype=np.uint8)
+    n = len(indexes)
+    hs = (_vp * n)(*[ix._h for ix in indexes])
+    flags = (SA_FLAG_LOWERCASE if lowercase else 0) | (SA_FLAG_TIMING if timing else 0)
+    check(lib().sa_build_text_multi(hs, n, _ptr(t) if t.size else None, t.size, flags))
 
 
 def _pack(queries):

@@ -61,7 +61,8 @@ uint32_t sa_newline_tiles(uint32_t n);
 cudaError_t sa_launch_newline_count(const uint8_t* text, uint32_t n, uint32_t* counts, cudaStream_t s);
 cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, cudaStream_t s);
 cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint32_t* tile_offsets,
-                                    uint32_t* nlpos, unsigned long long* nlbits, uint32_t* nlrank, cudaStream_t s);
+                                    uint32_t* nlpos, unsigned long long* nlbits, uint32_t* nlrank, cudaStream_t s,
+                                    uint32_t count_base = 0, uint32_t pos_base = 0);
 cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa, uint32_t n, uint32_t max_suffix_length,
                             const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
                             uint32_t* end, int mode /* 0 auto, 1 thread per query, 2 eight lanes per query */,

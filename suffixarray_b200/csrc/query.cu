@@ -174,11 +174,15 @@ __device__ __forceinline__ uint32_t nl_mask8(uint64_t w)
 // positions of the '\n' bytes (nlpos, ascending) and a rank structure over them: one bit per text
 // byte (nlbits, 64 per word) + the number of '\n' in front of every 64-byte block (nlrank), so
 // "record index of text position p" is two independent loads instead of a bisection over nlpos.
+// count_base / pos_base: the kernel may run on a slice of a longer text (sharded preparation): text16,
+// nlbits and nlrank then point at the slice, the counts start at count_base (newlines in front of the
+// slice) and positions at pos_base; nlpos may be NULL (built afterwards from the rank structure).
 __global__ void __launch_bounds__(256) newline_write_kernel(const uint4* __restrict__ text16, uint32_t n,
                                                             const uint32_t* __restrict__ tile_offsets,
                                                             uint32_t* __restrict__ nlpos,
                                                             unsigned long long* __restrict__ nlbits,
-                                                            uint32_t* __restrict__ nlrank)
+                                                            uint32_t* __restrict__ nlrank, uint32_t count_base,
+                                                            uint32_t pos_base)
 {
     __shared__ uint32_t ws[8];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -194,7 +198,7 @@ __global__ void __launch_bounds__(256) newline_write_kernel(const uint4* __restr
     }
     if (lane == 31) ws[warp] = inc;
     __syncthreads();
-    uint32_t pre = tile_offsets[blockIdx.x];
+    uint32_t pre = tile_offsets[blockIdx.x] + count_base;
     for (int w = 0; w < warp; ++w) pre += ws[w];
     uint32_t o = pre + inc - c;
     {
@@ -208,11 +212,11 @@ __global__ void __launch_bounds__(256) newline_write_kernel(const uint4* __restr
             nlrank[blk] = o;
         }
     }
-    if (c) {
+    if (c && nlpos) {
         const uint8_t* b = reinterpret_cast<const uint8_t*>(&v);
 #pragma unroll
         for (int i = 0; i < 16; ++i)
-            if (b[i] == '\n') nlpos[o++] = (uint32_t)(byte0 + i);
+            if (b[i] == '\n') nlpos[o++] = pos_base + (uint32_t)(byte0 + i);
     }
 }
 
@@ -544,12 +548,13 @@ cudaError_t sa_launch_scan_u32(uint32_t* counts, uint32_t num, uint32_t* total, 
 }
 
 cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint32_t* tile_offsets, uint32_t* nlpos,
-                                    unsigned long long* nlbits, uint32_t* nlrank, cudaStream_t s)
+                                    unsigned long long* nlbits, uint32_t* nlrank, cudaStream_t s, uint32_t count_base,
+                                    uint32_t pos_base)
 {
     const uint32_t tiles = sa_newline_tiles(n);
     if (!tiles) return cudaSuccess;
     sa::newline_write_kernel<<<tiles, 256, 0, s>>>(reinterpret_cast<const uint4*>(text), n, tile_offsets, nlpos, nlbits,
-                                                   nlrank);
+                                                   nlrank, count_base, pos_base);
     return cudaGetLastError();
 }
 

@@ -87,7 +87,7 @@ extern "C" void sa_destroy(sa_index* idx)
     DevBuf* all[] = {&idx->text, &idx->sa_final, &idx->nlpos, &idx->sa_file, &idx->qbits, &idx->map,
                      &idx->quoted_text, &idx->keys[0], &idx->keys[1], &idx->vals[0], &idx->vals[1],
                      &idx->aux[0], &idx->aux[1], &idx->lcp, &idx->tie, &idx->amask, &idx->hmask, &idx->counts,
-                     &idx->status, &idx->small, &idx->nl_counts, &idx->codes, &idx->rowpos,
+                     &idx->status, &idx->small, &idx->nl_counts, &idx->codes, &idx->rowpos, &idx->pack_keys, &idx->pack_pos, &idx->hist16,
                      &idx->ext_sa, &idx->ext_lcp, &idx->ext_out, &idx->split_table, &idx->split_offsets,
                      &idx->csv_file, &idx->csv_tq, &idx->csv_td, &idx->csv_te, &idx->csv_tr, &idx->rowbits, &idx->rowrank,
                      &idx->nlbits, &idx->nlrank};
@@ -104,6 +104,13 @@ extern "C" void sa_destroy(sa_index* idx)
         if (idx->peer_mapped[g]) { cudaIpcCloseMemHandle(idx->peer_keys[g]); cudaIpcCloseMemHandle(idx->peer_pos[g]); }
     for (int g = 0; g < 16; ++g)
         if (idx->peer_final_mapped[g]) cudaIpcCloseMemHandle(idx->peer_final[g]);
+    for (int g = 0; g < 16; ++g) {
+        if (idx->peer_text[g].mapped) cudaIpcCloseMemHandle(idx->peer_text[g].ptr);
+        if (idx->peer_nlbits[g].mapped) cudaIpcCloseMemHandle(idx->peer_nlbits[g].ptr);
+        if (idx->peer_nlrank[g].mapped) cudaIpcCloseMemHandle(idx->peer_nlrank[g].ptr);
+    }
+    if (idx->h_big) cudaFreeHost(idx->h_big);
+    if (idx->push_stream) cudaStreamDestroy(idx->push_stream);
     for (cudaEvent_t e : idx->event_pool) cudaEventDestroy(e);
     if (idx->h_small) cudaFreeHost(idx->h_small);
     if (idx->stream) cudaStreamDestroy(idx->stream);
@@ -213,11 +220,21 @@ int sa_stage_prepare(sa_index* idx, uint32_t flags)
         st.kernel_launches += 3;
         st.num_docs = (uint64_t)idx->num_nl + 1;
     }
-    // alphabet: dense order-preserving codes when <= 128 byte values occur (NUL is always code 0)
+    return sa_stage_alphabet(idx, idx->h_small + 256);
+}
+
+// Alphabet: dense order-preserving codes when <= 128 byte values occur (NUL is always code 0).
+// present[256]: which byte values occur in the text (host).  Encodes idx->text into idx->codes and
+// leaves idx->code, idx->cb0, idx->max_chars set.
+int sa_stage_alphabet(sa_index* idx, const uint32_t* present)
+{
+    cudaStream_t s = idx->stream;
+    const uint32_t n = (uint32_t)idx->n;
+    sa_stats& st = idx->stats;
+    uint32_t* sm = idx->small.as<uint32_t>();
     sa::CodeInfo ci{8, 0x100u, 0x100u};
     if (idx->lprime) {
         ScopedPhase ph(idx, &st.ms_pack);
-        const uint32_t* present = idx->h_small + 256;
         uint8_t* table = reinterpret_cast<uint8_t*>(idx->h_small + 512);
         uint32_t next = 1;
         table[0] = 0;

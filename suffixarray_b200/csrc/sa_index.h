@@ -114,6 +114,18 @@ struct sa_index {
     sa::CodeInfo code{8, 0x100u, 0x100u};
     int cb0 = 8, max_chars = 8;   // suffix bytes in the round-0 key / per key word
 
+    // native multi-GPU driver (sa_multi.cu): peers' buffers this rank stores into, mapped through CUDA IPC
+    struct PeerMapping {
+        void* ptr = nullptr;
+        cudaIpcMemHandle_t h{};
+        bool mapped = false;
+    };
+    PeerMapping peer_text[16], peer_nlbits[16], peer_nlrank[16];
+    DevBuf pack_keys, pack_pos, hist16;       // round-0 records of this rank's slice of positions, splitter histogram
+    uint8_t* h_big = nullptr;                 // pinned, one mailbox (256 KiB + 8 KiB)
+    cudaStream_t push_stream = nullptr;       // high priority: peer pushes that must not queue behind the sort kernels
+    uint64_t shard_m_last = 0, shard_exchange_bytes = 0;
+
     // sharded (multi-GPU) build state, see sa_shard.cu
     bool shard_prepared = false;
     bool shard_csv = false;          // the sharded build's text is a CSV column (sa_shard_begin_csv): remap when the array is complete
@@ -199,6 +211,7 @@ struct ScopedPhase {
 
 int sa_build_resident(sa_index* idx, uint32_t flags);
 int sa_stage_prepare(sa_index* idx, uint32_t flags);
+int sa_stage_alphabet(sa_index* idx, const uint32_t* present);
 const uint8_t* sa_key_source(const sa_index* idx);
 int sa_ensure_scratch(sa_index* idx, uint32_t m);
 int sa_stage_sort_refine(sa_index* idx, uint32_t m, bool identity, uint32_t** sa_sorted);

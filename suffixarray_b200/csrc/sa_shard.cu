@@ -545,8 +545,13 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     }
     if (m == 0) return SA_OK;
     cudaStream_t s = idx->stream;
+    // replication runs beside the finishing kernels: highest stream priority, so that its blocks are
+    // scheduled as soon as SM resources free up instead of queueing behind the finish kernel's grid
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     for (int g = 0; g < nranks; ++g)
-        if (g != my_rank && !idx->copy_streams[g]) SA_CU(cudaStreamCreateWithFlags(&idx->copy_streams[g], cudaStreamNonBlocking));
+        if (g != my_rank && !idx->copy_streams[g])
+            SA_CU(cudaStreamCreateWithPriority(&idx->copy_streams[g], cudaStreamNonBlocking, prio_hi));
     constexpr int CHUNKS = 8;
     for (int c = 0; c < CHUNKS; ++c)
         if (!idx->chunk_ev[c]) SA_CU(cudaEventCreateWithFlags(&idx->chunk_ev[c], cudaEventDisableTiming));
