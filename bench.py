@@ -81,6 +81,9 @@ def parse_args():
                          "ranks, replicas identical by digest")
     ap.add_argument("--share-builder", action="store_true",
                     help="global mode: the host-buffer leg reuses the device leg's index (half the scratch; for scale runs)")
+    ap.add_argument("--driver", default="native", choices=["native", "python"],
+                    help="global mode: the library's own driver (sa_shard_build: one call per rank, node-local communicator, "
+                         "every rank uploads only its slice of the text) or the round-1 Python loop over torch.distributed")
     ap.add_argument("--mode", default="global", choices=["global", "partition"],
                     help="N > 1: one global index built as a sample sort (default) or one independent "
                          "partition per GPU (the reference's own partitioning, suffix_array.pyx:148-180)")
@@ -231,7 +234,7 @@ def run_ours(args):
     S.lib()   # fail loudly when the extension is missing
     L = args.max_suffix_length
     if world > 1 and args.mode == "global":
-        return run_ours_global(args, world, rank, local)
+        return (run_ours_global_native if args.driver == "native" else run_ours_global)(args, world, rank, local)
 
     text, qbytes, qoff, lower = make_workload(args.workload, rank)
     n, nq = int(text.size), int(qoff.size - 1)
@@ -526,6 +529,182 @@ def run_ours_global(args, world, rank, local):
     for b in builders.values():
         if b is not None:
             b.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    return result
+
+
+def run_ours_global_native(args, world, rank, local):
+    """N > 1: ONE index over the concatenation of the N per-rank workload texts (weak scaling of a single
+    global index), built by the library's native driver: every rank hands sa_shard_build ITS text slice
+    (resident in HBM for the `value` leg, in pinned host memory for the e2e leg) and ends up with the
+    whole text and the complete array; it then answers its own query batch."""
+    import torch
+    import torch.distributed as dist
+    from suffixarray_b200 import _lib as S
+
+    L = args.max_suffix_length
+    dev = torch.device("cuda", local)
+    text_r, qbytes, qoff, lower = make_workload(args.workload, rank)
+    part = np.concatenate([text_r, np.frombuffer(b"\n", np.uint8)]) if rank < world - 1 else text_r
+    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(sizes, torch.tensor([part.size], dtype=torch.int64, device=dev))
+    sizes = [int(x.item()) for x in sizes]
+    n = int(sum(sizes))
+    off = int(sum(sizes[:rank]))
+    mlen = int(part.size)
+    nq = int(qoff.size - 1)
+    h_part = torch.from_numpy(part).pin_memory()              # e2e leg: this rank's slice, pinned host memory
+    d_part = torch.from_numpy(part).to(dev)                   # value leg: the slice resident in HBM
+    h_q = torch.from_numpy(qbytes).pin_memory()
+    h_qoff = torch.from_numpy(qoff.view(np.int64)).pin_memory()
+    h_start = torch.empty(nq, dtype=torch.int32, pin_memory=True)
+    h_end = torch.empty(nq, dtype=torch.int32, pin_memory=True)
+    h_hoff = torch.empty(nq + 1, dtype=torch.int64, pin_memory=True)
+    hits = {"doc": None, "cap": 0}
+    lib, vp = S.lib(), S._vp
+    comm = S.Comm(f"/sa_bench_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}", rank, world)
+    idx_dev = S.Index(L, device=local)
+    idx_e2e = idx_dev if args.share_builder else S.Index(L, device=local)
+    for kv in (os.environ.get("SA_BENCH_DEBUG") or "").split(","):
+        if "=" in kv:
+            idx_dev.debug_set(kv.split("=")[0], int(kv.split("=")[1]))
+    base_flags = S.SA_FLAG_TIMING | (S.SA_FLAG_LOWERCASE if lower else 0)
+
+    def build(idx, ptr, flags):
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        phases = S.shard_build(idx, comm, ptr, off, mlen, n, flags)
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) * 1e3, phases
+
+    def step():
+        r = {}
+        r["build_dev_ms"], r["phases"] = build(idx_dev, d_part.data_ptr(), base_flags | S.SA_FLAG_DEVICE_TEXT)
+        st = idx_dev.stats()
+        r["onesweep_ms"], r["onesweep_launches"], r["onesweep_elems"] = st["ms_onesweep_sum"], st["radix_passes"], st["onesweep_elems"]
+        r["build_launches"] = st["kernel_launches"]
+        r["rounds"] = st["rounds"]
+        r["m"], r["exchange_bytes"] = S.shard_info(idx_dev)
+        r["build_e2e_ms"], r["phases_e2e"] = build(idx_e2e, h_part.data_ptr(), base_flags)
+        r["build_launches"] += idx_e2e.stats()["kernel_launches"]
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        S.check(lib.sa_query_ranges(idx_e2e._h, vp(h_q.data_ptr()), vp(h_qoff.data_ptr()), nq, K_HITS,
+                                    vp(h_start.data_ptr()), vp(h_end.data_ptr()), vp(h_hoff.data_ptr())))
+        torch.cuda.synchronize()
+        r["range_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        r["query_kernel_ms"] = idx_e2e.stats()["ms_query"]
+        total = int(h_hoff[nq])
+        if total > hits["cap"]:
+            hits["cap"] = int(total * 1.1) + 1024
+            hits["doc"] = torch.empty(hits["cap"], dtype=torch.int32, pin_memory=True)
+        t0 = time.perf_counter()
+        S.check(lib.sa_query_hits(idx_e2e._h, None, vp(hits["doc"].data_ptr()), hits["cap"]))
+        torch.cuda.synchronize()
+        r["query_e2e_ms"] = r["range_e2e_ms"] + (time.perf_counter() - t0) * 1e3
+        st = idx_e2e.stats()
+        r["query_dev_ms"] = st["ms_query"] + st["ms_hits"]
+        r["query_launches"] = st["kernel_launches"]
+        r["hits"] = total
+        return r
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dist.barrier()
+    torch.cuda.synchronize()
+    t_wall0 = time.perf_counter()
+    recs = [step() for _ in range(args.steps)]
+    dist.barrier()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+
+    verify = None
+    if args.verify_single or args.verify_properties:
+        import hashlib
+        d_text = torch.from_numpy(idx_dev.text()).to(dev)       # every replica holds the whole text
+        if args.verify_properties:
+            class _B:
+                idx = idx_dev
+            verify = verify_properties(_B, d_text, n, dev, world)
+        if args.verify_single:
+            mine = idx_dev.sa()
+            digest = hashlib.blake2b(mine.tobytes(), digest_size=8).digest()
+            dg = torch.tensor(list(digest), dtype=torch.int32, device=dev)
+            all_dg = [torch.zeros_like(dg) for _ in range(world)]
+            dist.all_gather(all_dg, dg)
+            replicas_equal = all(bool(torch.equal(all_dg[0], x)) for x in all_dg)
+            if rank == 0:
+                single = S.Index(L, device=local)
+                single.build_text_device(d_text.data_ptr(), n, S.SA_FLAG_TIMING)      # the replicated text is already lower-cased
+                st1 = single.stats()
+                v = {"single_gpu_equal": bool(np.array_equal(single.sa(), mine)), "replicas_equal": replicas_equal, "n": int(n),
+                     "single_gpu_build_ms": round(st1["ms_total"], 2),
+                     "single_gpu_mchars_per_s": round(n / st1["ms_total"] / 1e3, 1)}
+                verify = dict(verify or {}, **v)
+                single.close()
+            del mine
+            dist.barrier()
+        del d_text
+
+    K = args.steps
+    phase_names = list(recs[-1]["phases"].keys())
+    sums = torch.tensor([sum(r["build_dev_ms"] for r in recs), sum(r["query_dev_ms"] for r in recs),
+                         sum(r["build_e2e_ms"] for r in recs), sum(r["query_e2e_ms"] for r in recs), wall_ms,
+                         sum(r["range_e2e_ms"] for r in recs), sum(r["query_kernel_ms"] for r in recs)] +
+                        [sum(r["phases"][p] for r in recs) for p in phase_names] +
+                        [sum(r["phases_e2e"][p] for r in recs) for p in phase_names], dtype=torch.float64, device=dev)
+    dist.all_reduce(sums, op=dist.ReduceOp.MAX)
+    ms = torch.tensor([float(recs[-1]["m"]), float(recs[-1]["exchange_bytes"])], dtype=torch.float64, device=dev)
+    ms_all = [torch.zeros_like(ms) for _ in range(world)]
+    dist.all_gather(ms_all, ms)
+    result = None
+    if rank == 0:
+        build_ms, query_ms, build_e2e_ms, query_e2e_ms = (sums[:4] / K).tolist()
+        range_e2e_ms, range_dev_ms = (sums[5:7] / K).tolist()
+        np_ = len(phase_names)
+        phases = {p: round(v / K, 3) for p, v in zip(phase_names, sums[7:7 + np_].tolist())}
+        phases_e2e = {p: round(v / K, 3) for p, v in zip(phase_names, sums[7 + np_:].tolist())}
+        result = assemble(args, world, recs, n // world, nq, float(n), float(nq * world), build_ms, query_ms,
+                          build_e2e_ms, query_e2e_ms, sums[4].item(), clocks, qbytes.size, text_r, qbytes, qoff, lower,
+                          range_e2e_ms, range_dev_ms)
+        result["e2e"]["h2d_bytes_per_step"] = int(mlen + qbytes.size + (nq + 1) * 8)     # per rank: ITS slice of the text
+        shard_sizes = [int(x[0].item()) for x in ms_all]
+        xbytes = [int(x[1].item()) for x in ms_all]
+        xms = phases.get("exchange", 0.0)
+        rep_bytes = max(shard_sizes) * 4 * (world - 1)
+        result["config_detail"] = {
+            "driver": "native: sa_shard_build, one call per rank; node-local communicator over POSIX shared memory + CUDA IPC",
+            "sharding": "one global index over the N concatenated per-rank texts: every rank uploads its slice and pushes it to "
+                        "the peers over NVLink; sample sort with splitters from the summed 65536-bin key histogram; records "
+                        "stored straight into the owner's sort buffers (peer stores); 128-record halos + device-side junction "
+                        "LCPs; each shard finished in chunks into the final array while finished chunks are pushed into every "
+                        "peer's array",
+            "n_chars_total": n}
+        result["timing"] = "wall clock between barrier + cudaDeviceSynchronize pairs, max over ranks (the build spans several kernels, peer stores and barriers per rank)"
+        if verify is not None:
+            result["verify"] = verify
+        result["multi_gpu"] = {"phases_ms_max_over_ranks": phases, "phases_e2e_ms_max_over_ranks": phases_e2e,
+                               "shard_records": shard_sizes,
+                               "imbalance": round(max(shard_sizes) * world / max(sum(shard_sizes), 1), 4),
+                               "exchange_bytes_sent_per_rank": xbytes,
+                               "exchange_gbs_per_rank": round(max(xbytes) / (xms * 1e-3) / 1e9, 1) if xms > 0 else None,
+                               "text_allgather_gbs_per_rank": (round(mlen * (world - 1) / (phases["text"] * 1e-3) / 1e9, 1)
+                                                               if phases.get("text", 0) > 0 else None),
+                               "replicate_bytes_sent_per_rank": int(rep_bytes),
+                               "finish_replicate_gbs_per_rank": (round(rep_bytes / (phases["finish+replicate"] * 1e-3) / 1e9, 1)
+                                                                 if phases.get("finish+replicate", 0) > 0 else None),
+                               "nvlink_peak_gbs_per_direction": 900.0}
+    if idx_e2e is not idx_dev:
+        idx_e2e.close()
+    idx_dev.close()
+    comm.barrier()
+    comm.close()
     dist.barrier()
     dist.destroy_process_group()
     return result
