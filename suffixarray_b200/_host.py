@@ -33,21 +33,29 @@ class SuffixArrayHost:
     # supplied by the concrete class
     _Index = None
     _build_csv_columns = None
+    _build_text_multi = None     # (indexes, u8 text, lowercase) -> one index sharded over the indexes' GPUs
 
     def __init__(self, max_suffix_length: int = 64, documents=None, csv_file: str | None = None,
                  search_column=None, device: int = 0, csv_query: str = "file", dedupe: bool = False,
-                 reference_records: bool = False):
+                 reference_records: bool = False, devices=None):
         """csv_query: "file" = the reference's CSV bisection (get_substring_positions_file,
         engine.c:920-999: probes compare the raw file bytes -- the only query its Python class
         reaches, suffix_array.pyx:221-247) or "text" = get_substring_positions on the parsed
         column (engine.c:869-918).  dedupe: every record at most once per query (first hit wins; the
         reference keeps duplicates, engine.c:1187).  reference_records: cut CSV records the way
         get_matching_records_file does (last byte dropped, engine.c:1314; first byte too for hits at
-        file offsets >= 4096)."""
+        file offsets >= 4096).  devices=[0, 1, ...]: ONE index built over several GPUs of this process
+        (sample sort, sa_build_text_multi; no torch.distributed needed): every GPU ends up with a replica
+        and query batches are split over them; texts up to 2^32 - 1025 bytes stay ONE index (no 2 GiB
+        partitioning).  A CSV index is built once per device (replicas)."""
         if csv_query not in ("file", "text"):
             raise ValueError('csv_query must be "file" or "text"')
         self.max_suffix_length = int(max_suffix_length)
-        self._device = int(device)
+        self._devices = [int(d) for d in devices] if devices else None
+        if self._devices is not None and len(set(self._devices)) != len(self._devices):
+            raise ValueError("devices must be distinct")
+        self._device = self._devices[0] if self._devices else int(device)
+        self._replicas = []          # devices=: the other GPUs' copies of the (single) index
         self.csv_query = csv_query
         self.dedupe = bool(dedupe)
         self.reference_records = bool(reference_records)
@@ -65,6 +73,11 @@ class SuffixArrayHost:
                 raise ValueError("csv_file= needs search_column=")
             self.construct_truncated_suffix_array_from_csv(csv_file, search_column)
 
+    def _drop_replicas(self) -> None:
+        for r in self._replicas:
+            r.close()
+        self._replicas = []
+
     def _resize(self, count: int) -> None:
         for old in self._parts[count:]:
             old.close()
@@ -81,6 +94,15 @@ class SuffixArrayHost:
                 raise ValueError("Documents must be a list of strings")
         joined = "\n".join(documents).encode("utf-8")             # pyx:143 (no trailing '\n')
         text = np.frombuffer(joined, dtype=np.uint8)
+        self._drop_replicas()
+        if self._devices and len(self._devices) > 1:
+            # one index over all the GPUs: every handle ends up with the text and the complete array
+            self._resize(1)
+            self._replicas = [self._Index(self.max_suffix_length, d) for d in self._devices[1:]]
+            type(self)._build_text_multi([self._parts[0]] + self._replicas, text, True)
+            self._text = self._doc_starts = None
+            self._mode = "documents"
+            return
         pb = int(self.PARTITION_BYTES)
         nparts = max(1, -(-text.size // pb))                      # pyx:148-152
         self._resize(nparts)
@@ -117,8 +139,26 @@ class SuffixArrayHost:
         if not cols or len(set(cols)) != len(cols):
             raise ValueError("search_column must name one or more distinct columns")
         self._resize(len(cols))
+        self._drop_replicas()
         if len(cols) == 1:
             self._parts[0].build_csv(filename, cols[0])
+            if self._devices and len(self._devices) > 1:          # replicas: the same build on every other GPU
+                import threading
+                self._replicas = [self._Index(self.max_suffix_length, d) for d in self._devices[1:]]
+                errs = []
+
+                def _one(ix):
+                    try:
+                        ix.build_csv(filename, cols[0])
+                    except Exception as ex:                       # noqa: BLE001
+                        errs.append(ex)
+                th = [threading.Thread(target=_one, args=(ix,)) for ix in self._replicas]
+                for t in th:
+                    t.start()
+                for t in th:
+                    t.join()
+                if errs:
+                    raise errs[0]
         else:
             type(self)._build_csv_columns(self._parts, filename, cols)
         self.search_columns = cols
@@ -158,6 +198,8 @@ class SuffixArrayHost:
         file_sem = is_csv and self.csv_query == "file"
         if not is_csv and len(self._parts) > 1:
             return self._query_partitioned(sub, nonempty, out, k)
+        if self._replicas and len(self._parts) == 1 and len(sub) >= 2 * (1 + len(self._replicas)):
+            return self._query_replicas(sub, nonempty, out, k, is_csv, file_sem)
         recs = [[] for _ in sub]
         seen = [set() for _ in sub] if (self.dedupe and len(self._walk(column)) > 1) else None
         for p, part in enumerate(self._walk(column)):
@@ -181,11 +223,42 @@ class SuffixArrayHost:
                         seen[j].add(key)
                     recs[j].append(data[ro[h]:ro[h + 1]])
         for j, i in enumerate(nonempty):
-            if is_csv:
-                lines = [r.decode("utf-8", "replace").rstrip("\r") for r in recs[j]]
-                out[i] = [dict(zip(self.columns, row)) for row in csv.reader(lines)]   # pyx:258-260
-            else:
-                out[i] = [r.decode("utf-8", "replace") for r in recs[j]]
+            out[i] = self._decode(recs[j], is_csv)
+        return out
+
+    def _decode(self, recs, is_csv):
+        if is_csv:
+            lines = [r.decode("utf-8", "replace").rstrip("\r") for r in recs]
+            return [dict(zip(self.columns, row)) for row in csv.reader(lines)]   # pyx:258-260
+        return [r.decode("utf-8", "replace") for r in recs]
+
+    def _query_replicas(self, sub, nonempty, out, k, is_csv, file_sem):
+        """devices=[...]: every GPU holds a replica of the index; the batch is split over them (no
+        collective: SURVEY 8(e) "replicas / batch split")."""
+        import threading
+        reps = [self._parts[0]] + self._replicas
+        cut = [len(sub) * g // len(reps) for g in range(len(reps) + 1)]
+        res, errs = [None] * len(reps), []
+
+        def _one(g):
+            try:
+                res[g] = reps[g].query_records(sub[cut[g]:cut[g + 1]], k, file_sem, self.dedupe,
+                                               is_csv and self.reference_records)
+            except Exception as ex:                               # noqa: BLE001
+                errs.append(ex)
+        th = [threading.Thread(target=_one, args=(g,)) for g in range(len(reps))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        if errs:
+            raise errs[0]
+        for g in range(len(reps)):
+            hoff, roff, buf, _ = res[g]
+            data, ro = buf.tobytes(), roff.tolist()
+            for t in range(cut[g + 1] - cut[g]):
+                recs = [data[ro[h]:ro[h + 1]] for h in range(int(hoff[t]), int(hoff[t + 1]))]
+                out[nonempty[cut[g] + t]] = self._decode(recs, is_csv)
         return out
 
     def _query_partitioned(self, sub, nonempty, out, k):
@@ -279,6 +352,7 @@ class SuffixArrayHost:
         for idx in self._parts:
             idx.close()
         self._parts = []
+        self._drop_replicas()
 
     def __del__(self):
         try:

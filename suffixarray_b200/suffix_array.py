@@ -32,6 +32,7 @@ class _Index(S.Index):
 class SuffixArray(SuffixArrayHost):
     _Index = _Index
     _build_csv_columns = staticmethod(S.Index.build_csv_columns)
+    _build_text_multi = staticmethod(lambda indexes, text, lowercase: S.build_text_multi(indexes, text, lowercase=lowercase))
 
     @property
     def _idx(self):

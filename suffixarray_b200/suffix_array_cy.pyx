@@ -51,6 +51,7 @@ cdef extern from "sa_cuda.h" nogil:
     int sa_query_records(sa_index* idx, sa_result* res, uint8_t* out, uint64_t cap_bytes, uint64_t* rec_off,
                          uint64_t cap_records, uint64_t* hit_off_out, uint32_t* hit_doc)
     int sa_attach_csv_file(sa_index* idx, const char* csv_path)
+    int sa_build_text_multi(sa_index** idxs, int ndev, const uint8_t* text, uint64_t n, uint32_t flags)
     int sa_save(sa_index* idx, const char* path)
     int sa_load(sa_index* idx, const char* path)
 
@@ -225,8 +226,28 @@ def _build_csv_columns(list handles, str path_s, list columns):
     _check(rc)
 
 
+def _build_text_multi(list handles, text, bint lowercase):
+    """ONE index over the GPUs of `handles` (sample sort, a thread per handle inside the library)."""
+    cdef sa_index* hs[16]
+    cdef int n = len(handles)
+    if n < 1 or n > 16:
+        raise ValueError("1..16 handles")
+    cdef int i
+    for i in range(n):
+        hs[i] = (<_Handle> handles[i]).h
+    text = np.ascontiguousarray(text, dtype=np.uint8)
+    cdef uintptr_t p = text.ctypes.data if text.size else 0
+    cdef uint64_t nbytes = text.size
+    cdef uint32_t flags = SA_FLAG_LOWERCASE if lowercase else 0
+    cdef int rc
+    with nogil:
+        rc = sa_build_text_multi(hs, n, <const uint8_t*> p, nbytes, flags)
+    _check(rc)
+
+
 class SuffixArray(SuffixArrayHost):
     """The reference's class surface (suffix_array.pyx:110-267); the logic is _host.SuffixArrayHost,
     shared with the ctypes class, bound here to the compiled handle type."""
     _Index = _Handle
     _build_csv_columns = staticmethod(_build_csv_columns)
+    _build_text_multi = staticmethod(_build_text_multi)

@@ -116,3 +116,36 @@ def test_processes_over_shared_memory_and_ipc(world, tmp_path):
         line = [ln for ln in o.splitlines() if ln.startswith("RESULT")][-1]
         outs.append(json.loads(line[len("RESULT"):]))
     assert all(o["ok"] for o in outs), outs
+
+
+@pytest.mark.parametrize("flavour", ["ctypes", "cython"])
+def test_class_devices_keyword(flavour, tmp_path):
+    """SuffixArray(documents=..., devices=[0, 1, ...]): one index over the GPUs of this process, no
+    torch.distributed in the caller; query batches are split over the replicas."""
+    import torch
+    ndev = torch.cuda.device_count()
+    if ndev < 2:
+        pytest.skip("needs 2 GPUs in one process")
+    if flavour == "cython":
+        from suffixarray_b200.suffix_array_cy import SuffixArray
+    else:
+        from suffixarray_b200 import SuffixArray
+    names = W.company_names(60_000, seed=77, upper=True)
+    docs = [b.decode() for b in names]
+    devs = list(range(min(ndev, 4)))
+    multi = SuffixArray(documents=docs, max_suffix_length=32, devices=devs)
+    single = SuffixArray(documents=docs, max_suffix_length=32, device=0)
+    assert np.array_equal(multi.suffix_array, single.suffix_array)
+    qs = ["inc", "group", docs[5].lower(), docs[17][:4].lower(), "qqqq", "", "llc", "a", "holdings", "co", "corp", "sa"]
+    assert multi.query_records_batch(qs, k=25) == single.query_records_batch(qs, k=25)
+    assert multi.query_records("inc", k=5) == single.query_records("inc", k=5)
+    data = W.csv_file_bytes(3000, seed=3, quoted_fraction=0.1)
+    p = str(tmp_path / "d.csv")
+    with open(p, "wb") as f:
+        f.write(data)
+    a = SuffixArray(csv_file=p, search_column="name", max_suffix_length=32, devices=devs[:2])
+    b = SuffixArray(csv_file=p, search_column="name", max_suffix_length=32)
+    qs2 = ["inc", "llc", "corp", "a", "group", "zz"]
+    assert a.query_records_batch(qs2, k=10) == b.query_records_batch(qs2, k=10)
+    for x in (multi, single, a, b):
+        x.close()
