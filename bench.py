@@ -53,6 +53,9 @@ WORKLOADS = {
     "c2": (100_000_000, 1_000_000, "100M-char synthetic English document list, max_suffix_length=32, 1M-query batch"),
     "c1": (0, 10_000, "1M synthetic company-name strings, max_suffix_length=32, 10k whole-name queries"),
     "small": (4_000_000, 50_000, "4M-char synthetic English (debug size)"),
+    # the two below run through scripts/sweeps.py (their own step structure), 1 GPU
+    "c3": (0, 1_000_000, "CSV indexer: 1 GB synthetic search_column via mmap, max_suffix_length=32, end-to-end build + query"),
+    "c5": (100_000_000, 1_000_000, "max_suffix_length sweep 8/16/32/64 and query-length sweep 3-64 bytes"),
 }
 
 
@@ -1051,12 +1054,48 @@ def run_reference(args):
             "gpu_launches": 0}
 
 
+def run_sweep_workload(args):
+    """--workload c3 | c5: BASELINE configs 3 and 5 on one GPU through scripts/sweeps.py, every GPU number
+    with the reference's CPU number beside it (engine.c on all host cores; the CSV path end to end through
+    construct_..._mmap_full and get_matching_records_file).  One JSON line in the bench's shape."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("sweeps", os.path.join(ROOT, "scripts", "sweeps.py"))
+    sw = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sw)
+
+    class A:
+        chars = OVERRIDE.get("chars") or 100_000_000
+        queries = OVERRIDE.get("queries") or 1_000_000
+        csv_mb = int(os.environ.get("SA_BENCH_CSV_MB", "1024"))
+        no_cpu = args.no_cpu_baseline
+    out = {}
+    if args.workload == "c3":
+        sw.section_c3(A, out)
+        c = out["c3"]
+        line = {"metric": METRIC, "value": c["mchars_per_s_e2e"], "unit": "Mchars/s (CSV file -> queryable index, end to end)",
+                "n_gpus": 1, "higher_is_better": True, "data": "synthetic", "dtype": "u8 / u64 keys / u32 positions",
+                "config": {"workload": WORKLOADS["c3"][2], "name": "c3"},
+                "cpu_baseline": dict(c.get("cpu_engine_c", {}), kind="reference", value=c.get("cpu_engine_c", {}).get("mchars_per_s_e2e")),
+                "sweep": out}
+    else:
+        sw.section_c5(A, out)
+        r32 = [r for r in out["c5_L_sweep"]["rows"] if r["max_suffix_length"] == 32][0]
+        line = {"metric": METRIC, "value": r32["mchars_per_s"], "unit": "Mchars/s (SA build, L = 32 row of the sweep)", "n_gpus": 1,
+                "higher_is_better": True, "data": "synthetic", "dtype": "u8 / u64 keys / u32 positions",
+                "config": {"workload": WORKLOADS["c5"][2], "name": "c5"},
+                "cpu_baseline": dict(r32["cpu_engine_c"], kind="reference", value=r32["cpu_engine_c"]["mchars_per_s"]),
+                "sweep": out}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse_args()
     if args.chars_per_gpu:
         OVERRIDE["chars"] = args.chars_per_gpu
     if args.queries_per_gpu:
         OVERRIDE["queries"] = args.queries_per_gpu
+    if args.workload in ("c3", "c5"):
+        return run_sweep_workload(args)
     res = run_reference(args) if args.impl == "reference" else run_ours(args)
     if res is not None:
         if OVERRIDE and "config" in res:

@@ -94,6 +94,15 @@ int sa_build_text_device(sa_index* idx, const uint8_t* d_text, uint64_t n, uint3
  * Single partition (file < 2 GiB), as the reference handles one partition per 2 GiB. */
 int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags);
 
+/* Files of 2 GiB and more (also accepts smaller ones): the reference cuts the FILE every 2^31 bytes into
+ * partitions with one suffix array each, every partition resuming where the previous one stopped
+ * (engine.c:1437-1438, :1469-1481).  One call = one partition into one handle: partition_start = 0, then
+ * the *partition_end of the previous call, until *partition_end == *file_bytes.  The array holds absolute
+ * u32 file offsets (engine.c:560), so the file must stay below 4 GiB.  Host column scan (the reference's
+ * state machine; a partition need not start at a record boundary). */
+int sa_build_csv_partition(sa_index* idx, const char* csv_path, const char* column, uint64_t partition_start,
+                           uint32_t flags, uint64_t* partition_end, uint64_t* file_bytes);
+
 /* Several columns of one file, one index per column (idxs[c] indexes columns[c]; distinct handles on
  * one device).  The reference's entry already takes `char** search_cols, uint32_t num_search_cols`
  * (engine.h:209-215) but indexes search_cols[0] only (engine.c:1476; suffix_array.pyx:197 "TODO:

@@ -113,6 +113,8 @@ def ref_lib():
         lib.ref_csv_build.restype = C.c_uint32
         lib.ref_libsais.argtypes = [_u8p, _i32p, C.c_int32, C.c_int]
         lib.ref_libsais.restype = C.c_int
+        lib.ref_libsais64.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int]
+        lib.ref_libsais64.restype = C.c_int64
         lib.ref_max_threads.argtypes = []
         lib.ref_max_threads.restype = C.c_int
         lib.ref_set_threads.argtypes = [C.c_int]
@@ -121,6 +123,14 @@ def ref_lib():
         lib.ref_csv_open.restype = C.c_void_p
         lib.ref_csv_n.argtypes = [C.c_void_p]
         lib.ref_csv_n.restype = C.c_uint32
+        lib.ref_csv_partitions.argtypes = [C.c_void_p]
+        lib.ref_csv_partitions.restype = C.c_uint32
+        lib.ref_csv_part_n.argtypes = [C.c_void_p, C.c_uint32]
+        lib.ref_csv_part_n.restype = C.c_uint32
+        lib.ref_csv_part_bounds.argtypes = [C.c_void_p, C.c_uint32, _u64p, _u64p]
+        lib.ref_csv_part_bounds.restype = None
+        lib.ref_csv_part_copy.argtypes = [C.c_void_p, C.c_uint32, _u32p, _u8p]
+        lib.ref_csv_part_copy.restype = None
         lib.ref_csv_copy.argtypes = [C.c_void_p, _u32p, _u8p]
         lib.ref_csv_copy.restype = None
         lib.ref_csv_close.argtypes = [C.c_void_p]
@@ -326,6 +336,19 @@ class RefCsvIndex:
         ref_lib().ref_csv_copy(self.h, _p(sa, _u32p), _p(qd, _u8p))
         return sa[: self.n], qd[: self.n]
 
+    def partitions(self) -> int:
+        return int(ref_lib().ref_csv_partitions(self.h))
+
+    def partition(self, p: int):
+        """-> (start, end, sa u32, quoted u8) of partition p (files >= 2 GiB have several)."""
+        n = int(ref_lib().ref_csv_part_n(self.h, p))
+        a, b = np.zeros(1, np.uint64), np.zeros(1, np.uint64)
+        ref_lib().ref_csv_part_bounds(self.h, p, _p(a, _u64p), _p(b, _u64p))
+        sa = np.zeros(max(n, 1), dtype=np.uint32)
+        qd = np.zeros(max(n, 1), dtype=np.uint8)
+        ref_lib().ref_csv_part_copy(self.h, p, _p(sa, _u32p), _p(qd, _u8p))
+        return int(a[0]), int(b[0]), sa[:n], qd[:n]
+
     def query(self, queries, nthreads: int = 0):
         """get_substring_positions_file -> (start, end, skipped)."""
         nq = len(queries)
@@ -411,6 +434,16 @@ def ref_libsais(text, threads: int = 1) -> np.ndarray:
     rc = ref_lib().ref_libsais(_p(t, _u8p), _p(sa, _i32p), t.size, threads)
     if rc != 0:
         raise RuntimeError(f"libsais failed: {rc}")
+    return sa[: t.size]
+
+
+def ref_libsais64(text, threads: int = 0) -> np.ndarray:
+    """libsais64[_omp] of the reference tree: int64 FULL suffix array (timing baseline B at n >= 2^31)."""
+    t = _as_u8(text)
+    sa = np.empty(max(t.size, 1), dtype=np.int64)
+    rc = ref_lib().ref_libsais64(t.ctypes.data, sa.ctypes.data, t.size, threads)
+    if rc != 0:
+        raise RuntimeError(f"libsais64 failed: {rc}")
     return sa[: t.size]
 
 

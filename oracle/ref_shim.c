@@ -17,6 +17,7 @@
 #include <ctype.h>
 #include "engine.h"
 #include "libsais.h"
+#include "libsais64.h"
 
 static int g_saved_fd = -1;
 static void hush(void)
@@ -166,6 +167,22 @@ void* ref_csv_open(const char* path, const char* column, uint32_t max_suffix_len
 
 uint32_t ref_csv_n(void* h) { return ((SuffixArrayIndex*)h)->suffix_arrays[0].n; }
 
+/* files >= 2 GiB: one SuffixArray_struct per 2 GiB partition of the FILE (engine.c:1437-1438, :1469-1481) */
+uint32_t ref_csv_partitions(void* h) { return ((SuffixArrayIndex*)h)->num_partitions; }
+uint32_t ref_csv_part_n(void* h, uint32_t p) { return ((SuffixArrayIndex*)h)->suffix_arrays[p].n; }
+void ref_csv_part_bounds(void* h, uint32_t p, uint64_t* start, uint64_t* end)
+{
+    *start = ((SuffixArrayIndex*)h)->suffix_arrays[p].global_byte_start_idx;
+    *end = ((SuffixArrayIndex*)h)->suffix_arrays[p].global_byte_end_idx;
+}
+void ref_csv_part_copy(void* h, uint32_t p, uint32_t* sa_out, uint8_t* quoted_out)
+{
+    SuffixArray_struct* s = &((SuffixArrayIndex*)h)->suffix_arrays[p];
+    memcpy(sa_out, s->suffix_array, (size_t)s->n * sizeof(uint32_t));
+    if (quoted_out)
+        for (uint32_t i = 0; i < s->n; ++i) quoted_out[i] = get_buffer_bit(s->is_quoted_bitflag, i);
+}
+
 void ref_csv_copy(void* h, uint32_t* sa_out, uint8_t* quoted_out)
 {
     SuffixArray_struct* s = &((SuffixArrayIndex*)h)->suffix_arrays[0];
@@ -259,6 +276,17 @@ int ref_libsais(const uint8_t* text, int32_t* sa, int32_t n, int threads)
 #endif
     (void)threads;
     return libsais(text, sa, n, 0, NULL);
+}
+
+/* libsais64 (vendored, /root/reference/suffix_array/libsais64.h:61,:86): the int64 arm BASELINE.json names
+ * for the 4 G-char config; never called by the reference's live path.  Timing baseline only. */
+int64_t ref_libsais64(const uint8_t* text, int64_t* sa, int64_t n, int threads)
+{
+#ifdef LIBSAIS_OPENMP
+    if (threads != 1) return libsais64_omp(text, sa, n, 0, NULL, threads < 0 ? 0 : threads);
+#endif
+    (void)threads;
+    return libsais64(text, sa, n, 0, NULL);
 }
 
 int ref_max_threads(void) { return omp_get_max_threads(); }

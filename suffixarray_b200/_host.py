@@ -138,8 +138,27 @@ class SuffixArrayHost:
         cols = [search_column] if isinstance(search_column, str) else list(search_column)
         if not cols or len(set(cols)) != len(cols):
             raise ValueError("search_column must name one or more distinct columns")
-        self._resize(len(cols))
         self._drop_replicas()
+        if os.path.getsize(filename) >= self.PARTITION_BYTES:
+            # engine.c:1437-1438, :1469-1481: the FILE is cut every 2 GiB, one suffix array per partition, each
+            # partition resuming where the previous one stopped; queries walk them in order (pyx:221-247)
+            if len(cols) != 1:
+                raise ValueError("files of 2 GiB and more are indexed one search column at a time")
+            self._resize(1)
+            start, size, p = 0, None, 0
+            while size is None or start < size:
+                if p >= len(self._parts):
+                    self._parts.append(self._Index(self.max_suffix_length, self._device))
+                start, size = self._parts[p].build_csv_partition(filename, cols[0], start)
+                p += 1
+            self._resize(p)
+            self.search_columns = cols
+            self._csv_path = filename
+            self._mode = "csv"
+            self._csv_partitions = p
+            return
+        self._csv_partitions = 1
+        self._resize(len(cols))
         if len(cols) == 1:
             self._parts[0].build_csv(filename, cols[0])
             if self._devices and len(self._devices) > 1:          # replicas: the same build on every other GPU
@@ -172,7 +191,7 @@ class SuffixArrayHost:
         return self.query_records_batch([substring], k, column=column)[0]
 
     def _walk(self, column):
-        if self._mode == "csv" and column is not None:
+        if self._mode == "csv" and column is not None and getattr(self, "_csv_partitions", 1) == 1:
             if column not in self.search_columns:
                 raise ValueError(f"column {column!r} is not indexed (indexed: {self.search_columns})")
             return [self._parts[self.search_columns.index(column)]]

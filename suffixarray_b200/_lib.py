@@ -29,7 +29,7 @@ UINT32_MAX = 0xFFFFFFFF
 # every symbol include/sa_cuda.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "sa_last_error", "sa_abi_version", "sa_create", "sa_destroy", "sa_build_text", "sa_build_text_tail", "sa_build_text_device",
-    "sa_build_csv", "sa_build_csv_columns", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
+    "sa_build_csv", "sa_build_csv_partition", "sa_build_csv_columns", "sa_size", "sa_copy_sa_u32", "sa_copy_sa_i64", "sa_copy_text_positions_u32",
     "sa_copy_quoted_bits", "sa_copy_text", "sa_device_sa", "sa_get_stats", "sa_query_ranges", "sa_query_hits",
     "sa_query_ranges_device", "sa_num_docs", "sa_copy_doc_starts", "sa_debug_copy_lcp", "sa_debug_set",
     "sa_shard_begin", "sa_shard_begin_csv", "sa_shard_text_size", "sa_shard_copy_text", "sa_shard_pack", "sa_shard_split", "sa_shard_sort", "sa_shard_edges", "sa_shard_finish",
@@ -117,6 +117,8 @@ def lib():
     L.sa_build_text_device.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
     L.sa_build_text_tail.argtypes = [_vp, _vp, C.c_uint64, C.c_uint64, C.c_uint32]
     L.sa_build_csv.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint32]
+    L.sa_build_csv_partition.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64),
+                                         C.POINTER(C.c_uint64)]
     L.sa_build_csv_columns.argtypes = [C.POINTER(_vp), C.POINTER(C.c_char_p), C.c_uint32, C.c_char_p, C.c_uint32]
     L.sa_size.argtypes = [_vp]
     L.sa_size.restype = C.c_uint64
@@ -225,6 +227,13 @@ class Index:
 
     def build_csv(self, path: str, column: str, timing: bool = False):
         check(lib().sa_build_csv(self._h, path.encode(), column.encode(), SA_FLAG_TIMING if timing else 0))
+
+    def build_csv_partition(self, path: str, column: str, partition_start: int = 0, timing: bool = False):
+        """One 2 GiB partition of a (big) file, engine.c:1469-1481 -> (partition_end, file_bytes)."""
+        end, size = C.c_uint64(0), C.c_uint64(0)
+        check(lib().sa_build_csv_partition(self._h, path.encode(), column.encode(), partition_start,
+                                           SA_FLAG_TIMING if timing else 0, C.byref(end), C.byref(size)))
+        return int(end.value), int(size.value)
 
     @staticmethod
     def build_csv_columns(indexes, path: str, columns, timing: bool = False):

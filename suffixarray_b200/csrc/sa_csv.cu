@@ -80,15 +80,22 @@ struct FileView {
 // the reference does: its scan starts at byte 0, engine.c:513).  Same outputs as the reference's
 // three append_* streams: lower-cased text with a '\n' per row, file offset per text byte
 // (u32, as buffer_u32 truncates), quoted flag per text byte.
+// Partitions (engine.c:1469-1481): the scan starts at `start` as if a record began there (col = 0, outside
+// quotes) and runs while pos < end_point; a cell that straddles end_point is copied to its end (the
+// inner loops of engine.c:553-598 do not look at end_point).  *stop = where the scan stopped =
+// global_byte_end_idx (engine.c:611), the start of the next partition.
 uint64_t scan_column(FileView v, uint32_t column_idx, uint32_t num_columns, uint8_t* text, uint32_t* map,
-                     uint8_t* quoted)
+                     uint8_t* quoted, size_t start = 0, size_t end_point = (size_t)-1, size_t* stop = nullptr,
+                     uint64_t cap = ~0ull)
 {
-    const size_t end = v.size;
-    size_t pos = 0;
+    const size_t end = end_point < v.size ? end_point : v.size;
+    size_t pos = start;
     uint64_t out = 0;
     uint32_t col = 0;
+    struct StopAt { size_t* p; size_t& pos; ~StopAt() { if (p) *p = pos; } } stop_at{stop, pos};
     auto emit = [&](uint8_t c, size_t where, uint8_t q) {
-        text[out] = c; map[out] = (uint32_t)where; quoted[out] = q; ++out;
+        if (out < cap) { text[out] = c; map[out] = (uint32_t)where; quoted[out] = q; }
+        ++out;
     };
     while (pos < end) {
         // skip cells in front of the wanted column (quote aware), engine.c:523-551
@@ -117,7 +124,7 @@ uint64_t scan_column(FileView v, uint32_t column_idx, uint32_t num_columns, uint
                 if (c == '"' && (c1 == '\n' || c1 == ',' || c1 == 0)) { ++pos; break; }
                 emit(lower_ascii(c), pos, 1);
                 ++pos;
-                if (pos >= end) break;                // unterminated quote (the reference runs off the mapping)
+                if (pos >= v.size) break;             // unterminated quote (the reference runs off the mapping)
             }
         } else {                                      // engine.c:588-598
             for (;;) {
@@ -293,7 +300,7 @@ static int scan_column_host(sa_index* idx, const Mapped& m, uint32_t col, uint32
     return SA_OK;
 }
 
-static int open_csv(const char* csv_path, Mapped& m, std::vector<std::string>& cells)
+static int open_csv(const char* csv_path, Mapped& m, std::vector<std::string>& cells, bool allow_big = false)
 {
     m.fd = open(csv_path, O_RDONLY);
     if (m.fd < 0) { sa_set_error("cannot open %s", csv_path); return SA_ERR_IO; }
@@ -301,8 +308,13 @@ static int open_csv(const char* csv_path, Mapped& m, std::vector<std::string>& c
     if (fstat(m.fd, &sb) != 0) { sa_set_error("fstat failed on %s", csv_path); return SA_ERR_IO; }
     m.size = (size_t)sb.st_size;
     if (m.size == 0) { sa_set_error("%s is empty", csv_path); return SA_ERR_IO; }
-    if (m.size >= (1ull << 31)) {
-        sa_set_error("%s: files >= 2 GiB span several reference partitions (engine.c:1437); not supported yet", csv_path);
+    if (m.size >= (1ull << 31) && !allow_big) {
+        sa_set_error("%s: files >= 2 GiB span several reference partitions (engine.c:1437): build them one by one with "
+                     "sa_build_csv_partition", csv_path);
+        return SA_ERR_LIMIT;
+    }
+    if (m.size >= (1ull << 32) - 4096) {
+        sa_set_error("%s: file offsets do not fit the uint32 suffix array (the reference truncates them, engine.c:560)", csv_path);
         return SA_ERR_LIMIT;
     }
     void* mp = mmap(nullptr, m.size, PROT_READ, MAP_PRIVATE, m.fd, 0);
@@ -484,6 +496,83 @@ extern "C" int sa_shard_begin_csv(sa_index* idx, const char* csv_path, const cha
     idx->shard_csv = true;
     idx->shard_csv_regular = regular;
     idx->shard_prepared = true;
+    return SA_OK;
+}
+
+// ------------------------------------------------------------------------------ partitions of a big file
+// Files of 2 GiB and more: the reference cuts the FILE every 2^31 bytes and builds one suffix array per
+// partition, each partition resuming where the previous one stopped (engine.c:1437-1438, :1469-1481; the
+// scan of a partition starts with col_idx = 0 and outside quotes, wherever that is).  One call builds one
+// partition into one handle: partition_start = 0 for the first, then the *partition_end of the previous
+// call; *partition_end == file size (returned in *file_bytes) means it was the last.  The array holds
+// ABSOLUTE file offsets (u32, as engine.c:560 stores them), so hits and records resolve against the one
+// row table of the whole file, of which every partition's handle keeps a copy on the device.  The column
+// scan runs on the host (the byte state machine of engine.c:522-605 on the mmap'd file): the
+// tile-parallel device scanner assumes the scan starts at a record boundary, which a partition cut
+// does not guarantee.  Also accepts files below 2 GiB (one partition).
+extern "C" int sa_build_csv_partition(sa_index* idx, const char* csv_path, const char* column, uint64_t partition_start,
+                                      uint32_t flags, uint64_t* partition_end, uint64_t* file_bytes)
+{
+    if (!idx || !csv_path || !column || !partition_end) { sa_set_error("sa_build_csv_partition: NULL argument"); return SA_ERR_INVALID; }
+    std::unique_lock<std::shared_mutex> lock(idx->mu);
+    SA_CU(cudaSetDevice(idx->device));
+    Mapped m;
+    std::vector<std::string> cells;
+    int rc = open_csv(csv_path, m, cells, true);
+    if (rc != SA_OK) return rc;
+    if (file_bytes) *file_bytes = m.size;
+    if (partition_start >= m.size) { sa_set_error("sa_build_csv_partition: partition_start beyond the end of the file"); return SA_ERR_INVALID; }
+    uint32_t col = 0;
+    rc = find_column(cells, column, csv_path, &col);
+    if (rc != SA_OK) return rc;
+    idx->timing = (flags & SA_FLAG_TIMING) != 0;
+    idx->built = false;
+    sa_invalidate_results(idx);
+    idx->shard_prepared = false;
+    idx->shard_csv = false;
+    memset(&idx->stats, 0, sizeof idx->stats);
+    const uint64_t TWO_GB = 1ull << 31;
+    const uint64_t length = std::min<uint64_t>(TWO_GB, m.size - partition_start);     // engine.c:487
+    const size_t end_point = (size_t)(partition_start + length);                       // engine.c:513
+    // size of the column text of this partition: a first pass that only counts, then the real one
+    size_t stop = 0;
+    const uint64_t n = scan_column(FileView{m.p, m.size}, col, (uint32_t)cells.size(), nullptr, nullptr, nullptr,
+                                   (size_t)partition_start, end_point, &stop, 0);
+    if (n > SA_MAX_INDEX_BYTES) { sa_set_error("column text of %llu bytes exceeds the 2^31 limit", (unsigned long long)n); return SA_ERR_LIMIT; }
+    *partition_end = stop;
+    std::vector<uint8_t> h_text((size_t)n + 1), h_q((size_t)n + 1);
+    std::vector<uint32_t> h_map((size_t)n + 1);
+    scan_column(FileView{m.p, m.size}, col, (uint32_t)cells.size(), h_text.data(), h_map.data(), h_q.data(), (size_t)partition_start,
+                end_point, nullptr, n);
+    // the whole file on the device: row table (hits -> rows), file-semantics probes, records
+    rc = csv_load_device(idx, m.fd, m.size, false);
+    if (rc != SA_OK) return rc;
+    cudaStream_t s = idx->stream;
+    idx->n = n; idx->tail = 0;
+    const size_t bytes = ((size_t)n + SA_TEXT_PAD + 255) & ~(size_t)255;
+    SA_CU(idx->text.ensure(bytes));
+    SA_CU(idx->map.ensure((size_t)n * 4 + 4));
+    SA_CU(idx->quoted_text.ensure((size_t)n + 1));
+    SA_CU(cudaMemsetAsync(idx->text.as<uint8_t>() + ((size_t)n & ~(size_t)15), 0, bytes - ((size_t)n & ~(size_t)15), s));
+    if (n) {
+        SA_CU(cudaMemcpyAsync(idx->text.p, h_text.data(), n, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaMemcpyAsync(idx->map.p, h_map.data(), n * 4, cudaMemcpyHostToDevice, s));
+        SA_CU(cudaMemcpyAsync(idx->quoted_text.p, h_q.data(), n, cudaMemcpyHostToDevice, s));
+    }
+    SA_CU(cudaStreamSynchronize(s));
+    const float h2d = idx->stats.ms_h2d;
+    rc = sa_build_resident(idx, flags & ~SA_FLAG_LOWERCASE);
+    if (rc != SA_OK) return rc;
+    idx->stats.ms_h2d = h2d;
+    idx->built = false;
+    idx->stats.csv_host_scan = 1u;
+    rc = csv_remap(idx, false);
+    if (rc != SA_OK) return rc;
+    SA_CU(cudaStreamSynchronize(s));
+    sa_time_collect(idx);
+    idx->csv = true;
+    idx->csv_file_bytes = m.size;
+    idx->built = true;
     return SA_OK;
 }
 

@@ -37,6 +37,8 @@ cdef extern from "sa_cuda.h" nogil:
         pass
     int sa_build_text_tail(sa_index* idx, const uint8_t* text, uint64_t n, uint64_t tail, uint32_t flags)
     int sa_build_csv(sa_index* idx, const char* csv_path, const char* column, uint32_t flags)
+    int sa_build_csv_partition(sa_index* idx, const char* csv_path, const char* column, uint64_t partition_start,
+                               uint32_t flags, uint64_t* partition_end, uint64_t* file_bytes)
     int sa_build_csv_columns(sa_index** idxs, const char** columns, uint32_t ncols, const char* csv_path, uint32_t flags)
     uint64_t sa_size(const sa_index* idx)
     int sa_copy_sa_u32(sa_index* idx, uint32_t* out, uint64_t cap)
@@ -116,6 +118,19 @@ cdef class _Handle:
         with nogil:
             rc = sa_build_csv(self.h, c_path, c_col, 0)
         _check(rc)
+
+    def build_csv_partition(self, str path, str column, uint64_t partition_start=0):
+        """One 2 GiB partition of a big file (engine.c:1469-1481) -> (partition_end, file_bytes)."""
+        cdef bytes b_path = path.encode("utf-8")
+        cdef bytes b_col = column.encode("utf-8")
+        cdef const char* c_path = b_path
+        cdef const char* c_col = b_col
+        cdef uint64_t end = 0, size = 0
+        cdef int rc
+        with nogil:
+            rc = sa_build_csv_partition(self.h, c_path, c_col, partition_start, 0, &end, &size)
+        _check(rc)
+        return int(end), int(size)
 
     def attach_csv_file(self, str path):
         _check(sa_attach_csv_file(self.h, path.encode("utf-8")))
