@@ -66,7 +66,9 @@ cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint3
 cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa, uint32_t n, uint32_t max_suffix_length,
                             const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
                             uint32_t* end, int mode /* 0 auto, 1 thread per query, 2 eight lanes per query */,
-                            cudaStream_t s);
+                            cudaStream_t s, const void* qtop = nullptr, int qtop_levels = 0);
+// probe cache of the top `levels` levels of the bisection tree (16 bytes per node, 2^levels entries)
+cudaError_t sa_launch_qtop_build(const uint8_t* text, const uint32_t* sa, uint32_t n, int levels, void* qtop, cudaStream_t s);
 cudaError_t sa_launch_hit_counts(const uint32_t* start, const uint32_t* end, uint32_t nq, uint32_t k, uint32_t n,
                                  uint32_t* counts, cudaStream_t s);
 // exclusive scan of u32 counts into u64 offsets (off[num] = total)

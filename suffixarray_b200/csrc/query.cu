@@ -322,10 +322,19 @@ query_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, 
 // window), so throughput is set by how many chains are in flight; one query per lane keeps 32 per
 // warp in flight instead of 4.  The first 32 query bytes live in registers, text words are
 // fetched lazily (most probes differ in the first 8 bytes).  Same probe sequence as above.
+//
+// Probe cache ("qtop"): the probe sequence mid = (first + last) / 2 does not depend on the query, so the
+// nodes of the top T levels of the bisection tree are the same for every query.  qtop[node] (heap order:
+// root 1, "go left" 2i, "go right" 2i + 1) holds the first 16 text bytes of the suffix at that node's
+// mid: a probe there costs ONE 16-byte read of a 16 MB, L2-resident table instead of the two dependent
+// random reads SA[mid] -> text.  Only when the query and the suffix agree on all 16 bytes (and the query
+// is longer) does the probe go to SA + text for bytes 16... -- the comparison result, hence the path and
+// the ranges, are exactly those of strncmp(text + SA[mid], q, c).
 __device__ __forceinline__ int thread_compare(const uint8_t* __restrict__ text, uint32_t pos, const uint8_t* q,
-                                              uint32_t c, uint64_t q0, uint64_t q1, uint64_t q2, uint64_t q3)
+                                              uint32_t c, uint64_t q0, uint64_t q1, uint64_t q2, uint64_t q3,
+                                              uint32_t from = 0)
 {
-    for (uint32_t off = 0; off < c; off += 8) {
+    for (uint32_t off = from; off < c; off += 8) {
         const uint32_t nb = (c - off) < 8u ? (c - off) : 8u;
         const uint64_t tw = keep_top_bytes(load_be64(text, (uint64_t)pos + off), (int)nb);
         const uint32_t j = off >> 3;
@@ -336,10 +345,48 @@ __device__ __forceinline__ int thread_compare(const uint8_t* __restrict__ text, 
     return 0;
 }
 
+// one thread per node of the top `levels` levels: walk from the root along the bits of the node id
+__global__ void __launch_bounds__(256)
+qtop_build_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, uint32_t n, int levels,
+                  ulonglong2* __restrict__ qtop)
+{
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node == 0 || node >= (1u << levels)) return;
+    const int depth = 31 - __clz((int)node);
+    int64_t first = 0, last = (int64_t)n - 1;
+    for (int b = depth - 1; b >= 0 && first <= last; --b) {
+        const int64_t mid = (first + last) / 2;
+        if ((node >> b) & 1u) first = mid + 1; else last = mid - 1;
+    }
+    if (first > last) return;                       // no query ever reaches this node
+    const uint32_t p = sa[(first + last) / 2];
+    uint64_t w0, w1;
+    load_be128(text, p, w0, w1);
+    qtop[node] = make_ulonglong2(w0, w1);
+}
+
+// sign of strncmp(text + SA[mid], q, c) for a probe at `node` (< 2^levels): from the table, falling
+// back to SA + text past byte 16
+__device__ __forceinline__ int qtop_compare(const ulonglong2* __restrict__ qtop, uint32_t node, const uint8_t* __restrict__ text,
+                                            const uint32_t* __restrict__ sa, int64_t mid, const uint8_t* q, uint32_t c,
+                                            uint64_t q0, uint64_t q1, uint64_t q2, uint64_t q3)
+{
+    if (c == 0u) return 0;
+    const ulonglong2 k = __ldg(qtop + node);
+    const uint64_t t0 = keep_top_bytes(k.x, (int)(c < 8u ? c : 8u));
+    if (t0 != q0) return t0 < q0 ? -1 : 1;
+    if (c <= 8u) return 0;
+    const uint64_t t1 = keep_top_bytes(k.y, (int)(c - 8u < 8u ? c - 8u : 8u));
+    if (t1 != q1) return t1 < q1 ? -1 : 1;
+    if (c <= 16u) return 0;
+    return thread_compare(text, __ldg(sa + mid), q, c, q0, q1, q2, q3, 16u);
+}
+
 __global__ void __launch_bounds__(128)
 query_thread_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, uint32_t n, uint32_t L,
                     const uint8_t* __restrict__ qbytes, const uint64_t* __restrict__ qoff, uint32_t nq,
-                    uint32_t* __restrict__ start_out, uint32_t* __restrict__ end_out)
+                    uint32_t* __restrict__ start_out, uint32_t* __restrict__ end_out,
+                    const ulonglong2* __restrict__ qtop, int levels)
 {
     const uint32_t gq = blockIdx.x * blockDim.x + threadIdx.x;
     if (gq >= nq) return;
@@ -352,26 +399,36 @@ query_thread_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict
         if (q[i] == 0) { c = i; break; }
     const uint64_t q0 = load_query_word(q, 0, c), q1 = load_query_word(q, 8, c), q2 = load_query_word(q, 16, c),
                    q3 = load_query_word(q, 24, c);
+    const uint32_t top = qtop ? (1u << levels) : 0u;
 
     uint32_t start = 0xFFFFFFFFu, end = 0xFFFFFFFFu;
     int64_t f1 = 0, l1 = (int64_t)n - 1, f2 = 0, l2 = (int64_t)n - 1;
+    uint32_t n1 = 1, n2 = 1;                                        // nodes of the two searches (heap order)
     while (f1 <= l1 || f2 <= l2) {
         const bool a1 = f1 <= l1, a2 = f2 <= l2;
         const int64_t m1 = (f1 + l1) / 2, m2 = (f2 + l2) / 2;
         const bool same = a1 && a2 && m1 == m2;
-        // both SA entries first (independent loads), then the text windows
-        const uint32_t p1 = a1 ? __ldg(sa + m1) : 0u;
-        const uint32_t p2 = (a2 && !same) ? __ldg(sa + m2) : p1;
         int c1 = 0, c2 = 0;
-        if (a1) c1 = thread_compare(text, p1, q, c, q0, q1, q2, q3);
-        if (a2) c2 = same ? c1 : thread_compare(text, p2, q, c, q0, q1, q2, q3);
+        if (n1 < top || n2 < top) {
+            // top of the tree: one table read per probe
+            if (a1) c1 = n1 < top ? qtop_compare(qtop, n1, text, sa, m1, q, c, q0, q1, q2, q3)
+                                  : thread_compare(text, __ldg(sa + m1), q, c, q0, q1, q2, q3);
+            if (a2) c2 = same ? c1 : (n2 < top ? qtop_compare(qtop, n2, text, sa, m2, q, c, q0, q1, q2, q3)
+                                               : thread_compare(text, __ldg(sa + m2), q, c, q0, q1, q2, q3));
+        } else {
+            // both SA entries first (independent loads), then the text windows
+            const uint32_t p1 = a1 ? __ldg(sa + m1) : 0u;
+            const uint32_t p2 = (a2 && !same) ? __ldg(sa + m2) : p1;
+            if (a1) c1 = thread_compare(text, p1, q, c, q0, q1, q2, q3);
+            if (a2) c2 = same ? c1 : thread_compare(text, p2, q, c, q0, q1, q2, q3);
+        }
         if (a1) {
-            if (c1 < 0) f1 = m1 + 1;                                // engine.c:887-893
-            else { l1 = m1 - 1; start = (uint32_t)m1; }
+            if (c1 < 0) { f1 = m1 + 1; n1 = n1 < top ? 2 * n1 + 1 : top; }      // engine.c:887-893
+            else { l1 = m1 - 1; start = (uint32_t)m1; n1 = n1 < top ? 2 * n1 : top; }
         }
         if (a2) {
-            if (c2 > 0) l2 = m2 - 1;                                // engine.c:904-913
-            else { f2 = m2 + 1; end = (uint32_t)m2; }
+            if (c2 > 0) { l2 = m2 - 1; n2 = n2 < top ? 2 * n2 : top; }          // engine.c:904-913
+            else { f2 = m2 + 1; end = (uint32_t)m2; n2 = n2 < top ? 2 * n2 + 1 : top; }
         }
     }
     if (start == 0xFFFFFFFFu) end = 0xFFFFFFFFu;                    // engine.c:896-899
@@ -560,17 +617,25 @@ cudaError_t sa_launch_newline_write(const uint8_t* text, uint32_t n, const uint3
 
 cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa_, uint32_t n, uint32_t max_suffix_length,
                             const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start,
-                            uint32_t* end, int mode, cudaStream_t s)
+                            uint32_t* end, int mode, cudaStream_t s, const void* qtop, int qtop_levels)
 {
     if (!nq) return cudaSuccess;
     if (mode == 1 || (mode == 0 && nq >= 4096)) {        // enough queries to fill the GPU with one query per lane
         sa::query_thread_kernel<<<(nq + 127) / 128, 128, 0, s>>>(text, sa_, n, max_suffix_length, qbytes, qoff, nq, start,
-                                                                 end);
+                                                                 end, static_cast<const ulonglong2*>(qtop), qtop_levels);
     } else {                 // small batches: 8 lanes per query shorten each query's critical path
         const uint64_t threads = (uint64_t)nq * 8;
         sa::query_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(text, sa_, n, max_suffix_length, qbytes,
                                                                           qoff, nq, start, end);
     }
+    return cudaGetLastError();
+}
+
+// levels: top levels of the bisection tree to cache; qtop holds 2^levels entries of 16 bytes
+cudaError_t sa_launch_qtop_build(const uint8_t* text, const uint32_t* sa_, uint32_t n, int levels, void* qtop, cudaStream_t s)
+{
+    const uint32_t nodes = 1u << levels;
+    sa::qtop_build_kernel<<<(nodes + 255) / 256, 256, 0, s>>>(text, sa_, n, levels, static_cast<ulonglong2*>(qtop));
     return cudaGetLastError();
 }
 

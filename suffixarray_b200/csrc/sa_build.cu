@@ -87,7 +87,7 @@ extern "C" void sa_destroy(sa_index* idx)
     DevBuf* all[] = {&idx->text, &idx->sa_final, &idx->nlpos, &idx->sa_file, &idx->qbits, &idx->map,
                      &idx->quoted_text, &idx->keys[0], &idx->keys[1], &idx->vals[0], &idx->vals[1],
                      &idx->aux[0], &idx->aux[1], &idx->lcp, &idx->tie, &idx->amask, &idx->hmask, &idx->counts,
-                     &idx->status, &idx->small, &idx->nl_counts, &idx->codes, &idx->rowpos, &idx->pack_keys, &idx->pack_pos, &idx->hist16,
+                     &idx->status, &idx->small, &idx->nl_counts, &idx->codes, &idx->rowpos, &idx->qtop, &idx->pack_keys, &idx->pack_pos, &idx->hist16,
                      &idx->ext_sa, &idx->ext_lcp, &idx->ext_out, &idx->split_table, &idx->split_offsets,
                      &idx->csv_file, &idx->csv_tq, &idx->csv_td, &idx->csv_te, &idx->csv_tr, &idx->rowbits, &idx->rowrank,
                      &idx->nlbits, &idx->nlrank};

@@ -150,6 +150,12 @@ struct sa_index {
     sa_result* default_res = nullptr;   // the result object behind sa_query_ranges / sa_query_hits
     std::mutex res_mu;                  // creates default_res
     float ms_query_last = 0.f, ms_hits_last = 0.f;   // mirrored into sa_stats for the legacy calls
+    // probe cache of the batched bisection (query.cu "qtop"), built on the first big batch after a build
+    DevBuf qtop;
+    int qtop_levels = 0;
+    bool qtop_ready = false;
+    std::mutex qtop_mu;
+    int64_t dbg_qtop_levels = -1;   // -1: automatic (<= 20); 0: off
     // CSV: positions of the record ends of the file (built on first use from rowbits / rowrank)
     DevBuf rowpos;
     uint64_t num_row_ends = 0;
@@ -221,4 +227,4 @@ int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, u
                        uint32_t r_end, const sa::FinishOut& outs, uint32_t block0 = 0, uint32_t nblocks = 0xFFFFFFFFu);
 int sa_check_device_error(sa_index* idx);
 int sa_csv_finalize_shard(sa_index* idx);
-inline void sa_invalidate_results(sa_index* idx) { idx->generation += 1; idx->rowpos_ready = false; }   // sa_csv.cu: SA[i] = map[SA[i]] + quoted bits on the complete array of a sharded CSV build
+inline void sa_invalidate_results(sa_index* idx) { idx->generation += 1; idx->rowpos_ready = false; idx->qtop_ready = false; }   // sa_csv.cu: SA[i] = map[SA[i]] + quoted bits on the complete array of a sharded CSV build

@@ -62,6 +62,28 @@ static float elapsed(cudaEvent_t a, cudaEvent_t b)
     return cudaEventElapsedTime(&ms, a, b) == cudaSuccess ? ms : 0.f;
 }
 
+// ------------------------------------------------------------------------------ probe cache
+// The first thread-per-query batch after a build fills the table (about 1 M gathers); later batches and
+// other threads find it ready.  Small batches (8 lanes per query) do not use it.
+static int ensure_qtop(sa_index* idx, cudaStream_t s)
+{
+    std::lock_guard<std::mutex> g(idx->qtop_mu);
+    if (idx->qtop_ready) return SA_OK;
+    int levels = 0;
+    if (idx->dbg_qtop_levels != 0 && idx->n >= 2) {
+        while (levels < 20 && (2ull << levels) <= idx->n) ++levels;      // 2^levels <= n: every cached level is full-ish
+        if (idx->dbg_qtop_levels > 0 && idx->dbg_qtop_levels < levels) levels = (int)idx->dbg_qtop_levels;
+    }
+    idx->qtop_levels = levels;
+    if (levels > 0) {
+        SA_CU(idx->qtop.ensure(((size_t)1 << levels) * 16));
+        SA_CU(sa_launch_qtop_build(idx->text.as<uint8_t>(), idx->sa_final.as<uint32_t>(), (uint32_t)idx->n, levels, idx->qtop.p, s));
+        SA_CU(cudaStreamSynchronize(s));
+    }
+    idx->qtop_ready = true;
+    return SA_OK;
+}
+
 // ------------------------------------------------------------------------------ ranges
 static int ranges_locked(sa_index* idx, sa_result* r, const uint8_t* qbytes, const uint64_t* qoff, uint64_t nq, uint32_t k,
                          uint32_t flags, uint32_t* start, uint32_t* end, uint64_t* hit_off)
@@ -107,6 +129,11 @@ static int ranges_locked(sa_index* idx, sa_result* r, const uint8_t* qbytes, con
     SA_CU(r->blocksums.ensure(((size_t)(nq + 1023) / 1024 + 2) * 8));
     if (qlen) SA_CU(cudaMemcpyAsync(r->qbytes.p, qbytes, qlen, cudaMemcpyHostToDevice, s));
     SA_CU(cudaMemcpyAsync(r->qoff.p, qoff, (nq + 1) * 8, cudaMemcpyHostToDevice, s));
+    const bool thread_kernel = !file_mode && (idx->dbg_query_kernel == 1 || (idx->dbg_query_kernel == 0 && nq >= 4096));
+    if (thread_kernel) {
+        int rc = ensure_qtop(idx, s);
+        if (rc != SA_OK) return rc;
+    }
     SA_CU(cudaEventRecord(r->ev[0], s));
     if (file_mode)
         SA_CU(sa_launch_query_file(idx->csv_file.as<uint8_t>(), idx->csv_file_bytes, idx->sa_file.as<uint32_t>(),
@@ -115,7 +142,8 @@ static int ranges_locked(sa_index* idx, sa_result* r, const uint8_t* qbytes, con
     else
         SA_CU(sa_launch_query(idx->text.as<uint8_t>(), idx->sa_final.as<uint32_t>(), (uint32_t)idx->n, idx->L,
                               r->qbytes.as<uint8_t>(), r->qoff.as<uint64_t>(), (uint32_t)nq, r->qstart.as<uint32_t>(),
-                              r->qend.as<uint32_t>(), (int)idx->dbg_query_kernel, s));
+                              r->qend.as<uint32_t>(), (int)idx->dbg_query_kernel, s,
+                              thread_kernel && idx->qtop_levels ? idx->qtop.p : nullptr, idx->qtop_levels));
     SA_CU(cudaEventRecord(r->ev[1], s));
     SA_CU(cudaEventRecord(r->ev[2], s));
     SA_CU(sa_launch_hit_counts(r->qstart.as<uint32_t>(), r->qend.as<uint32_t>(), (uint32_t)nq, k, (uint32_t)idx->n,
@@ -437,9 +465,15 @@ extern "C" int sa_query_ranges_device(sa_index* idx, const uint8_t* d_qbytes, co
     SA_CU(cudaSetDevice(idx->device));
     r->have_ranges = r->have_hits = r->have_records = false;
     r->launches = 1;
+    const bool thread_kernel = idx->dbg_query_kernel == 1 || (idx->dbg_query_kernel == 0 && nq >= 4096);
+    if (thread_kernel) {
+        int rc = ensure_qtop(idx, r->stream);
+        if (rc != SA_OK) return rc;
+    }
     SA_CU(cudaEventRecord(r->ev[0], r->stream));
     SA_CU(sa_launch_query(idx->text.as<uint8_t>(), idx->sa_final.as<uint32_t>(), (uint32_t)idx->n, idx->L, d_qbytes, d_qoff,
-                          (uint32_t)nq, d_start, d_end, (int)idx->dbg_query_kernel, r->stream));
+                          (uint32_t)nq, d_start, d_end, (int)idx->dbg_query_kernel, r->stream,
+                          thread_kernel && idx->qtop_levels ? idx->qtop.p : nullptr, idx->qtop_levels));
     SA_CU(cudaEventRecord(r->ev[1], r->stream));
     SA_CU(cudaStreamSynchronize(r->stream));
     r->ms_query = elapsed(r->ev[0], r->ev[1]);

@@ -20,11 +20,13 @@ def check_queries(text, L, queries, k=1000, ref=False):
     want_sa = O.oracle_build(text, L)
     assert np.array_equal(sa, want_sa)
     ws, we = O.oracle_query(text, want_sa, L, queries)
-    for mode in (1, 2):              # one thread per query / eight lanes per query
+    # one thread per query (with the probe cache of the top levels off / shallow / automatic) and eight lanes per query
+    for mode, levels in ((1, 0), (1, 2), (1, 7), (1, -1), (2, -1)):
         idx.debug_set("query_kernel", mode)
+        idx.debug_set("qtop_levels", levels)
         s, e, off = idx.query_ranges(queries, k=k)
-        assert np.array_equal(s, ws), f"kernel {mode}: start differs at {np.flatnonzero(s != ws)[:5]}"
-        assert np.array_equal(e, we), f"kernel {mode}: end differs at {np.flatnonzero(e != we)[:5]}"
+        assert np.array_equal(s, ws), f"kernel {mode}/{levels}: start differs at {np.flatnonzero(s != ws)[:5]}"
+        assert np.array_equal(e, we), f"kernel {mode}/{levels}: end differs at {np.flatnonzero(e != we)[:5]}"
     woff, wpos, wdoc = O.oracle_hits(text, want_sa, ws, we, k)
     assert np.array_equal(off, woff)
     pos, doc = idx.query_hits(int(off[-1]))
