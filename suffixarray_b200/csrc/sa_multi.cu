@@ -604,7 +604,8 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
         std::vector<uint64_t> hist(65536, 0);
         for (int g = 0; g < R; ++g) {
             const uint32_t* h = reinterpret_cast<const uint32_t*>(all + (size_t)g * MAILBOX_BYTES);
-            for (int b = 0; b < 65536; ++b) hist[b] += h[b];
+            const uint64_t w = (bound(g + 1) - bound(g)) >= (16u << 20) ? 64 : 16;      // the rank's sample stride (sa_shard_pack)
+            for (int b = 0; b < 65536; ++b) hist[b] += w * h[b];
         }
         // bins in order; rank g gets the bins whose first record falls into the g-th equal share
         uint64_t total = 0, before = 0;

@@ -25,15 +25,22 @@ __global__ void iota_offset_kernel(uint32_t* __restrict__ out, uint32_t m, uint3
     if (i < m) out[i] = first + i;
 }
 
-// top-16-bit histogram of every HIST_STRIDE-th key (global reductions; the bins are far too many
-// for shared memory, and a 1-in-16 sample balances the shards to well under a percent)
-constexpr uint32_t HIST_STRIDE = 16;
-__global__ void hist16_kernel(const uint64_t* __restrict__ keys, uint32_t m, uint32_t* __restrict__ hist)
+// top-16-bit histogram of a sample of the keys (global reductions: the bins are far too many for shared
+// memory).  Every 16th key of small slices, every 64th of slices of 16 M records and more (1.5 M samples
+// of a 100 M-record slice still balance the shards to a fraction of a percent); lanes that hit the same
+// bin are merged into one atomic (text keys are skewed: a handful of bins take most of the samples).
+__global__ void hist16_kernel(const uint64_t* __restrict__ keys, uint32_t m, uint32_t stride_keys, uint32_t* __restrict__ hist)
 {
     const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t ms = (m + HIST_STRIDE - 1) / HIST_STRIDE;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ms; i += stride)
-        atomicAdd(hist + (uint32_t)(__ldg(keys + (size_t)i * HIST_STRIDE) >> 48), 1u);
+    const uint32_t ms = (m + stride_keys - 1) / stride_keys;
+    const uint32_t rounds = (ms + stride - 1) / stride;
+    for (uint32_t it = 0; it < rounds; ++it) {
+        const uint32_t i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        const bool ok = i < ms;
+        const uint32_t bin = ok ? (uint32_t)(__ldg(keys + (size_t)i * stride_keys) >> 48) : 0xFFFFFFFFu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+        if (ok && (threadIdx.x & 31) == (uint32_t)(__ffs((int)peers) - 1)) atomicAdd(hist + bin, (uint32_t)__popc(peers));
+    }
 }
 
 constexpr int SPLIT_THREADS = 256, SPLIT_IPT = 8, SPLIT_TILE = SPLIT_THREADS * SPLIT_IPT, SPLIT_MAXR = 16;
@@ -298,7 +305,7 @@ extern "C" int sa_shard_pack(sa_index* idx, uint64_t pos_begin, uint64_t pos_end
         ScopedPhase ph(idx, &idx->stats.ms_pack);
         SA_CU(sa_launch_pack0(sa_key_source(idx) + pos_begin, m, idx->cb0, idx->code, d_keys, s));
         sa::iota_offset_kernel<<<(m + 255) / 256, 256, 0, s>>>(d_pos, m, (uint32_t)pos_begin);
-        if (d_hist16) sa::hist16_kernel<<<idx->num_sms * 8, 256, 0, s>>>(d_keys, m, d_hist16);
+        if (d_hist16) sa::hist16_kernel<<<idx->num_sms * 8, 256, 0, s>>>(d_keys, m, m >= (16u << 20) ? 64u : 16u, d_hist16);
         SA_CU(cudaGetLastError());
         idx->stats.kernel_launches += d_hist16 ? 3 : 2;
     }
