@@ -50,14 +50,14 @@ def test_partition_entry_on_a_small_file(tmp_path):
         ix.close()
 
 
-@pytest.mark.skipif(os.environ.get("SA_TEST_BIG_CSV") != "1", reason="set SA_TEST_BIG_CSV=1 (2.3 GB file, ~4 min of CPU)")
+@pytest.mark.skipif(os.environ.get("SA_TEST_BIG_CSV") != "1", reason="set SA_TEST_BIG_CSV=1 (2.3 GB file, ~5 min of CPU)")
 def test_two_partitions_match_the_reference():
     if not O.have_ref():
         pytest.skip("oracle/_ref/libsa_ref.so not present")
     d = tempfile.mkdtemp(prefix="sa_big_")
     path = os.path.join(d, "big.csv")
     try:
-        rows, fbytes = W.write_csv_file(path, 1150, seed=7001, quoted_rows_per_chunk=5000)
+        rows, fbytes = W.write_csv_file(path, 1500, seed=7001, quoted_rows_per_chunk=5000)
         assert (1 << 31) < fbytes < (1 << 32) - 4096
         O.ref_use_all_cores()
         R = O.RefCsvIndex(path, "name", 32)
