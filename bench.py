@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- SA build Mchars/s + batched substring queries/s (BASELINE.json's metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c5|small]
 
 A "step" is one pass of the hot path over one batch of synthetic input: build the truncated
 suffix array of the workload text (max_suffix_length = 32) and answer the workload's query batch
@@ -12,21 +12,28 @@ English document list + a 1 M-query batch.
               the library's stream, max over ranks).  `queries_per_s` is the query half of the
               metric on the same footing (query batch resident in HBM).
 * `e2e`     : the same two numbers through the C-ABI calls a user of the drop-in makes
-              (sa_build_text / sa_query_ranges / sa_query_hits) with PINNED HOST buffers, the
-              host->device and device->host copies inside the timed region.
+              (sa_build_text / sa_query_ranges / sa_query_hits; sa_shard_build at N > 1) with PINNED
+              HOST buffers, the host->device and device->host copies inside the timed region.
 * `roofline`: the dominant kernel (onesweep radix scatter pass): algorithmic bytes per launch
               (24 B per record moved: read 8+4, write 8+4) / average launch time, against the
-              measured HBM copy peak in MEASURED_PEAKS.json.
+              measured HBM copy peak in MEASURED_PEAKS.json.  `roofline_query`: the query kernel
+              against SURVEY 8(d)'s B_query (useful and sector bytes).
 * `cpu_baseline`: the reference's own engine.c (oracle/_ref/libsa_ref.so, built from
-              /root/reference in the authoring container) timed on the host cores, rank 0, N = 1.
+              /root/reference in the authoring container) timed on ALL host cores (thread count set
+              explicitly: torchrun exports OMP_NUM_THREADS=1), rank 0, at every N.
+* `parity_checked`: the text the CPU arm indexed is built on the GPU too and the arrays, the ranges of
+              the whole batch and a sample of hit lists are compared entry by entry.
 
-N > 1 (torchrun, one process per GPU): the reference partitions a large text into independent
-sub-indexes (suffix_array.pyx:148-180); each rank builds and queries its own partition of the
-same size (weak scaling, no data-path collective).  Aggregation of the times is a
-torch.distributed all-reduce(MAX) over NCCL.
+N > 1 (torchrun, one process per GPU): ONE global index over the concatenation of the N per-rank
+texts (weak scaling), built by the library's native driver (sa_shard_build: every rank uploads only
+its slice; records, text and array slices move as peer stores over NVLink; small exchanges through a
+shared-memory communicator).  torch.distributed / NCCL carries the bench's own barriers and the
+max / sum of the timings.  `--driver python` is the round-1 Python loop, `--mode partition` the
+reference's own sharding (independent partitions).
 
-`--impl reference` times the reference CPU path on a bounded sample, rank 0 only.
-The oracle/ directory is used here ONLY for the cpu_baseline / reference arm.
+`--impl reference` times the reference CPU path on the per-GPU workload of the same config, rank 0 only.
+`--workload c3|c5` run BASELINE configs 3 and 5 through scripts/sweeps.py (CPU arm beside every number).
+The oracle/ directory is used here ONLY for the cpu_baseline / reference arm and the parity check.
 """
 from __future__ import annotations
 
