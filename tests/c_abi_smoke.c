@@ -44,6 +44,28 @@ int main(void)
         printf("hits differ\n");
         return 8;
     }
+    /* ABI 2: a per-call result object, de-duplicated hits, records cut in the library */
+    sa_result* res = NULL;
+    if (sa_result_create(idx, &res) != SA_OK) { printf("sa_result_create: %s\n", sa_last_error()); return 9; }
+    rc = sa_query_ranges_r(idx, res, q, qoff, 2, 1000, 0, start, end, hit_off);
+    uint64_t doff[3];
+    if (rc == SA_OK) rc = sa_query_hits_r(idx, res, SA_QUERY_DEDUPE, pos, doc, 5, doff);
+    /* "ana" -> records 1, 0 (the second hit in record 0 is dropped); "ban" -> records 0, 1 */
+    static const uint32_t want_ddoc[4] = {1, 0, 0, 1};
+    if (rc != SA_OK || doff[1] != 2 || doff[2] != 4 || memcmp(doc, want_ddoc, sizeof want_ddoc) != 0) {
+        printf("de-duplicated hits differ: %d %s\n", rc, sa_last_error());
+        return 10;
+    }
+    uint64_t nrec = 0, nbytes = 0, rec_off[6];
+    uint8_t recs[64];
+    rc = sa_query_records_size(idx, res, 0, &nrec, &nbytes);
+    if (rc == SA_OK && nrec == 5 && nbytes <= sizeof recs) rc = sa_query_records(idx, res, recs, sizeof recs, rec_off, 6, NULL, NULL);
+    /* records of the five hits: bandana, banana, banana, banana, bandana */
+    if (rc != SA_OK || nrec != 5 || nbytes != 7 + 6 + 6 + 6 + 7 || memcmp(recs, "bandanabananabananabananabandana", 32) != 0) {
+        printf("records differ: %d n=%llu bytes=%llu %s\n", rc, (unsigned long long)nrec, (unsigned long long)nbytes, sa_last_error());
+        return 11;
+    }
+    sa_result_destroy(res);
     sa_destroy(idx);
     printf("ok\n");
     return 0;
