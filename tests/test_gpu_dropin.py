@@ -162,3 +162,32 @@ def test_two_devices_in_one_process():
         idx.build_text(t)
         assert np.array_equal(idx.sa(), want), dev
         idx.close()
+
+
+def test_load_rejects_truncated_and_corrupt_containers(tmp_path):
+    """sa_load checks the file length against the header and that every stored position is in
+    range (a corrupt container must fail with an error, not become an out-of-bounds device read)."""
+    rng = np.random.default_rng(3)
+    t = (rng.integers(0, 6, size=50_000) + ord("a")).astype(np.uint8)
+    t[rng.random(t.size) < 0.03] = 10
+    idx = S.Index(32)
+    idx.build_text(t)
+    p = str(tmp_path / "x.sa")
+    idx.save(p)
+    want = idx.sa()
+    idx.close()
+    raw = bytearray(open(p, "rb").read())
+    ok = S.Index(32)
+    ok.load(p)
+    assert np.array_equal(ok.sa(), want)
+    ok.close()
+    with open(str(tmp_path / "short.sa"), "wb") as f:
+        f.write(raw[: len(raw) // 2])
+    with pytest.raises(S.SaCudaError):
+        S.Index(32).load(str(tmp_path / "short.sa"))
+    bad = bytearray(raw)
+    bad[-4:] = (0xFFFFFFF0).to_bytes(4, "little")          # the last array entry now points far outside the text
+    with open(str(tmp_path / "bad.sa"), "wb") as f:
+        f.write(bad)
+    with pytest.raises(S.SaCudaError):
+        S.Index(32).load(str(tmp_path / "bad.sa"))
