@@ -77,6 +77,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="global mode: fused split + peer stores through CUDA IPC (default) or split + NCCL all-to-all")
+    ap.add_argument("--sharded-sa", action="store_true",
+                    help="native driver: do not replicate the finished array (SA_FLAG_SHARDED_SA): every rank keeps its key "
+                         "range, queries read the other ranges from the peers over NVLink")
     ap.add_argument("--replicate", default="fused", choices=["fused", "allgather"],
                     help="N > 1: how every rank gets the complete array: the finish kernel stores into all ranks' arrays "
                          "(peer stores over NVLink), or NCCL all-gather of the slices + copy")
@@ -579,7 +582,7 @@ def run_ours_global_native(args, world, rank, local):
     for kv in (os.environ.get("SA_BENCH_DEBUG") or "").split(","):
         if "=" in kv:
             idx_dev.debug_set(kv.split("=")[0], int(kv.split("=")[1]))
-    base_flags = S.SA_FLAG_TIMING | (S.SA_FLAG_LOWERCASE if lower else 0)
+    base_flags = S.SA_FLAG_TIMING | (S.SA_FLAG_LOWERCASE if lower else 0) | (S.SA_FLAG_SHARDED_SA if args.sharded_sa else 0)
 
     def build(idx, ptr, flags):
         dist.barrier()
@@ -600,6 +603,8 @@ def run_ours_global_native(args, world, rank, local):
         r["build_e2e_ms"], r["phases_e2e"] = build(idx_e2e, h_part.data_ptr(), base_flags)
         r["build_launches"] += idx_e2e.stats()["kernel_launches"]
         torch.cuda.synchronize()
+        if args.sharded_sa:
+            dist.barrier()          # queries read the peers' shards: every rank's build must be complete
         t0 = time.perf_counter()
         S.check(lib.sa_query_ranges(idx_e2e._h, vp(h_q.data_ptr()), vp(h_qoff.data_ptr()), nq, K_HITS,
                                     vp(h_start.data_ptr()), vp(h_end.data_ptr()), vp(h_hoff.data_ptr())))
@@ -618,6 +623,8 @@ def run_ours_global_native(args, world, rank, local):
         r["query_dev_ms"] = st["ms_query"] + st["ms_hits"]
         r["query_launches"] = st["kernel_launches"]
         r["hits"] = total
+        if args.sharded_sa:
+            dist.barrier()          # nobody rebuilds while a peer still reads this build's shard
         return r
 
     for _ in range(args.warmup):
@@ -635,6 +642,8 @@ def run_ours_global_native(args, world, rank, local):
     clocks = sampler.stop() if rank == 0 else None
 
     verify = None
+    if args.verify_properties and args.sharded_sa:
+        raise SystemExit("--verify-properties needs the replicated array (drop --sharded-sa)")
     if args.verify_single or args.verify_properties:
         import hashlib
         d_text = torch.from_numpy(idx_dev.text()).to(dev)       # every replica holds the whole text
@@ -695,7 +704,9 @@ def run_ours_global_native(args, world, rank, local):
                         "stored straight into the owner's sort buffers (peer stores); 128-record halos + device-side junction "
                         "LCPs; each shard finished in chunks into the final array while finished chunks are pushed into every "
                         "peer's array",
-            "n_chars_total": n}
+            "n_chars_total": n,
+            "array": ("distributed (SA_FLAG_SHARDED_SA): every rank keeps its key range, queries read the others over NVLink"
+                      if args.sharded_sa else "replicated on every GPU")}
         result["timing"] = "wall clock between barrier + cudaDeviceSynchronize pairs, max over ranks (the build spans several kernels, peer stores and barriers per rank)"
         if verify is not None:
             result["verify"] = verify

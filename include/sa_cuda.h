@@ -38,7 +38,12 @@ typedef enum sa_status {
 #define SA_FLAG_LOWERCASE 1u   /* ASCII A-Z -> a-z on the device copy of the text: replaces
                                   lowercase_string, suffix_array.pyx:103-107 */
 #define SA_FLAG_TIMING    2u   /* record per-phase CUDA-event times into sa_stats */
-#define SA_FLAG_DEVICE_TEXT 4u /* sa_shard_begin: `text` is a device pointer (copied device to device) */
+#define SA_FLAG_DEVICE_TEXT 4u /* sa_shard_begin / sa_shard_build: `text` is a device pointer (copied device to device) */
+#define SA_FLAG_SHARDED_SA 8u  /* sa_shard_build / sa_build_text_multi: do NOT replicate the finished array: every rank keeps
+                                  its key range ("bucket-ranged SA shards") and queries read the other ranges from the
+                                  peers' memory over NVLink (CUDA IPC / peer access).  Saves (N-1)/N * 4n bytes of
+                                  NVLink traffic per GPU per build; the peers' indexes must stay alive while this one is
+                                  queried, and sa_save / sa_device_sa are not available on such an index. */
 
 /* Opaque index: owns the device text, the SA, the doc-offset table and all scratch.
  * Replaces SuffixArray_struct (engine.h:123-130) / SuffixArrayIndex (engine.h:163-172). */

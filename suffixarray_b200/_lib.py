@@ -21,6 +21,7 @@ SA_OK = 0
 SA_FLAG_LOWERCASE = 1
 SA_FLAG_TIMING = 2
 SA_FLAG_DEVICE_TEXT = 4
+SA_FLAG_SHARDED_SA = 8
 SA_QUERY_FILE_SEMANTICS = 1
 SA_QUERY_DEDUPE = 2
 SA_RECORDS_REFERENCE_COMPAT = 4
@@ -400,14 +401,14 @@ def shard_info(index: "Index"):
     return int(a.value), int(b.value)
 
 
-def build_text_multi(indexes, text, lowercase: bool = False, timing: bool = False):
+def build_text_multi(indexes, text, lowercase: bool = False, timing: bool = False, sharded_sa: bool = False):
     """ONE index over the GPUs of `indexes` (handles of one process, a thread per handle): every handle
     ends up with the text and the complete array."""
     t = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray, memoryview)) \
         else np.ascontiguousarray(text, dtype=np.uint8)
     n = len(indexes)
     hs = (_vp * n)(*[ix._h for ix in indexes])
-    flags = (SA_FLAG_LOWERCASE if lowercase else 0) | (SA_FLAG_TIMING if timing else 0)
+    flags = (SA_FLAG_LOWERCASE if lowercase else 0) | (SA_FLAG_TIMING if timing else 0) | (SA_FLAG_SHARDED_SA if sharded_sa else 0)
     check(lib().sa_build_text_multi(hs, n, _ptr(t) if t.size else None, t.size, flags))
 
 

@@ -185,6 +185,24 @@ struct FinishOut {
 };
 }  // namespace sa
 
+namespace sa {
+// The complete array as a set of key ranges that live on different GPUs (a sharded build without
+// replication): global rank r with bound[g] <= r < bound[g + 1] is base[g][r] -- base[g] is rank g's final
+// array (its own memory, or a peer's mapped through CUDA IPC and read over NVLink).
+struct SaView {
+    const uint32_t* base[16];
+    uint32_t bound[17];
+    int n;
+};
+__device__ __forceinline__ uint32_t sa_at(const SaView& v, uint64_t r)
+{
+    int g = 0;
+#pragma unroll
+    for (int t = 1; t < 16; ++t) g += (t < v.n && r >= (uint64_t)v.bound[t]) ? 1 : 0;
+    return __ldg(v.base[g] + r);
+}
+}  // namespace sa
+
 #define SA_DEVERR_LOOKBACK_TIMEOUT 1u
 #define SA_DEVERR_RUN_TOO_LONG 2u
 // csv_scan.cu: the file is outside the cases where the tile-parallel scan equals the reference's state machine

@@ -121,3 +121,12 @@ cudaError_t sa_launch_record_bounds(const uint32_t* hit_pos, const uint32_t* hit
 cudaError_t sa_launch_record_gather(const uint8_t* src, const unsigned long long* src_off, const uint64_t* rec_off,
                                     uint64_t num, uint8_t* out, cudaStream_t s);
 cudaError_t sa_launch_count_out_of_range(const uint32_t* a, uint64_t n, uint64_t limit, unsigned int* bad, cudaStream_t s);
+// ---- query.cu: the array as key ranges on several GPUs (sa::SaView, common.cuh)
+cudaError_t sa_launch_query_sharded(const uint8_t* text, const sa::SaView& view, uint32_t n, uint32_t max_suffix_length,
+                                    const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start, uint32_t* end,
+                                    cudaStream_t s, const void* qtop, int qtop_levels);
+cudaError_t sa_launch_qtop_build_sharded(const uint8_t* text, const sa::SaView& view, uint32_t n, int levels, void* qtop,
+                                         cudaStream_t s);
+cudaError_t sa_launch_hits_sharded(const sa::SaView& view, const uint32_t* start, const uint64_t* hit_off, uint32_t nq,
+                                   const unsigned long long* nlbits, const uint32_t* nlrank, uint32_t* hit_pos,
+                                   uint32_t* hit_doc, cudaStream_t s);

@@ -345,9 +345,20 @@ __device__ __forceinline__ int thread_compare(const uint8_t* __restrict__ text, 
     return 0;
 }
 
+// SA[r]: a plain array, or key ranges spread over several GPUs (SaView, common.cuh)
+struct SaPlain {
+    const uint32_t* sa;
+    __device__ __forceinline__ uint32_t operator()(uint64_t r) const { return __ldg(sa + r); }
+};
+struct SaSharded {
+    SaView v;
+    __device__ __forceinline__ uint32_t operator()(uint64_t r) const { return sa_at(v, r); }
+};
+
 // one thread per node of the top `levels` levels: walk from the root along the bits of the node id
+template <class SA>
 __global__ void __launch_bounds__(256)
-qtop_build_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, uint32_t n, int levels,
+qtop_build_kernel(const uint8_t* __restrict__ text, const SA sa, uint32_t n, int levels,
                   ulonglong2* __restrict__ qtop)
 {
     const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
@@ -359,7 +370,7 @@ qtop_build_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__
         if ((node >> b) & 1u) first = mid + 1; else last = mid - 1;
     }
     if (first > last) return;                       // no query ever reaches this node
-    const uint32_t p = sa[(first + last) / 2];
+    const uint32_t p = sa((uint64_t)((first + last) / 2));
     uint64_t w0, w1;
     load_be128(text, p, w0, w1);
     qtop[node] = make_ulonglong2(w0, w1);
@@ -367,8 +378,9 @@ qtop_build_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__
 
 // sign of strncmp(text + SA[mid], q, c) for a probe at `node` (< 2^levels): from the table, falling
 // back to SA + text past byte 16
+template <class SA>
 __device__ __forceinline__ int qtop_compare(const ulonglong2* __restrict__ qtop, uint32_t node, const uint8_t* __restrict__ text,
-                                            const uint32_t* __restrict__ sa, int64_t mid, const uint8_t* q, uint32_t c,
+                                            const SA& sa, int64_t mid, const uint8_t* q, uint32_t c,
                                             uint64_t q0, uint64_t q1, uint64_t q2, uint64_t q3)
 {
     if (c == 0u) return 0;
@@ -379,11 +391,12 @@ __device__ __forceinline__ int qtop_compare(const ulonglong2* __restrict__ qtop,
     const uint64_t t1 = keep_top_bytes(k.y, (int)(c - 8u < 8u ? c - 8u : 8u));
     if (t1 != q1) return t1 < q1 ? -1 : 1;
     if (c <= 16u) return 0;
-    return thread_compare(text, __ldg(sa + mid), q, c, q0, q1, q2, q3, 16u);
+    return thread_compare(text, sa((uint64_t)mid), q, c, q0, q1, q2, q3, 16u);
 }
 
+template <class SA>
 __global__ void __launch_bounds__(128)
-query_thread_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict__ sa, uint32_t n, uint32_t L,
+query_thread_kernel(const uint8_t* __restrict__ text, const SA sa, uint32_t n, uint32_t L,
                     const uint8_t* __restrict__ qbytes, const uint64_t* __restrict__ qoff, uint32_t nq,
                     uint32_t* __restrict__ start_out, uint32_t* __restrict__ end_out,
                     const ulonglong2* __restrict__ qtop, int levels)
@@ -412,13 +425,13 @@ query_thread_kernel(const uint8_t* __restrict__ text, const uint32_t* __restrict
         if (n1 < top || n2 < top) {
             // top of the tree: one table read per probe
             if (a1) c1 = n1 < top ? qtop_compare(qtop, n1, text, sa, m1, q, c, q0, q1, q2, q3)
-                                  : thread_compare(text, __ldg(sa + m1), q, c, q0, q1, q2, q3);
+                                  : thread_compare(text, sa((uint64_t)m1), q, c, q0, q1, q2, q3);
             if (a2) c2 = same ? c1 : (n2 < top ? qtop_compare(qtop, n2, text, sa, m2, q, c, q0, q1, q2, q3)
-                                               : thread_compare(text, __ldg(sa + m2), q, c, q0, q1, q2, q3));
+                                               : thread_compare(text, sa((uint64_t)m2), q, c, q0, q1, q2, q3));
         } else {
             // both SA entries first (independent loads), then the text windows
-            const uint32_t p1 = a1 ? __ldg(sa + m1) : 0u;
-            const uint32_t p2 = (a2 && !same) ? __ldg(sa + m2) : p1;
+            const uint32_t p1 = a1 ? sa((uint64_t)m1) : 0u;
+            const uint32_t p2 = (a2 && !same) ? sa((uint64_t)m2) : p1;
             if (a1) c1 = thread_compare(text, p1, q, c, q0, q1, q2, q3);
             if (a2) c2 = same ? c1 : thread_compare(text, p2, q, c, q0, q1, q2, q3);
         }
@@ -543,8 +556,9 @@ __global__ void hit_counts_kernel(const uint32_t* __restrict__ start, const uint
 }
 
 // one warp per query: rank -> text position -> record index (# of '\n' before the position)
+template <class SA>
 __global__ void __launch_bounds__(256)
-hits_kernel(const uint32_t* __restrict__ sa, const uint32_t* __restrict__ start,
+hits_kernel(const SA sa, const uint32_t* __restrict__ start,
             const uint64_t* __restrict__ hit_off, uint32_t nq, const unsigned long long* __restrict__ nlbits,
             const uint32_t* __restrict__ nlrank, uint32_t* __restrict__ hit_pos, uint32_t* __restrict__ hit_doc)
 {
@@ -554,7 +568,7 @@ hits_kernel(const uint32_t* __restrict__ sa, const uint32_t* __restrict__ start,
     const uint32_t take = (uint32_t)(hit_off[wq + 1] - o);
     const uint32_t s = start[wq];
     for (uint32_t j = threadIdx.x & 31; j < take; j += 32) {
-        const uint32_t p = sa[(uint64_t)s + j];      // s + j <= end < n by construction of the counts
+        const uint32_t p = sa((uint64_t)s + j);      // s + j <= end < n by construction of the counts
         if (hit_pos) hit_pos[o + j] = p;
         if (hit_doc) {
             // record index = number of '\n' in front of p
@@ -621,8 +635,8 @@ cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa_, uint32_t n
 {
     if (!nq) return cudaSuccess;
     if (mode == 1 || (mode == 0 && nq >= 4096)) {        // enough queries to fill the GPU with one query per lane
-        sa::query_thread_kernel<<<(nq + 127) / 128, 128, 0, s>>>(text, sa_, n, max_suffix_length, qbytes, qoff, nq, start,
-                                                                 end, static_cast<const ulonglong2*>(qtop), qtop_levels);
+        sa::query_thread_kernel<<<(nq + 127) / 128, 128, 0, s>>>(text, sa::SaPlain{sa_}, n, max_suffix_length, qbytes, qoff, nq,
+                                                                 start, end, static_cast<const ulonglong2*>(qtop), qtop_levels);
     } else {                 // small batches: 8 lanes per query shorten each query's critical path
         const uint64_t threads = (uint64_t)nq * 8;
         sa::query_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(text, sa_, n, max_suffix_length, qbytes,
@@ -635,7 +649,37 @@ cudaError_t sa_launch_query(const uint8_t* text, const uint32_t* sa_, uint32_t n
 cudaError_t sa_launch_qtop_build(const uint8_t* text, const uint32_t* sa_, uint32_t n, int levels, void* qtop, cudaStream_t s)
 {
     const uint32_t nodes = 1u << levels;
-    sa::qtop_build_kernel<<<(nodes + 255) / 256, 256, 0, s>>>(text, sa_, n, levels, static_cast<ulonglong2*>(qtop));
+    sa::qtop_build_kernel<<<(nodes + 255) / 256, 256, 0, s>>>(text, sa::SaPlain{sa_}, n, levels, static_cast<ulonglong2*>(qtop));
+    return cudaGetLastError();
+}
+
+// ---- the same three kernels over an array whose key ranges live on several GPUs (no replication)
+cudaError_t sa_launch_query_sharded(const uint8_t* text, const sa::SaView& view, uint32_t n, uint32_t max_suffix_length,
+                                    const uint8_t* qbytes, const uint64_t* qoff, uint32_t nq, uint32_t* start, uint32_t* end,
+                                    cudaStream_t s, const void* qtop, int qtop_levels)
+{
+    if (!nq) return cudaSuccess;
+    sa::query_thread_kernel<<<(nq + 127) / 128, 128, 0, s>>>(text, sa::SaSharded{view}, n, max_suffix_length, qbytes, qoff, nq,
+                                                             start, end, static_cast<const ulonglong2*>(qtop), qtop_levels);
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_qtop_build_sharded(const uint8_t* text, const sa::SaView& view, uint32_t n, int levels, void* qtop,
+                                         cudaStream_t s)
+{
+    const uint32_t nodes = 1u << levels;
+    sa::qtop_build_kernel<<<(nodes + 255) / 256, 256, 0, s>>>(text, sa::SaSharded{view}, n, levels, static_cast<ulonglong2*>(qtop));
+    return cudaGetLastError();
+}
+
+cudaError_t sa_launch_hits_sharded(const sa::SaView& view, const uint32_t* start, const uint64_t* hit_off, uint32_t nq,
+                                   const unsigned long long* nlbits, const uint32_t* nlrank, uint32_t* hit_pos,
+                                   uint32_t* hit_doc, cudaStream_t s)
+{
+    if (!nq) return cudaSuccess;
+    const uint64_t threads = (uint64_t)nq * 32;
+    sa::hits_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(sa::SaSharded{view}, start, hit_off, nq, nlbits, nlrank,
+                                                                     hit_pos, hit_doc);
     return cudaGetLastError();
 }
 
@@ -666,8 +710,8 @@ cudaError_t sa_launch_hits(const uint32_t* sa_, const uint32_t* start, const uin
 {
     if (!nq) return cudaSuccess;
     const uint64_t threads = (uint64_t)nq * 32;
-    sa::hits_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(sa_, start, hit_off, nq, nlbits, nlrank, hit_pos,
-                                                                     hit_doc);
+    sa::hits_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(sa::SaPlain{sa_}, start, hit_off, nq, nlbits, nlrank,
+                                                                     hit_pos, hit_doc);
     return cudaGetLastError();
 }
 

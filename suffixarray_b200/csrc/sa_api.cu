@@ -77,7 +77,7 @@ extern "C" uint64_t sa_size(const sa_index* idx) { return idx && idx->built ? id
 extern "C" uint64_t sa_num_docs(const sa_index* idx) { return idx && idx->built ? (uint64_t)idx->num_nl + 1 : 0; }
 extern "C" const uint32_t* sa_device_sa(const sa_index* idx)
 {
-    if (!idx || !idx->built) return nullptr;
+    if (!idx || !idx->built || idx->sharded_sa) return nullptr;     // a sharded array has no single device pointer
     return idx->csv ? idx->sa_file.as<uint32_t>() : idx->sa_final.as<uint32_t>();
 }
 
@@ -96,12 +96,22 @@ extern "C" int sa_copy_sa_u32(sa_index* idx, uint32_t* out, uint64_t cap)
     SA_REQUIRE(out || idx->n == 0, SA_ERR_INVALID, "out is NULL");
     SA_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "cap %llu < n %llu", (unsigned long long)cap, (unsigned long long)idx->n);
     std::unique_lock<std::shared_mutex> lock(idx->mu);
+    if (idx->sharded_sa) {                       // gather the key ranges from their owners (peer memory)
+        SA_CU(cudaSetDevice(idx->device));
+        for (int g = 0; g < idx->view.n; ++g) {
+            const uint64_t a = idx->view.bound[g], b = idx->view.bound[g + 1];
+            if (b > a) SA_CU(cudaMemcpyAsync(out + a, idx->view.base[g] + a, (size_t)(b - a) * 4, cudaMemcpyDefault, idx->stream));
+        }
+        SA_CU(cudaStreamSynchronize(idx->stream));
+        return SA_OK;
+    }
     return copy_out(idx, sa_device_sa(idx), out, (size_t)idx->n * 4);
 }
 
 extern "C" int sa_copy_text_positions_u32(sa_index* idx, uint32_t* out, uint64_t cap)
 {
     SA_REQUIRE(idx && idx->built, SA_ERR_INVALID, "index not built");
+    if (idx->sharded_sa) return sa_copy_sa_u32(idx, out, cap);
     SA_REQUIRE(cap >= idx->n, SA_ERR_INVALID, "cap too small");
     std::unique_lock<std::shared_mutex> lock(idx->mu);
     return copy_out(idx, idx->sa_final.p, out, (size_t)idx->n * 4);

@@ -125,6 +125,11 @@ struct sa_index {
     uint8_t* h_big = nullptr;                 // pinned, one mailbox (256 KiB + 8 KiB)
     cudaStream_t push_stream = nullptr;       // high priority: peer pushes that must not queue behind the sort kernels
     uint64_t shard_m_last = 0, shard_exchange_bytes = 0;
+    // SA_FLAG_SHARDED_SA: the array stays distributed; `view` routes a global rank to its owner's memory
+    bool shard_no_replicate = false;          // set for the duration of a build
+    bool sharded_sa = false;                  // the built index answers queries through `view`
+    sa::SaView view{};
+    uint32_t* shard_peer_base[16] = {};       // every rank's final array as this rank addresses it (finish_bcast)
 
     // sharded (multi-GPU) build state, see sa_shard.cu
     bool shard_prepared = false;
@@ -227,4 +232,4 @@ int sa_stage_finish_to(sa_index* idx, const uint32_t* sa, const uint16_t* lcp, u
                        uint32_t r_end, const sa::FinishOut& outs, uint32_t block0 = 0, uint32_t nblocks = 0xFFFFFFFFu);
 int sa_check_device_error(sa_index* idx);
 int sa_csv_finalize_shard(sa_index* idx);
-inline void sa_invalidate_results(sa_index* idx) { idx->generation += 1; idx->rowpos_ready = false; idx->qtop_ready = false; }   // sa_csv.cu: SA[i] = map[SA[i]] + quoted bits on the complete array of a sharded CSV build
+inline void sa_invalidate_results(sa_index* idx) { idx->generation += 1; idx->rowpos_ready = false; idx->qtop_ready = false; idx->sharded_sa = false; }   // sa_csv.cu: SA[i] = map[SA[i]] + quoted bits on the complete array of a sharded CSV build

@@ -68,6 +68,7 @@ extern "C" int sa_save(sa_index* idx, const char* path)
 {
     if (!idx || !path) { sa_set_error("sa_save: NULL argument"); return SA_ERR_INVALID; }
     if (!idx->built) { sa_set_error("sa_save: index not built"); return SA_ERR_INVALID; }
+    if (idx->sharded_sa) { sa_set_error("sa_save: the array of a SA_FLAG_SHARDED_SA index is spread over several GPUs"); return SA_ERR_INVALID; }
     std::unique_lock<std::shared_mutex> lock(idx->mu);
     SA_CU(cudaSetDevice(idx->device));
     File out;

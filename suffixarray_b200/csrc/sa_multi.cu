@@ -422,6 +422,8 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
     cudaStream_t s = idx->stream;
     Lap lap(idx, phase_ms);
     if (c->local) idx->dbg_same_process = 1;
+    idx->shard_no_replicate = (flags & SA_FLAG_SHARDED_SA) != 0 && R > 1;
+    idx->sharded_sa = false;
 
     // ---- state of a fresh sharded build (what sa_shard_begin sets)
     {
@@ -659,6 +661,7 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
     std::vector<uint16_t> left_lcp, right_lcp;
     uint32_t lcp_first = 0;
     uint64_t global_offset = 0;
+    uint64_t shard_ms[16] = {};
     {
         EdgeBlock eb{};
         eb.m = m_recv;
@@ -668,6 +671,7 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
         MG_TRY(comm_allgather(c, &eb, sizeof eb, &all));
         auto E = [&](int g) { return reinterpret_cast<const EdgeBlock*>(all + (size_t)g * MAILBOX_BYTES); };
         for (int g = 0; g < me; ++g) global_offset += E(g)->m;
+        for (int g = 0; g < R; ++g) shard_ms[g] = E(g)->m;
         if (m_recv) {
             // which records form the halos (index logic of sharded.py assemble_halos), and the pairs whose
             // LCP across a shard boundary has to be computed from the text
@@ -746,6 +750,21 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
     MG_TRY(sa_shard_finish_bcast(idx, left_pos.data(), left_lcp.data(), (uint32_t)left_pos.size(), lcp_first, right_pos.data(),
                                  right_lcp.data(), (uint32_t)right_pos.size(), R, me, final_handles, global_offset));
     MG_TRY(comm_barrier(c));
+    if (idx->shard_no_replicate) {
+        // the array stays distributed: rank g's key range lives in rank g's final array
+        sa::SaView v{};
+        v.n = R;
+        uint64_t at = 0;
+        for (int g = 0; g < R; ++g) {
+            v.base[g] = idx->shard_peer_base[g];
+            v.bound[g] = (uint32_t)at;
+            at += shard_ms[g];
+        }
+        for (int g = R; g <= 16; ++g) v.bound[g] = (uint32_t)n;
+        idx->view = v;
+        idx->sharded_sa = true;
+        idx->shard_no_replicate = false;
+    }
     MG_TRY(sa_shard_mark_built(idx));
     idx->shard_m_last = m_recv;
     idx->shard_exchange_bytes = 0;

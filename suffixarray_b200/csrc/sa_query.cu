@@ -77,7 +77,10 @@ static int ensure_qtop(sa_index* idx, cudaStream_t s)
     idx->qtop_levels = levels;
     if (levels > 0) {
         SA_CU(idx->qtop.ensure(((size_t)1 << levels) * 16));
-        SA_CU(sa_launch_qtop_build(idx->text.as<uint8_t>(), idx->sa_final.as<uint32_t>(), (uint32_t)idx->n, levels, idx->qtop.p, s));
+        if (idx->sharded_sa)
+            SA_CU(sa_launch_qtop_build_sharded(idx->text.as<uint8_t>(), idx->view, (uint32_t)idx->n, levels, idx->qtop.p, s));
+        else
+            SA_CU(sa_launch_qtop_build(idx->text.as<uint8_t>(), idx->sa_final.as<uint32_t>(), (uint32_t)idx->n, levels, idx->qtop.p, s));
         SA_CU(cudaStreamSynchronize(s));
     }
     idx->qtop_ready = true;
@@ -129,13 +132,18 @@ static int ranges_locked(sa_index* idx, sa_result* r, const uint8_t* qbytes, con
     SA_CU(r->blocksums.ensure(((size_t)(nq + 1023) / 1024 + 2) * 8));
     if (qlen) SA_CU(cudaMemcpyAsync(r->qbytes.p, qbytes, qlen, cudaMemcpyHostToDevice, s));
     SA_CU(cudaMemcpyAsync(r->qoff.p, qoff, (nq + 1) * 8, cudaMemcpyHostToDevice, s));
-    const bool thread_kernel = !file_mode && (idx->dbg_query_kernel == 1 || (idx->dbg_query_kernel == 0 && nq >= 4096));
+    // an array whose key ranges live on several GPUs is always queried one thread per query (with the probe cache)
+    const bool thread_kernel = !file_mode && (idx->sharded_sa || idx->dbg_query_kernel == 1 || (idx->dbg_query_kernel == 0 && nq >= 4096));
     if (thread_kernel) {
         int rc = ensure_qtop(idx, s);
         if (rc != SA_OK) return rc;
     }
     SA_CU(cudaEventRecord(r->ev[0], s));
-    if (file_mode)
+    if (idx->sharded_sa && !file_mode)
+        SA_CU(sa_launch_query_sharded(idx->text.as<uint8_t>(), idx->view, (uint32_t)idx->n, idx->L, r->qbytes.as<uint8_t>(),
+                                      r->qoff.as<uint64_t>(), (uint32_t)nq, r->qstart.as<uint32_t>(), r->qend.as<uint32_t>(), s,
+                                      idx->qtop_levels ? idx->qtop.p : nullptr, idx->qtop_levels));
+    else if (file_mode)
         SA_CU(sa_launch_query_file(idx->csv_file.as<uint8_t>(), idx->csv_file_bytes, idx->sa_file.as<uint32_t>(),
                                    (uint32_t)idx->n, idx->L, r->qbytes.as<uint8_t>(), r->qoff.as<uint64_t>(), (uint32_t)nq,
                                    r->qstart.as<uint32_t>(), r->qend.as<uint32_t>(), s));
@@ -200,6 +208,11 @@ static int expand_locked(sa_index* idx, sa_result* r, uint32_t flags, bool want_
     // FILE (what the remapped array holds, engine.c:647-651), record = row of the file (header = 0)
     const bool rows = idx->csv && idx->rowbits.p && idx->rowrank.p;
     uint32_t* d_pos = want_pos ? r->hitpos.as<uint32_t>() : nullptr;
+    if (idx->sharded_sa && !rows)
+        SA_CU(sa_launch_hits_sharded(idx->view, r->qstart.as<uint32_t>(), r->hitoff.as<uint64_t>(), nq,
+                                     idx->nlbits.as<unsigned long long>(), idx->nlrank.as<uint32_t>(), d_pos,
+                                     r->hitdoc.as<uint32_t>(), s));
+    else
     SA_CU(sa_launch_hits(rows ? idx->sa_file.as<uint32_t>() : idx->sa_final.as<uint32_t>(), r->qstart.as<uint32_t>(),
                          r->hitoff.as<uint64_t>(), nq,
                          rows ? idx->rowbits.as<unsigned long long>() : idx->nlbits.as<unsigned long long>(),
@@ -461,6 +474,7 @@ extern "C" int sa_query_ranges_device(sa_index* idx, const uint8_t* d_qbytes, co
     std::shared_lock<std::shared_mutex> rd(idx->mu);
     SA_REQUIRE(idx->built, SA_ERR_INVALID, "index not built");
     SA_REQUIRE(idx->n > 0, SA_ERR_INVALID, "empty index");
+    SA_REQUIRE(!idx->sharded_sa, SA_ERR_INVALID, "sa_query_ranges_device: not available on a SA_FLAG_SHARDED_SA index");
     std::lock_guard<std::mutex> g(r->mu);
     SA_CU(cudaSetDevice(idx->device));
     r->have_ranges = r->have_hits = r->have_records = false;

@@ -549,7 +549,9 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
         }
         SH_REQUIRE(base, SA_ERR_INVALID, "sa_shard_finish_bcast: rank %d has no final array", g);
         peer_base[g] = static_cast<uint32_t*>(base);
+        idx->shard_peer_base[g] = peer_base[g];
     }
+    const bool replicate = !idx->shard_no_replicate;             // SA_FLAG_SHARDED_SA: the shard stays where it is
     if (m == 0) return SA_OK;
     cudaStream_t s = idx->stream;
     // replication runs beside the finishing kernels: highest stream priority, so that its blocks are
@@ -587,7 +589,7 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
         uint64_t upto = last ? (uint64_t)nleft + m : (uint64_t)(b0 + per) * FTR;
         if (!last) upto = upto > 32 ? upto - 32 : 0;
         if (upto > (uint64_t)nleft + m) upto = (uint64_t)nleft + m;
-        if (upto <= copied_to) continue;
+        if (upto <= copied_to || !replicate) continue;
         const size_t off = (size_t)global_offset + copied_to - nleft, cnt = (size_t)(upto - copied_to);
         if (idx->dbg_replicate_memcpy) {      // copy engines instead of the store kernel (slower at 8 GPUs)
             for (int k = 1; k < nranks; ++k) {

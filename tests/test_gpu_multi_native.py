@@ -33,8 +33,9 @@ def _cases(rng):
     ]
 
 
+@pytest.mark.parametrize("sharded_sa", [False, True])
 @pytest.mark.parametrize("world", [2, 3, 8])
-def test_threads_of_one_process_match_oracle(world):
+def test_threads_of_one_process_match_oracle(world, sharded_sa):
     import torch
     ndev = torch.cuda.device_count()
     rng = np.random.default_rng(60 + world)
@@ -42,7 +43,8 @@ def test_threads_of_one_process_match_oracle(world):
     for text, L, lower in _cases(rng):
         if L not in idxs:
             idxs[L] = [S.Index(L, device=g % ndev) for g in range(world)]      # handles are reused across builds
-        S.build_text_multi(idxs[L], text, lowercase=lower)
+        # sharded_sa: no replication -- every handle keeps its key range, queries read the others through peer memory
+        S.build_text_multi(idxs[L], text, lowercase=lower, sharded_sa=sharded_sa)
         want_text = O.oracle_lowercase(text) if lower else text
         want = O.oracle_build(want_text, L)
         qs = [bytes(want_text[p:p + 5]).split(b"\n")[0] or b"a" for p in rng.integers(0, max(1, text.size - 5), 20)]
@@ -81,7 +83,9 @@ for rep, (n_chars, seed, lower) in enumerate([(400_000, 5, False), (150_000, 6, 
     n = int(text.size)
     a, b = rank * n // world, (rank + 1) * n // world             # this rank uploads ONLY its slice
     mine = np.ascontiguousarray(text[a:b])
-    ph = S.shard_build(idx, comm, mine.ctypes.data, a, b - a, n, S.SA_FLAG_LOWERCASE if lower else 0)
+    # the second build keeps the array distributed (SA_FLAG_SHARDED_SA): queries and sa() read the peers' shards
+    flags = (S.SA_FLAG_LOWERCASE if lower else 0) | (S.SA_FLAG_SHARDED_SA if rep == 1 else 0)
+    ph = S.shard_build(idx, comm, mine.ctypes.data, a, b - a, n, flags)
     want_text = O.oracle_lowercase(text) if lower else text
     want = O.oracle_build(want_text, 32)
     ok = ok and bool(np.array_equal(idx.sa(), want)) and bool(np.array_equal(idx.text(), want_text))
@@ -90,6 +94,7 @@ for rep, (n_chars, seed, lower) in enumerate([(400_000, 5, False), (150_000, 6, 
     ws, we = O.oracle_query(want_text, want, 32, qs)
     s, e, _ = idx.query_ranges(qs)
     ok = ok and bool(np.array_equal(s, ws) and np.array_equal(e, we))
+    comm.barrier()          # nobody rebuilds while a peer still reads this build's shard
 comm.barrier()
 idx.close()
 comm.close()
