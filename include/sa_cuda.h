@@ -216,6 +216,22 @@ int sa_attach_csv_file(sa_index* idx, const char* csv_path);
 int sa_query_ranges_device(sa_index* idx, const uint8_t* d_qbytes, const uint64_t* d_qoff, uint64_t nq,
                            uint64_t qbytes_len, uint32_t k, uint32_t* d_start, uint32_t* d_end);
 
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The hit-offset scan of a batch whose ranges are already on the device (sa_query_ranges_device):
+ * d_hit_off[q] = sum over q' < q of min(k, end[q'] - start[q'] + 1) (0 for a miss, start == UINT32_MAX;
+ * engine.c:1181-1185), d_hit_off[nq] = the total -- the numbers sa_query_ranges_r returns in hit_off.
+ * Calls no cudaMalloc / cudaFree / allocating routine and does not synchronise: three kernels are queued
+ * on `stream` (a cudaStream_t; NULL = the default stream) and the call returns.  Its scratch is a fixed
+ * __device__ array inside the library (128 KiB + 8 B on every GPU that loads it, held until exit):
+ * at most SA_NOALLOC_MAX_QUERIES queries per call, more -> SA_ERR_LIMIT.  All calls share that array:
+ * calls that overlap on the GPU (different streams without an event between them) race; calls on one
+ * stream are ordered.  The first call on a device looks up the array's device address
+ * (cudaGetSymbolAddress): make it outside graph capture. */
+#define SA_NOALLOC_MAX_QUERIES (1ull << 24)
+int sa_hit_offsets_noalloc(sa_index* idx, const uint32_t* d_start, const uint32_t* d_end, uint64_t nq, uint32_t k,
+                           uint64_t* d_hit_off, void* stream);
+
 /* Document table: doc_start[num_docs] = text offset of each record's first byte. */
 uint64_t sa_num_docs(const sa_index* idx);
 int sa_copy_doc_starts(sa_index* idx, uint32_t* out, uint64_t cap);

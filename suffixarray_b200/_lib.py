@@ -40,8 +40,9 @@ EXPORTS = [
     "sa_result_create", "sa_result_destroy", "sa_query_ranges_r", "sa_query_hits_r", "sa_query_records_size",
     "sa_query_records", "sa_result_stats", "sa_num_rows", "sa_copy_row_starts", "sa_attach_csv_file",
     "sa_comm_create_local", "sa_comm_create_shm", "sa_comm_destroy", "sa_comm_rank", "sa_comm_size", "sa_comm_barrier",
-    "sa_shard_build", "sa_shard_info", "sa_build_text_multi",
+    "sa_shard_build", "sa_shard_info", "sa_build_text_multi", "sa_hit_offsets_noalloc",
 ]
+SA_NOALLOC_MAX_QUERIES = 1 << 24
 
 
 class SaStats(C.Structure):
@@ -134,6 +135,7 @@ def lib():
     L.sa_query_ranges.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp, _vp]
     L.sa_query_hits.argtypes = [_vp, _vp, _vp, C.c_uint64]
     L.sa_query_ranges_device.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint64, C.c_uint32, _vp, _vp]
+    L.sa_hit_offsets_noalloc.argtypes = [_vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp]
     L.sa_debug_set.argtypes = [_vp, C.c_char_p, C.c_int64]
     L.sa_shard_begin.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32]
     L.sa_shard_begin_csv.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_uint32]
@@ -200,6 +202,11 @@ class Index:
         self._h = _vp()
         check(lib().sa_create(C.byref(self._h), max_suffix_length, device))
         self.max_suffix_length = max_suffix_length
+
+    def hit_offsets_noalloc(self, d_start: int, d_end: int, nq: int, k: int, d_hit_off: int, stream: int = 0) -> None:
+        """sa_hit_offsets_noalloc: device pointers in, nq + 1 u64 hit offsets out, queued on `stream`
+        (a cudaStream_t as int); allocates nothing, does not synchronise (include/sa_cuda.h)."""
+        check(lib().sa_hit_offsets_noalloc(self._h, _vp(d_start), _vp(d_end), nq, k, _vp(d_hit_off), _vp(stream)))
 
     def close(self):
         r = getattr(self, "_res", None)
