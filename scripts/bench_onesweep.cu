@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "../suffixarray_b200/csrc/radix.cu"
+#include "onesweep_variants.cuh"
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(1); } } while (0)
 

@@ -7,7 +7,6 @@
 
 // ---- radix.cu
 uint32_t sa_onesweep_tile_items();
-extern int sa_onesweep_variant;
 cudaError_t sa_launch_hist(const uint64_t* keys, uint32_t n, int shift0, int npasses, uint32_t* hist,
                            int num_sms, cudaStream_t s);
 cudaError_t sa_launch_scan_hist(const uint32_t* hist, uint32_t n, int npasses, uint32_t* base, uint32_t* skip,

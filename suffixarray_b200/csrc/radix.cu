@@ -79,8 +79,6 @@ constexpr int OS_IPT = 12, OS_LBW = 4, OS_LB_REGS = 24;
 constexpr int OS_TILE = 256 * OS_IPT;
 }  // namespace
 
-int sa_onesweep_variant = 0;     // sa_debug_set("onesweep_variant"): tuning experiments only
-
 uint32_t sa_onesweep_tile_items() { return OS_TILE; }   // smallest tile of any variant: sizes the status words
 
 cudaError_t sa_launch_hist(const uint64_t* keys, uint32_t n, int shift0, int npasses, uint32_t* hist,
@@ -108,15 +106,6 @@ cudaError_t sa_launch_onesweep(const uint64_t* keys_in, const uint32_t* vals_in,
                                uint32_t* status, uint32_t* tile_counter, uint32_t* err, bool identity_vals,
                                cudaStream_t s)
 {
-    switch (sa_onesweep_variant) {
-    case 1:   // persistent CTAs, in-line look-back, bulk-copy prefetch (the previous default)
-        return sa::launch_onesweep2_cfg<256, 16, 2, 0, 8, true>(keys_in, vals_in, keys_out, vals_out, n, shift, digit_base,
-                                                                status, tile_counter, err, identity_vals, s);
-    case 2:   // same without the prefetch
-        return sa::launch_onesweep2_cfg<256, 16, 2, 0, 8, false>(keys_in, vals_in, keys_out, vals_out, n, shift, digit_base,
-                                                                 status, tile_counter, err, identity_vals, s);
-    default:  // warp-specialised look-back
-        return sa::launch_onesweep4_cfg<OS_IPT, 2, OS_LBW, OS_LB_REGS>(keys_in, vals_in, keys_out, vals_out, n, shift,
-                                                                       digit_base, status, tile_counter, err, identity_vals, s);
-    }
+    return sa::launch_onesweep4_cfg<OS_IPT, 2, OS_LBW, OS_LB_REGS>(keys_in, vals_in, keys_out, vals_out, n, shift, digit_base,
+                                                                   status, tile_counter, err, identity_vals, s);
 }

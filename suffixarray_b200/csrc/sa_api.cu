@@ -189,7 +189,6 @@ extern "C" int sa_debug_set(sa_index* idx, const char* key, int64_t value)
     else if (!strcmp(key, "same_process")) idx->dbg_same_process = value;
     else if (!strcmp(key, "query_kernel")) idx->dbg_query_kernel = value;
     else if (!strcmp(key, "qtop_levels")) { idx->dbg_qtop_levels = value; idx->qtop_ready = false; }
-    else if (!strcmp(key, "onesweep_variant")) sa_onesweep_variant = (int)value;
     else { sa_set_error("unknown debug key %s", key); return SA_ERR_INVALID; }
     return SA_OK;
 }
