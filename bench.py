@@ -682,6 +682,9 @@ def run_ours_global_native(args, world, rank, local):
     ms = torch.tensor([float(recs[-1]["m"]), float(recs[-1]["exchange_bytes"])], dtype=torch.float64, device=dev)
     ms_all = [torch.zeros_like(ms) for _ in range(world)]
     dist.all_gather(ms_all, ms)
+    ph_mine = torch.tensor([sum(r["phases"][p] for r in recs) / max(1, len(recs)) for p in phase_names], dtype=torch.float64, device=dev)
+    ph_all = [torch.zeros_like(ph_mine) for _ in range(world)]
+    dist.all_gather(ph_all, ph_mine)
     result = None
     if rank == 0:
         build_ms, query_ms, build_e2e_ms, query_e2e_ms = (sums[:4] / K).tolist()
@@ -711,12 +714,15 @@ def run_ours_global_native(args, world, rank, local):
         if verify is not None:
             result["verify"] = verify
         result["multi_gpu"] = {"phases_ms_max_over_ranks": phases, "phases_e2e_ms_max_over_ranks": phases_e2e,
+                               "phases_ms_by_rank": {p: [round(float(x[i]), 3) for x in ph_all] for i, p in enumerate(phase_names)},
                                "shard_records": shard_sizes,
                                "imbalance": round(max(shard_sizes) * world / max(sum(shard_sizes), 1), 4),
                                "exchange_bytes_sent_per_rank": xbytes,
                                "exchange_gbs_per_rank": round(max(xbytes) / (xms * 1e-3) / 1e9, 1) if xms > 0 else None,
-                               "text_allgather_gbs_per_rank": (round(mlen * (world - 1) / (phases["text"] * 1e-3) / 1e9, 1)
-                                                               if phases.get("text", 0) > 0 else None),
+                               "text_allgather": ("asynchronous: every rank's slice goes to the peers on the copy engines beside "
+                                                  "prepare / pack / split / exchange; the `text` phase is the upload of the own slice, "
+                                                  "the wait for the peers' slices is inside `exchange`"),
+                               "text_bytes_sent_per_rank": int(mlen * (world - 1)),
                                "replicate_bytes_sent_per_rank": int(rep_bytes),
                                "finish_replicate_gbs_per_rank": (round(rep_bytes / (phases["finish+replicate"] * 1e-3) / 1e9, 1)
                                                                  if phases.get("finish+replicate", 0) > 0 else None),

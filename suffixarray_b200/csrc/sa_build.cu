@@ -226,7 +226,7 @@ int sa_stage_prepare(sa_index* idx, uint32_t flags)
 // Alphabet: dense order-preserving codes when <= 128 byte values occur (NUL is always code 0).
 // present[256]: which byte values occur in the text (host).  Encodes idx->text into idx->codes and
 // leaves idx->code, idx->cb0, idx->max_chars set.
-int sa_stage_alphabet(sa_index* idx, const uint32_t* present)
+int sa_stage_alphabet(sa_index* idx, const uint32_t* present, uint64_t enc_lo, uint64_t enc_hi)
 {
     cudaStream_t s = idx->stream;
     const uint32_t n = (uint32_t)idx->n;
@@ -251,8 +251,13 @@ int sa_stage_alphabet(sa_index* idx, const uint32_t* present)
             SA_CU(idx->codes.ensure(tbytes));
             uint8_t* d_table = reinterpret_cast<uint8_t*>(sm + SM_TABLE);
             SA_CU(cudaMemcpyAsync(d_table, table, 256, cudaMemcpyHostToDevice, s));
-            SA_CU(sa_launch_encode(idx->text.as<uint8_t>(), tbytes, d_table, idx->codes.as<uint8_t>(), s));
-            st.kernel_launches += 1;
+            // [enc_lo, enc_hi) (16-byte aligned; default: everything) -- the sharded build encodes its own
+            // range first and the rest once the peers' slices have landed (sa_stage_encode_range)
+            if (enc_hi > tbytes) enc_hi = tbytes;
+            if (enc_lo < enc_hi) {
+                SA_CU(sa_launch_encode(idx->text.as<uint8_t>() + enc_lo, enc_hi - enc_lo, d_table, idx->codes.as<uint8_t>() + enc_lo, s));
+                st.kernel_launches += 1;
+            }
         }
     }
     idx->code = ci;
@@ -260,6 +265,20 @@ int sa_stage_alphabet(sa_index* idx, const uint32_t* present)
     idx->max_chars = ci.bits == 8 ? 8 : (63 / ci.bits > 16 ? 16 : 63 / ci.bits);
     idx->cb0 = idx->lprime < (uint32_t)idx->max_chars ? (int)idx->lprime : idx->max_chars;
     if (idx->dbg_sort0_chars >= 1 && idx->dbg_sort0_chars < idx->cb0) idx->cb0 = (int)idx->dbg_sort0_chars;
+    return SA_OK;
+}
+
+// Encode text[lo, hi) (16-byte aligned bounds, hi clipped to the padded size) with the table sa_stage_alphabet left
+// on the device; a no-op for 8-bit alphabets (the text is its own key source).
+int sa_stage_encode_range(sa_index* idx, uint64_t lo, uint64_t hi)
+{
+    if (idx->code.bits == 8 || !idx->lprime) return SA_OK;
+    const size_t tbytes = ((size_t)idx->n + SA_TEXT_PAD + 255) & ~(size_t)255;
+    if (hi > tbytes) hi = tbytes;
+    if (lo >= hi) return SA_OK;
+    const uint8_t* d_table = reinterpret_cast<const uint8_t*>(idx->small.as<uint32_t>() + SM_TABLE);
+    SA_CU(sa_launch_encode(idx->text.as<uint8_t>() + lo, hi - lo, d_table, idx->codes.as<uint8_t>() + lo, idx->stream));
+    idx->stats.kernel_launches += 1;
     return SA_OK;
 }
 

@@ -182,6 +182,10 @@ struct sa_index {
     int64_t dbg_query_kernel = 0;   // 0: by batch size; 1: one thread per query; 2: eight lanes per query
     int64_t dbg_same_process = 0;   // sharded build: peers live in this process (raw pointers instead of IPC)
     int64_t dbg_replicate_memcpy = 0;   // sharded finish: replicate with cudaMemcpyAsync instead of replicate_kernel
+    int64_t dbg_timeline = 0;       // sharded finish: print when each chunk was finished / pushed (stderr, CUDA events)
+    int64_t dbg_replicate_ctas = 0; // sharded finish: k > 0 = 512-thread push kernel with k blocks (0: 64); k < 0 = the 128-thread co-resident kernel
+    int64_t dbg_text_push = 0;      // sharded build: 0 = text slices travel on the copy engines beside pack / exchange; 1 = blocking push kernel
+    int64_t dbg_finish_chunks = 0;  // sharded finish: chunks the shard is finished / pushed in (0: 8; at most 16)
     int64_t dbg_csv_scanner = 0;    // 0: device scan, host scan for irregular files; 1: host scan; 2: device scan or fail
     int64_t dbg_sort0_chars = -1;   // -1: automatic; else at most this many characters in the first sort's keys
     int64_t dbg_code_bits = -1;     // -1: choose from the alphabet; 8: never compress; 1..7: at least this width
@@ -222,7 +226,8 @@ struct ScopedPhase {
 
 int sa_build_resident(sa_index* idx, uint32_t flags);
 int sa_stage_prepare(sa_index* idx, uint32_t flags);
-int sa_stage_alphabet(sa_index* idx, const uint32_t* present);
+int sa_stage_alphabet(sa_index* idx, const uint32_t* present, uint64_t enc_lo = 0, uint64_t enc_hi = ~0ull);
+int sa_stage_encode_range(sa_index* idx, uint64_t lo, uint64_t hi);
 const uint8_t* sa_key_source(const sa_index* idx);
 int sa_ensure_scratch(sa_index* idx, uint32_t m);
 int sa_stage_sort_refine(sa_index* idx, uint32_t m, bool identity, uint32_t** sa_sorted);

@@ -29,6 +29,7 @@
 #include <time.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <atomic>
 #include <new>
 #include <string>
@@ -461,17 +462,25 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
     unsigned long long* peer_nlbits[16] = {};
     uint32_t* peer_nlrank[16] = {};
     uint8_t final_handles[16 * 64];
+    uint64_t slice_lo[16] = {}, slice_hi[16] = {};       // every rank's slice of the text
     {
-        Export ex[4];
+        Export ex[5];
         export_buffer(idx, c->local, idx->text.p, ex[0].handle);
         export_buffer(idx, c->local, idx->sa_final.p, ex[1].handle);
         export_buffer(idx, c->local, idx->nlbits.p, ex[2].handle);
         export_buffer(idx, c->local, idx->nlrank.p, ex[3].handle);
+        memset(ex[4].handle, 0, 64);
+        memcpy(ex[4].handle, &slice_off, 8);
+        memcpy(ex[4].handle + 8, &slice_len, 8);
         const uint8_t* all = nullptr;
         MG_TRY(comm_allgather(c, ex, sizeof ex, &all));
         for (int g = 0; g < R; ++g) {
             const Export* e = reinterpret_cast<const Export*>(all + (size_t)g * MAILBOX_BYTES);
             memcpy(final_handles + (size_t)g * 64, e[1].handle, 64);
+            uint64_t len = 0;
+            memcpy(&slice_lo[g], e[4].handle, 8);
+            memcpy(&len, e[4].handle + 8, 8);
+            slice_hi[g] = slice_lo[g] + len;
             if (g == me) {
                 peer_text[g] = idx->text.as<uint8_t>();
                 peer_nlbits[g] = idx->nlbits.as<unsigned long long>();
@@ -511,21 +520,49 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
         // peers zero their own padding before anything of mine can land in it: the tail bytes [pad_from, n)
         // of the LAST slice are the only overlap, and they are pushed after the barrier below
         MG_CU(cudaStreamSynchronize(s));
-        MG_TRY(comm_barrier(c));
-        if (R > 1 && slice_len) {
-            sa::PushTable pt{};
-            for (int k = 1; k < R; ++k) pt.dst[pt.n++] = peer_text[(me + k) % R] + slice_off;
-            sa::push_bytes_kernel<<<idx->num_sms * 2, 512, 0, s>>>(d_text + slice_off, slice_len, pt);
-            MG_CU(cudaGetLastError());
-            MG_CU(cudaStreamSynchronize(s));
+        MG_TRY(comm_barrier(c));          // every rank's own slice sits in its own buffer
+    }
+    // This rank prepares and packs the positions [b_lo, b_hi) (4096-aligned bounds; they need not coincide with
+    // the slice it uploaded) and reads up to 64 bytes beyond them.
+    auto bound = [&](int g) -> uint64_t { return g >= R ? n : (g <= 0 ? 0 : (((uint64_t)g * n / R) & ~4095ull)); };
+    const uint64_t b_lo = bound(me), b_hi = bound(me + 1);
+    const uint64_t own_hi = (std::min<uint64_t>(text_bytes, b_hi + 64) + 15) & ~15ull;    // end of the early encode
+    const bool async_text = R > 1 && idx->dbg_text_push == 0;
+    if (R > 1) {
+        if (async_text) {
+            // 1. pull the part of [b_lo, b_hi + 64) other ranks uploaded straight from their buffers (a few KB when
+            //    the slices follow the bounds); 2. send this slice to every peer with the copy engines, beside the
+            //    prepare / pack / split / exchange kernels: the whole text is only needed by the refinement rounds.
+            const uint64_t need_hi = std::min<uint64_t>(n, b_hi + 64);
+            for (int g = 0; g < R; ++g) {
+                if (g == me) continue;
+                const uint64_t lo = std::max(b_lo, slice_lo[g]), hi = std::min(need_hi, slice_hi[g]);
+                if (lo < hi) MG_CU(cudaMemcpyAsync(d_text + lo, peer_text[g] + lo, hi - lo, cudaMemcpyDeviceToDevice, s));
+            }
+            if (slice_len) {
+                int lo = 0, hi = 0;
+                cudaDeviceGetStreamPriorityRange(&lo, &hi);
+                for (int k = 1; k < R; ++k) {
+                    const int g = (me + k) % R;
+                    if (!idx->copy_streams[g]) MG_CU(cudaStreamCreateWithPriority(&idx->copy_streams[g], cudaStreamNonBlocking, hi));
+                    MG_CU(cudaMemcpyAsync(peer_text[g] + slice_off, d_text + slice_off, slice_len, cudaMemcpyDeviceToDevice,
+                                          idx->copy_streams[g]));
+                }
+            }
+        } else {
+            if (slice_len) {
+                sa::PushTable pt{};
+                for (int k = 1; k < R; ++k) pt.dst[pt.n++] = peer_text[(me + k) % R] + slice_off;
+                sa::push_bytes_kernel<<<idx->num_sms * 2, 512, 0, s>>>(d_text + slice_off, slice_len, pt);
+                MG_CU(cudaGetLastError());
+                MG_CU(cudaStreamSynchronize(s));
+            }
+            MG_TRY(comm_barrier(c));          // the whole text is on every GPU
         }
-        MG_TRY(comm_barrier(c));          // the whole text is on every GPU
     }
     lap.mark();
 
     // ---- prepare: newline table + byte presence on this rank's slice of POSITIONS (4096-aligned)
-    auto bound = [&](int g) -> uint64_t { return g >= R ? n : (g <= 0 ? 0 : (((uint64_t)g * n / R) & ~4095ull)); };
-    const uint64_t b_lo = bound(me), b_hi = bound(me + 1);
     const uint32_t m_local = (uint32_t)(b_hi - b_lo);
     uint32_t* sm = idx->small.as<uint32_t>();
     MG_CU(cudaMemsetAsync(sm + SM_ERR, 0, 4 * sizeof(uint32_t), s));
@@ -578,8 +615,9 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
             std::unique_lock<std::shared_mutex> lock(idx->mu);
             idx->num_nl = nl_total;
             idx->stats.num_docs = (uint64_t)nl_total + 1;
-            // alphabet codes of the WHOLE text, locally (one pass over HBM; cheaper than receiving them)
-            rc = sa_stage_alphabet(idx, present);
+            // alphabet codes, locally (one pass over HBM; cheaper than receiving them): the whole text, or -- while
+            // the peers' slices are still on their way -- this rank's range now and the rest before the sort
+            rc = async_text ? sa_stage_alphabet(idx, present, b_lo, own_hi) : sa_stage_alphabet(idx, present);
         }
         if (rc != SA_OK) return fail(rc);
         MG_CU(cudaStreamSynchronize(s));
@@ -610,11 +648,12 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
             for (int b = 0; b < 65536; ++b) hist[b] += w * h[b];
         }
         // bins in order; rank g gets the bins whose first record falls into the g-th equal share
-        uint64_t total = 0, before = 0;
+        uint64_t total = 0, before = 0, r = 0;
         for (int b = 0; b < 65536; ++b) total += hist[b];
         for (int b = 0; b < 65536; ++b) {
-            uint64_t r = total ? before * (uint64_t)R / total : 0;
-            bin2rank[b] = (uint8_t)(r < (uint64_t)R ? r : (uint64_t)R - 1);
+            // r = min(R - 1, floor(before * R / total)), stepped instead of divided (before only grows)
+            while (r + 1 < (uint64_t)R && (r + 1) * total <= before * (uint64_t)R) ++r;
+            bin2rank[b] = (uint8_t)r;
             before += hist[b];
         }
     }
@@ -649,7 +688,14 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
     // ---- exchange: every record straight into its owner's sort buffers
     MG_TRY(sa_shard_scatter_p2p(idx, idx->pack_keys.as<uint64_t>(), idx->pack_pos.as<uint32_t>(), m_local, R, me, handles.data(),
                                 dst_off));
-    MG_TRY(comm_barrier(c));                  // all peer stores have landed
+    if (async_text)
+        for (int g = 0; g < R; ++g)
+            if (g != me && idx->copy_streams[g]) MG_CU(cudaStreamSynchronize(idx->copy_streams[g]));   // my slice has left
+    MG_TRY(comm_barrier(c));                  // all peer stores have landed (records, and every slice of the text)
+    if (async_text) {
+        MG_TRY(sa_stage_encode_range(idx, 0, b_lo));
+        MG_TRY(sa_stage_encode_range(idx, own_hi, text_bytes));
+    }
     lap.mark();
 
     // ---- sort + refine the received key range

@@ -485,6 +485,45 @@ __global__ void __launch_bounds__(512) replicate_kernel(const uint32_t* __restri
         for (int g = 0; g < t.n; ++g) t.dst[g][j] = v;
     }
 }
+
+// The same push as a kernel that fits BESIDE the finishing kernel instead of competing with it for block
+// slots: six resident finish_kernel blocks (256 threads x 40 registers, 33 KB of shared memory each) leave
+// 512 threads and 4096 registers of an SM free -- exactly one block of 128 threads x 32 registers.  Four
+// 16-byte loads per thread are in flight before their 4 x n peer stores are issued (stores are posted, so
+// only the local load latency is exposed).
+constexpr int REP_THREADS = 128, REP_UNROLL = 4;
+__global__ void __launch_bounds__(REP_THREADS, 16) replicate_small_kernel(const uint32_t* __restrict__ src, uint64_t count,
+                                                                          ReplicaTable t)
+{
+    const uint64_t head = min(count, (uint64_t)((16u - ((uintptr_t)src & 15u)) & 15u) / 4u);
+    const uint64_t nvec = (count - head) / 4u;
+    const uint64_t tail0 = head + nvec * 4u;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (uint64_t)gridDim.x * blockDim.x;
+    const uint4* sv = reinterpret_cast<const uint4*>(src + head);
+    const uint32_t nv = (uint32_t)nvec, nt = (uint32_t)nthreads;          // count <= n < 2^32 entries -> nvec < 2^30
+    for (uint32_t i0 = (uint32_t)tid; i0 < nv; i0 += nt * REP_UNROLL) {
+        uint4 v[REP_UNROLL];
+#pragma unroll
+        for (int u = 0; u < REP_UNROLL; ++u) {
+            const uint32_t i = i0 + (uint32_t)u * nt;
+            if (i < nv) v[u] = __ldcs(sv + i);
+        }
+#pragma unroll 1
+        for (int g = 0; g < t.n; ++g) {
+            uint4* d = reinterpret_cast<uint4*>(t.dst[g] + head);
+#pragma unroll
+            for (int u = 0; u < REP_UNROLL; ++u) {
+                const uint32_t i = i0 + (uint32_t)u * nt;
+                if (i < nv) d[i] = v[u];
+            }
+        }
+    }
+    for (uint64_t i = tid; i < head + (count - tail0); i += nthreads) {
+        const uint64_t j = i < head ? i : tail0 + (i - head);
+        const uint32_t v = src[j];
+        for (int g = 0; g < t.n; ++g) t.dst[g][j] = v;
+    }
+}
 }  // namespace sa
 
 // ------------------------------------------------------------------------------ finish + replicate, overlapped
@@ -561,7 +600,8 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     for (int g = 0; g < nranks; ++g)
         if (g != my_rank && !idx->copy_streams[g])
             SA_CU(cudaStreamCreateWithPriority(&idx->copy_streams[g], cudaStreamNonBlocking, prio_hi));
-    constexpr int CHUNKS = 8;
+    constexpr int MAX_CHUNKS = 16;
+    const int CHUNKS = idx->dbg_finish_chunks >= 1 && idx->dbg_finish_chunks <= MAX_CHUNKS ? (int)idx->dbg_finish_chunks : 8;
     for (int c = 0; c < CHUNKS; ++c)
         if (!idx->chunk_ev[c]) SA_CU(cudaEventCreateWithFlags(&idx->chunk_ev[c], cudaEventDisableTiming));
 
@@ -579,11 +619,22 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     const uint32_t blocks = sa_finish_blocks(total), FTR = sa_finish_block_ranks();
     const uint32_t per = (blocks + CHUNKS - 1) / CHUNKS;
     uint32_t copied_to = nleft;               // extended rank up to which the peers are up to date
+    // sa_debug_set("timeline", 1): when each chunk was finished / pushed, in ms after the first launch
+    const bool tl = idx->dbg_timeline != 0;
+    cudaEvent_t tl_ev[1 + 3 * MAX_CHUNKS] = {};
+    if (tl) {
+        for (auto& e : tl_ev) SA_CU(cudaEventCreate(&e));
+        SA_CU(cudaEventRecord(tl_ev[0], s));
+    }
+    // sa_debug_set("replicate_ctas", k): k > 0 = push kernel with k blocks of 512 threads (default 64, measured best at
+    // 4 GPUs: profiles/r02_multi_gpu_phases.md); k < 0 = the 128-thread kernel that fits beside the finishing blocks
+    const unsigned rep_ctas = idx->dbg_replicate_ctas > 0 ? (unsigned)idx->dbg_replicate_ctas : (idx->dbg_replicate_ctas < 0 ? 0u : 64u);
     for (int c = 0; c < CHUNKS && (uint64_t)c * per < blocks; ++c) {
         const uint32_t b0 = (uint32_t)c * per;
         rc = sa_stage_finish_to(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end, fo, b0, per);
         if (rc != SA_OK) return rc;
         SA_CU(cudaEventRecord(idx->chunk_ev[c], s));
+        if (tl) SA_CU(cudaEventRecord(tl_ev[1 + 3 * c], s));
         // a bucket may reach 32 ranks back into the previous chunk: ranks below hi_c - 32 are final now
         const bool last = (uint64_t)(c + 1) * per >= blocks;
         uint64_t upto = last ? (uint64_t)nleft + m : (uint64_t)(b0 + per) * FTR;
@@ -603,8 +654,13 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
             for (int k = 1; k < nranks; ++k) rt.dst[rt.n++] = peer_base[(my_rank + k) % nranks] + off;
             cudaStream_t cs = idx->copy_streams[(my_rank + 1) % nranks];
             SA_CU(cudaStreamWaitEvent(cs, idx->chunk_ev[c], 0));
-            sa::replicate_kernel<<<64, 512, 0, cs>>>(peer_base[my_rank] + off, (uint64_t)cnt, rt);
+            if (tl) SA_CU(cudaEventRecord(tl_ev[2 + 3 * c], cs));
+            if (rep_ctas)
+                sa::replicate_kernel<<<rep_ctas, 512, 0, cs>>>(peer_base[my_rank] + off, (uint64_t)cnt, rt);
+            else
+                sa::replicate_small_kernel<<<idx->num_sms * 2, sa::REP_THREADS, 0, cs>>>(peer_base[my_rank] + off, (uint64_t)cnt, rt);
             SA_CU(cudaGetLastError());
+            if (tl) SA_CU(cudaEventRecord(tl_ev[3 + 3 * c], cs));
             idx->stats.kernel_launches += 1;
         }
         copied_to = (uint32_t)upto;
@@ -612,6 +668,20 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     for (int g = 0; g < nranks; ++g)
         if (g != my_rank) SA_CU(cudaStreamSynchronize(idx->copy_streams[g]));
     rc = sa_check_device_error(idx);          // synchronises the build stream
+    if (tl) {
+        char line[2048];
+        int at = snprintf(line, sizeof line, "[timeline rank %d] chunk: finished | push start..end (ms)", my_rank);
+        for (int c = 0; c < CHUNKS; ++c) {
+            float f = -1.f, a = -1.f, b = -1.f;
+            cudaEventElapsedTime(&f, tl_ev[0], tl_ev[1 + 3 * c]);
+            cudaEventElapsedTime(&a, tl_ev[0], tl_ev[2 + 3 * c]);
+            cudaEventElapsedTime(&b, tl_ev[0], tl_ev[3 + 3 * c]);
+            at += snprintf(line + at, sizeof line - (size_t)at, "  %d: %.2f | %.2f..%.2f", c, f, a, b);
+        }
+        cudaGetLastError();                   // events of skipped chunks were never recorded
+        fprintf(stderr, "%s\n", line);
+        for (auto& e : tl_ev) cudaEventDestroy(e);
+    }
     sa_time_collect(idx);
     return rc;
 }
