@@ -703,7 +703,9 @@ def run_ours_global_native(args, world, rank, local):
         result["config_detail"] = {
             "driver": "native: sa_shard_build, one call per rank; node-local communicator over POSIX shared memory + CUDA IPC",
             "sharding": "one global index over the N concatenated per-rank texts: every rank uploads its slice and pushes it to "
-                        "the peers over NVLink; sample sort with splitters from the summed 65536-bin key histogram; records "
+                        "the peers over NVLink; sample sort with splitters from the summed 65536-bin key histogram, bins weighted by the "
+                        "sampled share of keys that repeat (those records go through the refinement rounds: shards are balanced "
+                        "by expected work, not by record count); records "
                         "stored straight into the owner's sort buffers (peer stores); 128-record halos + device-side junction "
                         "LCPs; each shard finished in chunks into the final array while finished chunks are pushed into every "
                         "peer's array",

@@ -95,7 +95,9 @@ extern "C" void sa_destroy(sa_index* idx)
     for (int i = 0; i < 16; ++i) {
         if (idx->copy_streams[i]) cudaStreamDestroy(idx->copy_streams[i]);
         if (idx->chunk_ev[i]) cudaEventDestroy(idx->chunk_ev[i]);
+        if (idx->ext_ev[i]) cudaEventDestroy(idx->ext_ev[i]);
     }
+    if (idx->ext_ev[16]) cudaEventDestroy(idx->ext_ev[16]);
     for (int i = 0; i < 2; ++i) {
         if (idx->h_ring[i]) cudaFreeHost(idx->h_ring[i]);
         if (idx->ring_ev[i]) cudaEventDestroy(idx->ring_ev[i]);

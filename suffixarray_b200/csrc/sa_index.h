@@ -148,6 +148,7 @@ struct sa_index {
     bool peer_final_mapped[16] = {};
     cudaStream_t copy_streams[16] = {};        // replication copies (one stream per peer) run beside the finishing kernels
     cudaEvent_t chunk_ev[16] = {};
+    cudaEvent_t ext_ev[17] = {};               // sharded finish: piece c of the shard staged into the ext arrays (+ "inputs ready")
 
     // queries: per-call state lives in sa_result; `generation` changes with every build / load so a
     // result of an older array cannot be expanded against a newer one
@@ -185,6 +186,8 @@ struct sa_index {
     int64_t dbg_timeline = 0;       // sharded finish: print when each chunk was finished / pushed (stderr, CUDA events)
     int64_t dbg_replicate_ctas = 0; // sharded finish: k > 0 = 512-thread push kernel with k blocks (0: 64); k < 0 = the 128-thread co-resident kernel
     int64_t dbg_text_push = 0;      // sharded build: 0 = text slices travel on the copy engines beside pack / exchange; 1 = blocking push kernel
+    int64_t dbg_split_gamma_x100 = -1;   // sharded build: extra cost of a record whose first-sort key repeats, in 1/100 records (-1: 170; 0: equal counts)
+    int64_t dbg_ext_fill = 0;       // sharded finish: 1 = one kernel copies the whole shard into the ext arrays first (round-1 behaviour)
     int64_t dbg_finish_chunks = 0;  // sharded finish: chunks the shard is finished / pushed in (0: 8; at most 16)
     int64_t dbg_csv_scanner = 0;    // 0: device scan, host scan for irregular files; 1: host scan; 2: device scan or fail
     int64_t dbg_sort0_chars = -1;   // -1: automatic; else at most this many characters in the first sort's keys

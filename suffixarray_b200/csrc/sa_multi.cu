@@ -49,7 +49,7 @@
 // ------------------------------------------------------------------------------ communicator
 namespace {
 
-constexpr size_t MAILBOX_BYTES = 65536 * sizeof(uint32_t) + 8192;   // one histogram, or a few KB of small data
+constexpr size_t MAILBOX_BYTES = 2 * 65536 * sizeof(uint32_t) + 8192;   // two histograms, or a few KB of small data
 constexpr double COMM_TIMEOUT_S = 120.0;
 
 struct CommShared {
@@ -292,6 +292,34 @@ __global__ void junction_lcp_kernel(const uint8_t* __restrict__ text, uint64_t n
     out[t] = r;
 }
 
+}  // namespace sa
+
+// Cost-weighted splitters: how many of the slice's sampled keys (the sample hist16_kernel takes) have a twin --
+// another sampled key with the same 64 bits -- per top-16-bit bin.  Records whose whole first-sort key repeats
+// are the ones the refinement rounds work on, and they cost ~2.7x a record that is placed by the first sort
+// (profiles/r02_multi_gpu_phases.md), so key ranges with many of them get fewer records.  Two passes over the
+// sample with a table of 2^24 counters addressed by a hash of the key (9 % of the slots taken at 1.5 M samples:
+// a false twin now and then only adds a near-uniform offset).
+namespace sa {
+constexpr int TWIN_TABLE_BITS = 24;
+__device__ __forceinline__ uint32_t twin_slot(uint64_t key) { return (uint32_t)((key * 0x9E3779B97F4A7C15ull) >> (64 - TWIN_TABLE_BITS)); }
+
+__global__ void twin_count_kernel(const uint64_t* __restrict__ keys, uint32_t m, uint32_t stride_keys, uint32_t* __restrict__ table)
+{
+    const uint32_t ms = (m + stride_keys - 1) / stride_keys;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ms; i += gridDim.x * blockDim.x)
+        atomicAdd(table + twin_slot(__ldg(keys + (size_t)i * stride_keys)), 1u);
+}
+
+__global__ void twin_hist_kernel(const uint64_t* __restrict__ keys, uint32_t m, uint32_t stride_keys,
+                                 const uint32_t* __restrict__ table, uint32_t* __restrict__ hist)
+{
+    const uint32_t ms = (m + stride_keys - 1) / stride_keys;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ms; i += gridDim.x * blockDim.x) {
+        const uint64_t k = __ldg(keys + (size_t)i * stride_keys);
+        if (table[twin_slot(k)] >= 2u) atomicAdd(hist + (uint32_t)(k >> 48), 1u);
+    }
+}
 }  // namespace sa
 
 // ------------------------------------------------------------------------------ peer buffers
@@ -632,29 +660,48 @@ extern "C" int sa_shard_build(sa_index* idx, sa_comm* c, const uint8_t* text_sli
     // ---- pack: round-0 keys of the slice + top-16-bit histogram; sum over the ranks
     MG_CU(idx->pack_keys.ensure((size_t)(m_local ? m_local : 1) * 8));
     MG_CU(idx->pack_pos.ensure((size_t)(m_local ? m_local : 1) * 4));
-    MG_CU(idx->hist16.ensure(65536 * 4));
-    MG_CU(cudaMemsetAsync(idx->hist16.p, 0, 65536 * 4, s));
+    MG_CU(idx->hist16.ensure(2 * 65536 * 4));                 // sampled keys per bin | sampled keys with a twin per bin
+    MG_CU(cudaMemsetAsync(idx->hist16.p, 0, 2 * 65536 * 4, s));
     MG_TRY(sa_shard_pack(idx, b_lo, b_hi, idx->pack_keys.as<uint64_t>(), idx->pack_pos.as<uint32_t>(), idx->hist16.as<uint32_t>()));
+    // sa_debug_set("split_gamma_x100", g): a record whose key repeats counts 1 + g / 100 (default 1.7, profiles/r02_multi_gpu_phases.md); 0 = equal record counts
+    const uint64_t gamma100 = idx->dbg_split_gamma_x100 >= 0 ? (uint64_t)idx->dbg_split_gamma_x100 : 170u;
+    if (gamma100 && m_local && R > 1) {
+        const size_t tbytes = ((size_t)4 << sa::TWIN_TABLE_BITS);
+        MG_CU(idx->aux[1].ensure(tbytes));
+        MG_CU(cudaMemsetAsync(idx->aux[1].p, 0, tbytes, s));
+        const uint32_t stride_keys = m_local >= (16u << 20) ? 64u : 16u;       // the sample of hist16_kernel (sa_shard_pack)
+        sa::twin_count_kernel<<<idx->num_sms * 8, 256, 0, s>>>(idx->pack_keys.as<uint64_t>(), m_local, stride_keys, idx->aux[1].as<uint32_t>());
+        sa::twin_hist_kernel<<<idx->num_sms * 8, 256, 0, s>>>(idx->pack_keys.as<uint64_t>(), m_local, stride_keys, idx->aux[1].as<uint32_t>(),
+                                                             idx->hist16.as<uint32_t>() + 65536);
+        MG_CU(cudaGetLastError());
+        idx->stats.kernel_launches += 2;
+    }
     std::vector<uint8_t> bin2rank(65536);
     {
-        MG_CU(cudaMemcpyAsync(idx->h_big, idx->hist16.p, 65536 * 4, cudaMemcpyDeviceToHost, s));
+        MG_CU(cudaMemcpyAsync(idx->h_big, idx->hist16.p, 2 * 65536 * 4, cudaMemcpyDeviceToHost, s));
         MG_CU(cudaStreamSynchronize(s));
         const uint8_t* all = nullptr;
-        MG_TRY(comm_allgather(c, idx->h_big, 65536 * 4, &all));
-        std::vector<uint64_t> hist(65536, 0);
+        MG_TRY(comm_allgather(c, idx->h_big, 2 * 65536 * 4, &all));
+        // per bin: records and records with a twin (sample counts x the rank's sample stride; both stay below n < 2^32,
+        // so the sums over the ranks run in 32 bits -- the compiler vectorises these loops, the 64-bit form cost 0.4 ms)
+        std::vector<uint32_t> acc(2 * 65536, 0);
         for (int g = 0; g < R; ++g) {
-            const uint32_t* h = reinterpret_cast<const uint32_t*>(all + (size_t)g * MAILBOX_BYTES);
-            const uint64_t w = (bound(g + 1) - bound(g)) >= (16u << 20) ? 64 : 16;      // the rank's sample stride (sa_shard_pack)
-            for (int b = 0; b < 65536; ++b) hist[b] += w * h[b];
+            const uint32_t* __restrict__ h = reinterpret_cast<const uint32_t*>(all + (size_t)g * MAILBOX_BYTES);
+            const uint32_t w = (bound(g + 1) - bound(g)) >= (16u << 20) ? 64u : 16u;      // the rank's sample stride (sa_shard_pack)
+            uint32_t* __restrict__ a = acc.data();
+            for (int b = 0; b < 2 * 65536; ++b) a[b] += w * h[b];
         }
-        // bins in order; rank g gets the bins whose first record falls into the g-th equal share
+        // bins in order; rank g gets the bins whose first record falls into the g-th equal share of the cost
+        // (in 1/100 records: 100 per record + gamma100 per record with a twin)
+        const uint32_t* cntv = acc.data();
+        const uint32_t* twv = acc.data() + 65536;
         uint64_t total = 0, before = 0, r = 0;
-        for (int b = 0; b < 65536; ++b) total += hist[b];
+        for (int b = 0; b < 65536; ++b) total += 100ull * cntv[b] + gamma100 * twv[b];
         for (int b = 0; b < 65536; ++b) {
             // r = min(R - 1, floor(before * R / total)), stepped instead of divided (before only grows)
             while (r + 1 < (uint64_t)R && (r + 1) * total <= before * (uint64_t)R) ++r;
             bin2rank[b] = (uint8_t)r;
-            before += hist[b];
+            before += 100ull * cntv[b] + gamma100 * twv[b];
         }
     }
     lap.mark();

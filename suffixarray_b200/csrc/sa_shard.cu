@@ -243,6 +243,19 @@ __global__ void ext_fill_kernel(const uint32_t* __restrict__ own_sa, const uint1
     }
 }
 
+// The halos alone (the shard itself is staged piece by piece with device copies, sa_shard_finish_bcast)
+__global__ void ext_halo_kernel(const uint32_t* __restrict__ halo_pos, const uint16_t* __restrict__ halo_lcp, uint32_t m,
+                                uint32_t nleft, uint32_t nright, uint32_t* __restrict__ ext_sa, uint16_t* __restrict__ ext_lcp)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nleft + nright) return;
+    const uint32_t x = i < nleft ? i : i + m;
+    ext_sa[x] = halo_pos[i];
+    ext_lcp[x] = halo_lcp[i];
+}
+
+__global__ void set_u16_kernel(uint16_t* p, uint32_t v) { *p = (uint16_t)v; }
+
 }  // namespace sa
 
 #define SH_REQUIRE(cond, code, ...)            \
@@ -405,7 +418,7 @@ extern "C" int sa_shard_edges(sa_index* idx, uint32_t edge, uint32_t* head_pos, 
 // outs == nullptr: results go to idx->ext_out (extended rank space).
 static int shard_finish_common(sa_index* idx, const uint32_t* left_pos, const uint16_t* left_lcp, uint32_t nleft,
                                uint32_t lcp_first, const uint32_t* right_pos, const uint16_t* right_lcp,
-                               uint32_t nright, const sa::FinishOut* outs)
+                               uint32_t nright, const sa::FinishOut* outs, bool bulk = true)
 {
     cudaStream_t s = idx->stream;
     const uint32_t m = idx->shard_m;
@@ -425,10 +438,14 @@ static int shard_finish_common(sa_index* idx, const uint32_t* left_pos, const ui
         SA_CU(cudaMemcpyAsync(idx->aux[0].as<uint32_t>() + nleft, right_pos, (size_t)nright * 4, cudaMemcpyHostToDevice, s));
         SA_CU(cudaMemcpyAsync(idx->aux[1].as<uint16_t>() + nleft, right_lcp, (size_t)nright * 2, cudaMemcpyHostToDevice, s));
     }
-    sa::ext_fill_kernel<<<(total + 255) / 256, 256, 0, s>>>(idx->shard_sa, idx->lcp.as<uint16_t>(), m,
-                                                            idx->aux[0].as<uint32_t>(), idx->aux[1].as<uint16_t>(), nleft,
-                                                            nright, lcp_first, idx->ext_sa.as<uint32_t>(),
-                                                            idx->ext_lcp.as<uint16_t>());
+    if (bulk)
+        sa::ext_fill_kernel<<<(total + 255) / 256, 256, 0, s>>>(idx->shard_sa, idx->lcp.as<uint16_t>(), m,
+                                                                idx->aux[0].as<uint32_t>(), idx->aux[1].as<uint16_t>(), nleft,
+                                                                nright, lcp_first, idx->ext_sa.as<uint32_t>(),
+                                                                idx->ext_lcp.as<uint16_t>());
+    else if (nh)
+        sa::ext_halo_kernel<<<(nh + 255) / 256, 256, 0, s>>>(idx->aux[0].as<uint32_t>(), idx->aux[1].as<uint16_t>(), m, nleft, nright,
+                                                             idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>());
     SA_CU(cudaGetLastError());
     idx->stats.kernel_launches += 1;
     const uint32_t r_begin = nleft - (nleft < 32 ? nleft : 32);
@@ -611,13 +628,45 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     fo.lo = nleft;
     fo.hi = nleft + m;
     fo.out[0] = peer_base[my_rank] + global_offset - nleft;
-    int rc = shard_finish_common(idx, left_pos, left_lcp, nleft, lcp_first, right_pos, right_lcp, nright, &fo);
+    // the halos go into the [left halo | shard | right halo] arrays with a small kernel; the shard itself follows in
+    // pieces -- device copies on a second stream, piece c + 1 beside the finishing kernels of chunk c
+    const bool staged = idx->dbg_ext_fill == 0;
+    int rc = shard_finish_common(idx, left_pos, left_lcp, nleft, lcp_first, right_pos, right_lcp, nright, &fo, !staged);
     if (rc != SA_OK) return rc;
     const uint32_t total = nleft + m + nright;
     const uint32_t r_begin = nleft - (nleft < 32 ? nleft : 32);
     const uint32_t r_end = nleft + m + (nright < 32 ? nright : 32);
     const uint32_t blocks = sa_finish_blocks(total), FTR = sa_finish_block_ranks();
     const uint32_t per = (blocks + CHUNKS - 1) / CHUNKS;
+    if (staged) {
+        if (!idx->push_stream) SA_CU(cudaStreamCreateWithPriority(&idx->push_stream, cudaStreamNonBlocking, prio_hi));
+        for (int c = 0; c <= CHUNKS; ++c)
+            if (!idx->ext_ev[c]) SA_CU(cudaEventCreateWithFlags(&idx->ext_ev[c], cudaEventDisableTiming));
+        cudaStream_t ps = idx->push_stream;
+        SA_CU(cudaEventRecord(idx->ext_ev[CHUNKS], s));          // sorted shard + halos are in place
+        SA_CU(cudaStreamWaitEvent(ps, idx->ext_ev[CHUNKS], 0));
+        uint64_t done = 0;                                        // records of the shard staged so far
+        for (int c = 0; c < CHUNKS && (uint64_t)c * per < blocks; ++c) {
+            // chunk c reads LCPs up to 96 ranks past its last block
+            const bool last = (uint64_t)(c + 1) * per >= blocks;
+            uint64_t need = last ? (uint64_t)total : (uint64_t)((uint64_t)c * per + per) * FTR + 128;
+            if (need > total) need = total;
+            uint64_t hi = need > nleft ? need - nleft : 0;
+            if (hi > m) hi = m;
+            if (hi > done) {
+                SA_CU(cudaMemcpyAsync(idx->ext_sa.as<uint32_t>() + nleft + done, idx->shard_sa + done, (size_t)(hi - done) * 4,
+                                      cudaMemcpyDeviceToDevice, ps));
+                SA_CU(cudaMemcpyAsync(idx->ext_lcp.as<uint16_t>() + nleft + done, idx->lcp.as<uint16_t>() + done, (size_t)(hi - done) * 2,
+                                      cudaMemcpyDeviceToDevice, ps));
+                if (done == 0) {                                  // the first record's LCP is the junction with the left halo
+                    sa::set_u16_kernel<<<1, 1, 0, ps>>>(idx->ext_lcp.as<uint16_t>() + nleft, lcp_first);
+                    SA_CU(cudaGetLastError());
+                }
+                done = hi;
+            }
+            SA_CU(cudaEventRecord(idx->ext_ev[c], ps));
+        }
+    }
     uint32_t copied_to = nleft;               // extended rank up to which the peers are up to date
     // sa_debug_set("timeline", 1): when each chunk was finished / pushed, in ms after the first launch
     const bool tl = idx->dbg_timeline != 0;
@@ -631,6 +680,7 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     const unsigned rep_ctas = idx->dbg_replicate_ctas > 0 ? (unsigned)idx->dbg_replicate_ctas : (idx->dbg_replicate_ctas < 0 ? 0u : 64u);
     for (int c = 0; c < CHUNKS && (uint64_t)c * per < blocks; ++c) {
         const uint32_t b0 = (uint32_t)c * per;
+        if (staged) SA_CU(cudaStreamWaitEvent(s, idx->ext_ev[c], 0));
         rc = sa_stage_finish_to(idx, idx->ext_sa.as<uint32_t>(), idx->ext_lcp.as<uint16_t>(), total, r_begin, r_end, fo, b0, per);
         if (rc != SA_OK) return rc;
         SA_CU(cudaEventRecord(idx->chunk_ev[c], s));
