@@ -92,15 +92,38 @@ __device__ __forceinline__ void put(const FinishOut& o, int64_t x, uint32_t pos)
     for (int g = 0; g < o.n; ++g) __stcs(o.out[g] + x, pos);
 }
 
+// STAGED (a sharded build that replicates: outs.n > 1): positions that land inside the block's own 1024 ranks are
+// collected in shared memory and leave as 16-byte stores -- one per replica, i.e. the push of the finished ranks
+// into every peer's array over NVLink happens inside this kernel, block by block, instead of in a copy kernel that
+// re-reads the local array afterwards.  Positions that land in a neighbouring block's ranks (a bucket may reach 31
+// ranks across the boundary) go out as single stores right away; slots nobody wrote keep the sentinel and are
+// skipped (a neighbour, or nobody -- ranks outside [lo, hi) -- owns them).
+constexpr uint32_t FSENT = 0xFFFFFFFFu;      // not a text position: n < 2^32 - 1024
+
+template <bool STAGED>
+__device__ __forceinline__ void place(const FinishOut& o, uint32_t* s_out, int64_t b0, int64_t x, uint32_t pos)
+{
+    if (!STAGED) { put(o, x, pos); return; }
+    if (x < (int64_t)o.lo || x >= (int64_t)o.hi) return;
+    const int64_t j = x - b0;
+    if (j >= 0 && j < FT) { s_out[j] = pos; return; }
+#pragma unroll 1
+    for (int g = 0; g < o.n; ++g) __stcs(o.out[g] + x, pos);
+}
+
+template <bool STAGED>
 __global__ void __launch_bounds__(FTHREADS)
 finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ lcp,
               const uint8_t* __restrict__ text, uint32_t n, uint32_t lprime, uint32_t r_begin, uint32_t r_end,
               const FinishOut outs, unsigned long long* __restrict__ run_counter, uint32_t* __restrict__ err,
               uint32_t block0)
 {
-    __shared__ int16_t s_l[FLCP];        // adjacent LCPs, -1 outside [1, n)
-    __shared__ int16_t s_p[FLCP];        // block prefix min of l, later block prefix max of m
-    __shared__ int16_t s_s[FLCP];        // block suffix min of l, later block suffix max of m
+    __shared__ __align__(16) int16_t s_lps[3 * FLCP];
+    int16_t* const s_l = s_lps;              // adjacent LCPs, -1 outside [1, n)
+    int16_t* const s_p = s_lps + FLCP;       // block prefix min of l, later block prefix max of m
+    int16_t* const s_s = s_lps + 2 * FLCP;   // block suffix min of l, later block suffix max of m
+    uint32_t* const s_out = reinterpret_cast<uint32_t*>(s_lps);   // STAGED: the block's FT output slots (phase D on: s_l/s_p/s_s are dead)
+    static_assert(3 * FLCP * sizeof(int16_t) >= FT * sizeof(uint32_t), "output slots fit into the LCP arrays");
     __shared__ uint64_t s_hi[FEXT], s_lo[FEXT], s_tp[FEXT];   // window key words; tp = byte16 << 32 | pos
     __shared__ uint32_t s_head[FEXT / 32 + 2], s_sort[FEXT / 32 + 2];
     __shared__ uint32_t s_runs;
@@ -207,6 +230,10 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
     }
     if (tid == 0) { s_head[FEXT / 32] = 0xFFFFFFFFu; s_sort[FEXT / 32] = 0; }
     __syncthreads();
+    if (STAGED) {
+        for (int j = tid; j < FT; j += FTHREADS) s_out[j] = FSENT;
+        __syncthreads();
+    }
 
     // D: rank inside the bucket
     uint32_t my_runs = 0;
@@ -217,23 +244,51 @@ finish_kernel(const uint32_t* __restrict__ sa_in, const uint16_t* __restrict__ l
         const int e = t + 32, q = e >> 5, i = e & 31;
         const uint64_t tp = s_tp[e];
         const uint32_t pos = (uint32_t)tp;
-        if (!((s_sort[q] >> i) & 1u)) { put(outs, r, pos); continue; }
+        if (!((s_sort[q] >> i) & 1u)) { place<STAGED>(outs, s_out, b0, r, pos); continue; }
         // bucket = [first, last]: last head at or before e, next head after e
         const uint64_t X = (((uint64_t)s_head[q] << 32) | s_head[q - 1]) & (~0ull >> (31 - i));
         const int first = (q - 1) * 32 + (63 - __clzll((long long)X));
         const uint64_t Y = ((((uint64_t)s_head[q + 1] << 32) | s_head[q]) >> i) >> 1;
         const int last = Y ? e + __ffsll((long long)Y) - 1 : e + 32;
-        if (X == 0 || last - first + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); put(outs, r, pos); continue; }
+        if (X == 0 || last - first + 1 > SA_SMALL) { atomicOr(err, SA_DEVERR_RUN_TOO_LONG); place<STAGED>(outs, s_out, b0, r, pos); continue; }
         const uint64_t hi = s_hi[e], lo = s_lo[e];
         uint32_t rank = 0;
         for (int x = first; x <= last; ++x)                 // branch-free (key, byte 16, position) compare
             rank -= less192(s_hi[x], s_lo[x], s_tp[x], hi, lo, tp);
-        put(outs, r - (e - first) + rank, pos);
+        place<STAGED>(outs, s_out, b0, r - (e - first) + rank, pos);
         if (e == first) ++my_runs;
     }
     if (my_runs) atomicAdd(&s_runs, my_runs);
     __syncthreads();
     if (tid == 0 && s_runs) atomicAdd(run_counter, (unsigned long long)s_runs);
+    if (STAGED) {
+        // the block's slots, in groups of four aligned to 16 bytes in the output arrays (all replicas share the alignment:
+        // same offset into 256-byte aligned allocations); a group with an empty slot or at the ragged ends goes out singly
+        const int mis = (int)((reinterpret_cast<uintptr_t>(outs.out[0] + b0) >> 2) & 3u);
+        for (int q = tid; q <= FT / 4; q += FTHREADS) {
+            const int j0 = 4 * q - mis;
+            uint32_t v[4];
+            bool all = true;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = j0 + u;
+                v[u] = (j >= 0 && j < FT) ? s_out[j] : FSENT;
+                all = all && v[u] != FSENT;
+            }
+            if (all) {
+                const uint4 w = make_uint4(v[0], v[1], v[2], v[3]);
+#pragma unroll 1
+                for (int g = 0; g < outs.n; ++g) __stcs(reinterpret_cast<uint4*>(outs.out[g] + (b0 + j0)), w);
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (v[u] == FSENT) continue;
+#pragma unroll 1
+                    for (int g = 0; g < outs.n; ++g) __stcs(outs.out[g] + (b0 + j0 + u), v[u]);
+                }
+            }
+        }
+    }
 }
 
 }  // namespace sa
@@ -247,8 +302,13 @@ cudaError_t sa_launch_finish(const uint32_t* sa_in, const uint16_t* lcp, const u
     const uint32_t blocks = sa_finish_blocks(n);
     if (block0 >= blocks) return cudaSuccess;
     if (nblocks > blocks - block0) nblocks = blocks - block0;
-    sa::finish_kernel<<<nblocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, outs, run_counter, err,
-                                                       block0);
+    // several replicas (a sharded build that replicates): the push into the peers' arrays is fused into the kernel
+    if (outs.n > 1)
+        sa::finish_kernel<true><<<nblocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, outs, run_counter,
+                                                                 err, block0);
+    else
+        sa::finish_kernel<false><<<nblocks, sa::FTHREADS, 0, s>>>(sa_in, lcp, text, n, lprime, r_begin, r_end, outs, run_counter,
+                                                                  err, block0);
     return cudaGetLastError();
 }
 

@@ -191,6 +191,7 @@ extern "C" int sa_debug_set(sa_index* idx, const char* key, int64_t value)
     else if (!strcmp(key, "finish_chunks")) idx->dbg_finish_chunks = value;
     else if (!strcmp(key, "text_push")) idx->dbg_text_push = value;
     else if (!strcmp(key, "ext_fill")) idx->dbg_ext_fill = value;
+    else if (!strcmp(key, "replicate_fused")) idx->dbg_replicate_fused = value;
     else if (!strcmp(key, "split_gamma_x100")) idx->dbg_split_gamma_x100 = value;
     else if (!strcmp(key, "same_process")) idx->dbg_same_process = value;
     else if (!strcmp(key, "query_kernel")) idx->dbg_query_kernel = value;

@@ -187,6 +187,7 @@ struct sa_index {
     int64_t dbg_replicate_ctas = 0; // sharded finish: k > 0 = 512-thread push kernel with k blocks (0: 64); k < 0 = the 128-thread co-resident kernel
     int64_t dbg_text_push = 0;      // sharded build: 0 = text slices travel on the copy engines beside pack / exchange; 1 = blocking push kernel
     int64_t dbg_split_gamma_x100 = -1;   // sharded build: extra cost of a record whose first-sort key repeats, in 1/100 records (-1: 170; 0: equal counts)
+    int64_t dbg_replicate_fused = 1;    // sharded finish: 1 = finish_kernel stores into every replica itself; 0 = replicate_kernel pushes finished chunks
     int64_t dbg_ext_fill = 0;       // sharded finish: 1 = one kernel copies the whole shard into the ext arrays first (round-1 behaviour)
     int64_t dbg_finish_chunks = 0;  // sharded finish: chunks the shard is finished / pushed in (0: 8; at most 16)
     int64_t dbg_csv_scanner = 0;    // 0: device scan, host scan for irregular files; 1: host scan; 2: device scan or fail

@@ -4,15 +4,19 @@
 // Python loop over torch.distributed.  Bulk data never touches it: text slices, (key, position) records
 // and finished array slices move GPU to GPU as peer stores over NVLink.
 //
-//   text      every rank uploads ITS slice of the text and pushes it into every peer's text buffer
-//             (the whole text is never sent over PCIe more than once per node)
+//   text      every rank uploads ITS slice; after one barrier it pulls the few KB of its own position range that
+//             another rank uploaded and hands its slice to the copy engines (one copy per peer): the all-gather
+//             of the text over NVLink runs beside the next four stages (the whole text is never sent over PCIe
+//             more than once per node)
 //   prepare   newline table + byte presence on the rank's slice of positions, exchanged / pushed;
-//             the alphabet codes of the whole text are computed locally (cheaper than NVLink)
-//   pack      round-0 keys of the slice + 65536-bin histogram; sum over ranks -> splitters
+//             the alphabet codes are computed locally (cheaper than NVLink): own range now, the rest before the sort
+//   pack      round-0 keys of the slice + two 65536-bin histograms of a sample (keys, keys with a twin in the
+//             sample); summed over ranks -> splitters by equal share of the expected work
 //   exchange  split_scatter_p2p_kernel: records stored straight into the owner's sort buffers
 //   sort      onesweep LSD sort + tie refinement of the received key range
 //   edges     first / last 128 records of every shard; junction LCPs computed on the device
-//   finish    <= 32 bucket finish in chunks, each finished chunk pushed into every peer's final array
+//   finish    <= 32 bucket finish; every finished block leaves finish_kernel as 16-byte stores into this rank's
+//             AND every peer's final array (the replication is fused into the kernel)
 //
 // Communicators: sa_comm_create_local (ranks are threads of one process: sa_build_text_multi,
 // SuffixArray(devices=[...])) and sa_comm_create_shm (one process per GPU on one node -- torchrun: a

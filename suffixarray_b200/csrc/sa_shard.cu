@@ -543,13 +543,15 @@ __global__ void __launch_bounds__(REP_THREADS, 16) replicate_small_kernel(const 
 }
 }  // namespace sa
 
-// ------------------------------------------------------------------------------ finish + replicate, overlapped
-// Instead of "finish into a local slice, all-gather the slices, copy into place", the shard is
-// finished in chunks straight into this rank's final array, and while chunk c+1 is being finished
-// chunk c is pushed into every peer's final array (device-to-device copies over NVLink into CUDA IPC
-// mappings, on a second stream): replication hides behind the finishing kernels and the gather /
-// adopt passes disappear.  (Letting finish_kernel itself store to all peers works too -- FinishOut
-// carries up to 16 replicas -- but 4-byte peer stores reach only ~260 GB/s at 8 GPUs.)
+// ------------------------------------------------------------------------------ finish + replicate, fused
+// Instead of "finish into a local slice, all-gather the slices, copy into place", the shard is finished straight
+// into this rank's final array AND into every peer's (CUDA IPC mappings, NVLink): finish_kernel<STAGED> collects the
+// positions of a block's 1024 ranks in shared memory and stores them 16 bytes at a time into all replicas, so the
+// gather / adopt passes and the re-read of the finished array disappear.  (Round 2 measured the alternatives:
+// single 4-byte peer stores from the unstaged kernel reach ~260 GB/s at 8 GPUs; finishing locally in chunks and
+// pushing finished chunks with replicate_kernel on a high-priority stream overlaps, but kernel and push slow each
+// other -- profiles/r02_multi_gpu_phases.md; sa_debug_set("replicate_fused", 0) selects that path.)
+// The shard itself is staged into the [left halo | shard | right halo] arrays in pieces beside the finishing kernels.
 // 1. sa_shard_final_prepare: allocate this rank's final array (n entries) and export its IPC handle.
 extern "C" int sa_shard_final_prepare(sa_index* idx, uint8_t* handle_final)
 {
@@ -628,6 +630,12 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
     fo.lo = nleft;
     fo.hi = nleft + m;
     fo.out[0] = peer_base[my_rank] + global_offset - nleft;
+    // fused (default): finish_kernel<STAGED> stores every finished block into all replicas itself -- 16-byte stores
+    // over NVLink from the block's shared-memory slots -- so nothing is re-read and no copy kernel competes with the
+    // finishing blocks; sa_debug_set("replicate_fused", 0) = finish locally, push finished chunks with replicate_kernel
+    const bool fused = replicate && nranks > 1 && idx->dbg_replicate_fused != 0;
+    if (fused)
+        for (int k = 1; k < nranks; ++k) fo.out[fo.n++] = peer_base[(my_rank + k) % nranks] + global_offset - nleft;
     // the halos go into the [left halo | shard | right halo] arrays with a small kernel; the shard itself follows in
     // pieces -- device copies on a second stream, piece c + 1 beside the finishing kernels of chunk c
     const bool staged = idx->dbg_ext_fill == 0;
@@ -690,7 +698,7 @@ extern "C" int sa_shard_finish_bcast(sa_index* idx, const uint32_t* left_pos, co
         uint64_t upto = last ? (uint64_t)nleft + m : (uint64_t)(b0 + per) * FTR;
         if (!last) upto = upto > 32 ? upto - 32 : 0;
         if (upto > (uint64_t)nleft + m) upto = (uint64_t)nleft + m;
-        if (upto <= copied_to || !replicate) continue;
+        if (upto <= copied_to || !replicate || fused) continue;
         const size_t off = (size_t)global_offset + copied_to - nleft, cnt = (size_t)(upto - copied_to);
         if (idx->dbg_replicate_memcpy) {      // copy engines instead of the store kernel (slower at 8 GPUs)
             for (int k = 1; k < nranks; ++k) {
