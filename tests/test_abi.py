@@ -110,3 +110,19 @@ def test_library_is_usable_from_plain_c(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, (r.stdout, r.stderr)
     assert r.stdout.startswith("ok" if _cuda_available() else "nogpu"), r.stdout
+
+
+def test_newline_tile_arithmetic_at_the_size_limit():
+    """the tile count of the newline scan must not wrap for n close to 2^32 (the sharded build
+    accepts n up to 2^32 - 1026).  Host arithmetic only: `sa_newline_tiles` (query.cu) through its C++ symbol."""
+    L = S.lib()
+    try:
+        f = getattr(L, "_Z16sa_newline_tilesj")
+    except AttributeError:
+        pytest.skip("sa_newline_tiles is not an exported symbol in this build")
+    f.argtypes = [ctypes.c_uint32]
+    f.restype = ctypes.c_uint32
+    tile = 4096
+    for n in (0, 1, tile - 1, tile, tile + 1, (1 << 31) - 1, 1 << 31, (1 << 32) - 4096, (1 << 32) - 4095,
+              (1 << 32) - 1026, (1 << 32) - 1):
+        assert f(n) == (n + tile - 1) // tile, n
